@@ -1,0 +1,716 @@
+// nn_kernels.cu — non-GEMM kernels of the training step (sm_100a, fp32 storage).
+//
+//   * first-layer convolution (C_in = 1) fused with bias + ReLU + 2x2 max-pool, forward and
+//     the matching fused pool-backward + ReLU-backward + filter/bias gradient
+//   * classifier head: Dense(C) + softmax cross-entropy + all of their gradients in one kernel
+//   * stand-alone softmax cross-entropy (+gradient, +accuracy count)
+//   * 2x2 max-pool forward / backward, bias gradient (column sums), ReLU backward
+//   * direct (CUDA-core) convolution fallbacks for shapes the tensor-core path does not take
+//   * SGD apply (+gradient zeroing) for the single-replica case
+//
+// Layouts follow Keras: activations NHWC, conv kernels HWIO, Dense kernels (in, out).
+// Reference behaviour: README.md:292-302 (the layer list, loss, optimizer and metric).
+#include "host_common.h"
+
+namespace b2d {
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// =======================================================================================
+// Conv2D(C_in = 1, KxK, valid, stride 1) + bias + ReLU + MaxPool(2x2)        [K1 + K2]
+//   one CTA = one image x a band of pooled rows; lane = output channel; the image band sits
+//   in shared memory and is read by broadcast; the 26x26xCo conv map never reaches HBM.
+//   code[n,ph,pw,c] = argmax position (0..3 = dy*2+dx) or 4 when ReLU clamped the maximum.
+// =======================================================================================
+template <int KS>
+__global__ void __launch_bounds__(256) conv_c1_pool_fwd_kernel(
+    const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+    float* __restrict__ y, uint8_t* __restrict__ code, int H, int W, int Co, int PH, int PW,
+    int band) {
+  extern __shared__ float xs[];  // [(2*band + KS) rows][W]
+  const int n = blockIdx.x;
+  const int ph0 = blockIdx.y * band;
+  const int ph1 = min(PH, ph0 + band);
+  const int r0 = 2 * ph0;
+  const int r1 = min(H, 2 * ph1 + KS - 1);
+  const float* xi = x + (size_t)n * H * W;
+  for (int i = threadIdx.x; i < (r1 - r0) * W; i += blockDim.x) xs[i] = xi[r0 * W + i];
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
+  const int npix = (ph1 - ph0) * PW;
+  for (int cg = 0; cg < Co; cg += 32) {
+    const int c = cg + lane;
+    const bool c_ok = c < Co;
+    float wr[KS * KS];
+#pragma unroll
+    for (int t = 0; t < KS * KS; ++t) wr[t] = c_ok ? w[t * Co + c] : 0.f;
+    const float bv = c_ok ? bias[c] : 0.f;
+    for (int p = warp; p < npix; p += nwarp) {
+      const int ph = ph0 + p / PW, pw = p % PW;
+      const float* base = xs + (2 * ph - r0) * W + 2 * pw;
+      float win[(KS + 1) * (KS + 1)];
+#pragma unroll
+      for (int i = 0; i < KS + 1; ++i)
+#pragma unroll
+        for (int j = 0; j < KS + 1; ++j) win[i * (KS + 1) + j] = base[i * W + j];
+      float best = -INFINITY;
+      int arg = 0;
+#pragma unroll
+      for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+        for (int dx = 0; dx < 2; ++dx) {
+          float acc = bv;
+#pragma unroll
+          for (int i = 0; i < KS; ++i)
+#pragma unroll
+            for (int j = 0; j < KS; ++j) acc = fmaf(win[(dy + i) * (KS + 1) + dx + j], wr[i * KS + j], acc);
+          if (acc > best) best = acc, arg = dy * 2 + dx;
+        }
+      if (c_ok) {
+        const size_t o = (((size_t)n * PH + ph) * PW + pw) * Co + c;
+        y[o] = fmaxf(best, 0.f);
+        code[o] = best > 0.f ? (uint8_t)arg : (uint8_t)4;
+      }
+    }
+  }
+}
+
+// Fused MaxPool-backward + ReLU-backward + conv filter/bias gradient for the layer above
+// [K8 + K9]: dW[i,j,0,c] += sum g * x[n, 2ph+ay+i, 2pw+ax+j],  db[c] += sum g.
+template <int KS>
+__global__ void __launch_bounds__(256) conv_c1_pool_bwd_kernel(
+    const float* __restrict__ x, const float* __restrict__ dy, const uint8_t* __restrict__ code,
+    float* __restrict__ dw, float* __restrict__ db, int H, int W, int Co, int PH, int PW, int band) {
+  extern __shared__ float sm[];
+  float* xs = sm;  // image band
+  const int n = blockIdx.x;
+  const int ph0 = blockIdx.y * band;
+  const int ph1 = min(PH, ph0 + band);
+  const int r0 = 2 * ph0;
+  const int r1 = min(H, 2 * ph1 + KS - 1);
+  const int band_elems = (2 * band + KS) * W;
+  float* red = sm + band_elems;  // [nwarp][KS*KS+1][32]
+  const float* xi = x + (size_t)n * H * W;
+  for (int i = threadIdx.x; i < (r1 - r0) * W; i += blockDim.x) xs[i] = xi[r0 * W + i];
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
+  const int npix = (ph1 - ph0) * PW;
+  constexpr int NT = KS * KS + 1;
+  for (int cg = 0; cg < Co; cg += 32) {
+    const int c = cg + lane;
+    const bool c_ok = c < Co;
+    float acc[NT];
+#pragma unroll
+    for (int t = 0; t < NT; ++t) acc[t] = 0.f;
+    for (int p = warp; p < npix; p += nwarp) {
+      const int ph = ph0 + p / PW, pw = p % PW;
+      const size_t o = (((size_t)n * PH + ph) * PW + pw) * Co + c;
+      const float g = c_ok ? dy[o] : 0.f;
+      const int cd = c_ok ? code[o] : 4;
+      if (cd < 4) {
+        const float* base = xs + (2 * ph - r0 + (cd >> 1)) * W + 2 * pw + (cd & 1);
+#pragma unroll
+        for (int i = 0; i < KS; ++i)
+#pragma unroll
+          for (int j = 0; j < KS; ++j) acc[i * KS + j] = fmaf(g, base[i * W + j], acc[i * KS + j]);
+        acc[KS * KS] += g;
+      }
+    }
+#pragma unroll
+    for (int t = 0; t < NT; ++t) red[(warp * NT + t) * 32 + lane] = acc[t];
+    __syncthreads();
+    for (int i = threadIdx.x; i < NT * 32; i += blockDim.x) {
+      const int t = i / 32, l = i % 32;
+      float s = 0.f;
+      for (int wv = 0; wv < nwarp; ++wv) s += red[(wv * NT + t) * 32 + l];
+      const int cc = cg + l;
+      if (cc < Co) {
+        if (t < KS * KS)
+          atomicAdd(&dw[t * Co + cc], s);
+        else
+          atomicAdd(&db[cc], s);
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// =======================================================================================
+// Classifier head: logits = h.W + b ; softmax cross-entropy ; all gradients.   [K4+K5+K6]
+//   one warp per batch row; W (K x C) lives in shared memory; dW/db partials are accumulated
+//   in shared memory and flushed with one global atomic per element per CTA.
+//   metrics[0] += sum of per-row losses, metrics[1] += #correct, metrics[2] += #rows.
+//   dh[r,k] = (sum_c dz[r,c] W[k,c]) * (h[r,k] > 0 if relu_mask)
+// =======================================================================================
+constexpr int kHeadMaxC = 32;
+
+__global__ void __launch_bounds__(256) dense_xent_head_kernel(
+    const float* __restrict__ h, const float* __restrict__ w, const float* __restrict__ bias,
+    const int* __restrict__ labels, float* __restrict__ logits_out, float* __restrict__ dh,
+    float* __restrict__ dw, float* __restrict__ db, float* __restrict__ metrics, int B, int K, int C,
+    float grad_scale, int relu_mask, int rows_per_cta) {
+  extern __shared__ float sm[];
+  float* ws = sm;            // [K][C]
+  float* dws = ws + K * C;   // [K][C]
+  float* dbs = dws + K * C;  // [C]
+  float* mts = dbs + kHeadMaxC;  // [2]
+  for (int i = threadIdx.x; i < K * C; i += blockDim.x) ws[i] = w[i], dws[i] = 0.f;
+  if (threadIdx.x < kHeadMaxC) dbs[threadIdx.x] = 0.f;
+  if (threadIdx.x < 2) mts[threadIdx.x] = 0.f;
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
+  const int row0 = blockIdx.x * rows_per_cta;
+  const int row1 = min(B, row0 + rows_per_cta);
+  for (int r = row0 + warp; r < row1; r += nwarp) {
+    const float* hr = h + (size_t)r * K;
+    float z[kHeadMaxC];
+#pragma unroll
+    for (int c = 0; c < kHeadMaxC; ++c) z[c] = 0.f;
+    for (int k = lane; k < K; k += 32) {
+      const float hv = hr[k];
+#pragma unroll
+      for (int c = 0; c < kHeadMaxC; ++c)
+        if (c < C) z[c] = fmaf(hv, ws[k * C + c], z[c]);
+    }
+    float mx = -INFINITY;
+    int arg = 0;
+#pragma unroll
+    for (int c = 0; c < kHeadMaxC; ++c)
+      if (c < C) {
+        z[c] = warp_sum(z[c]) + bias[c];
+        if (z[c] > mx) mx = z[c], arg = c;
+      }
+    const int yl = labels[r];
+    float se = 0.f, zy = 0.f;
+#pragma unroll
+    for (int c = 0; c < kHeadMaxC; ++c)
+      if (c < C) {
+        se += __expf(z[c] - mx);
+        if (c == yl) zy = z[c];
+      }
+    const float lse = mx + __logf(se);
+    const float inv = 1.f / se;
+#pragma unroll
+    for (int c = 0; c < kHeadMaxC; ++c)
+      if (c < C) {
+        if (logits_out != nullptr && lane == 0) logits_out[(size_t)r * C + c] = z[c];
+        z[c] = (__expf(z[c] - mx) * inv - (c == yl ? 1.f : 0.f)) * grad_scale;  // dz
+      }
+    if (lane == 0) {
+      atomicAdd(&mts[0], lse - zy);
+      atomicAdd(&mts[1], arg == yl ? 1.f : 0.f);
+    }
+    if (lane < C) {
+      float dzl = 0.f;
+#pragma unroll
+      for (int c = 0; c < kHeadMaxC; ++c)
+        if (c == lane) dzl = z[c];
+      atomicAdd(&dbs[lane], dzl);
+    }
+    for (int k = lane; k < K; k += 32) {
+      const float hv = hr[k];
+      float g = 0.f;
+#pragma unroll
+      for (int c = 0; c < kHeadMaxC; ++c)
+        if (c < C) {
+          g = fmaf(z[c], ws[k * C + c], g);
+          atomicAdd(&dws[k * C + c], hv * z[c]);
+        }
+      if (dh != nullptr) dh[(size_t)r * K + k] = (relu_mask && !(hv > 0.f)) ? 0.f : g;
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < K * C; i += blockDim.x) atomicAdd(&dw[i], dws[i]);
+  if (threadIdx.x < C) atomicAdd(&db[threadIdx.x], dbs[threadIdx.x]);
+  if (threadIdx.x == 0 && metrics != nullptr) {
+    atomicAdd(&metrics[0], mts[0]);
+    atomicAdd(&metrics[1], mts[1]);
+    atomicAdd(&metrics[2], (float)(row1 - row0));
+  }
+}
+
+// Stand-alone softmax cross-entropy on logits [B][C] (any C): one warp per row.   [K5]
+__global__ void __launch_bounds__(256) softmax_xent_kernel(const float* __restrict__ z,
+                                                            const int* __restrict__ labels,
+                                                            float* __restrict__ dz,
+                                                            float* __restrict__ metrics, int B, int C,
+                                                            float grad_scale) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= B) return;
+  const float* zr = z + (size_t)warp * C;
+  float mx = -INFINITY;
+  int arg = 0x7fffffff;
+  for (int c = lane; c < C; c += 32) {
+    const float v = zr[c];
+    if (v > mx) mx = v, arg = c;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {  // argmax with lowest-index tie-break
+    const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+    const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+    if (om > mx || (om == mx && oa < arg)) mx = om, arg = oa;
+  }
+  float se = 0.f;
+  for (int c = lane; c < C; c += 32) se += __expf(zr[c] - mx);
+  se = warp_sum(se);
+  const int yl = labels[warp];
+  const float inv = 1.f / se;
+  if (dz != nullptr)
+    for (int c = lane; c < C; c += 32)
+      dz[(size_t)warp * C + c] = (__expf(zr[c] - mx) * inv - (c == yl ? 1.f : 0.f)) * grad_scale;
+  if (lane == 0 && metrics != nullptr) {
+    atomicAdd(&metrics[0], mx + __logf(se) - zr[yl]);
+    atomicAdd(&metrics[1], arg == yl ? 1.f : 0.f);
+    atomicAdd(&metrics[2], 1.f);
+  }
+}
+
+// =======================================================================================
+// MaxPool 2x2 / stride 2 (NHWC), forward with argmax code and backward (optionally fused with
+// the ReLU backward of the producing layer: act_relu => gradient is dropped where y <= 0).
+// =======================================================================================
+__global__ void maxpool2_fwd_kernel(const float* __restrict__ x, float* __restrict__ y,
+                                    uint8_t* __restrict__ code, int N, int H, int W, int C, int PH,
+                                    int PW) {
+  const size_t total = (size_t)N * PH * PW * C;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const int c = i % C;
+    size_t t = i / C;
+    const int pw = t % PW;
+    t /= PW;
+    const int ph = t % PH;
+    const int n = t / PH;
+    const float* b = x + (((size_t)n * H + 2 * ph) * W + 2 * pw) * C + c;
+    float best = b[0];
+    int arg = 0;
+    float v = b[C];
+    if (v > best) best = v, arg = 1;
+    v = b[(size_t)W * C];
+    if (v > best) best = v, arg = 2;
+    v = b[(size_t)W * C + C];
+    if (v > best) best = v, arg = 3;
+    y[i] = best;
+    code[i] = (uint8_t)arg;
+  }
+}
+
+__global__ void maxpool2_bwd_kernel(const float* __restrict__ dy, const uint8_t* __restrict__ code,
+                                    const float* __restrict__ y_pooled, float* __restrict__ dx, int N,
+                                    int H, int W, int C, int PH, int PW, int act_relu) {
+  const size_t total = (size_t)N * H * W * C;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const int c = i % C;
+    size_t t = i / C;
+    const int w = t % W;
+    t /= W;
+    const int hh = t % H;
+    const int n = t / H;
+    const int ph = hh >> 1, pw = w >> 1;
+    float g = 0.f;
+    if (ph < PH && pw < PW) {
+      const size_t o = (((size_t)n * PH + ph) * PW + pw) * C + c;
+      if (code[o] == ((hh & 1) * 2 + (w & 1)) && !(act_relu && !(y_pooled[o] > 0.f))) g = dy[o];
+    }
+    dx[i] = g;
+  }
+}
+
+// Column sums: db[n] += sum_m dy[m][n]   (bias gradient)                         [K6/K7]
+__global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ dy,
+                                                      float* __restrict__ db, int M, int N,
+                                                      int rows_per_cta) {
+  __shared__ float part[8][33];
+  const int col = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int wy = threadIdx.x >> 5;
+  const int r0 = blockIdx.y * rows_per_cta, r1 = min(M, r0 + rows_per_cta);
+  float s = 0.f;
+  if (col < N)
+    for (int r = r0 + wy; r < r1; r += 8) s += dy[(size_t)r * N + col];
+  part[wy][threadIdx.x & 31] = s;
+  __syncthreads();
+  if (wy == 0 && col < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += part[k][threadIdx.x];
+    atomicAdd(&db[col], t);
+  }
+}
+
+// dx = dy where y > 0 else 0 (in place allowed).
+__global__ void relu_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y,
+                                float* __restrict__ dx, size_t n) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x)
+    dx[i] = y[i] > 0.f ? dy[i] : 0.f;
+}
+
+// =======================================================================================
+// Direct convolution fallbacks (any stride / zero padding, NHWC x HWIO).  Correct for every
+// shape; used where the tensor-core implicit GEMM does not apply (e.g. C_in * 4 B < 16 B).
+// =======================================================================================
+struct ConvShape {
+  int N, H, W, Ci, Co, KH, KW, OH, OW, sh, sw, ph, pw;
+};
+
+__global__ void conv2d_fwd_direct_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                         const float* __restrict__ bias, float* __restrict__ y,
+                                         ConvShape s, int relu) {
+  const size_t total = (size_t)s.N * s.OH * s.OW * s.Co;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const int co = i % s.Co;
+    size_t t = i / s.Co;
+    const int ow = t % s.OW;
+    t /= s.OW;
+    const int oh = t % s.OH;
+    const int n = t / s.OH;
+    float acc = bias != nullptr ? bias[co] : 0.f;
+    for (int kh = 0; kh < s.KH; ++kh) {
+      const int ih = oh * s.sh - s.ph + kh;
+      if (ih < 0 || ih >= s.H) continue;
+      for (int kw = 0; kw < s.KW; ++kw) {
+        const int iw = ow * s.sw - s.pw + kw;
+        if (iw < 0 || iw >= s.W) continue;
+        const float* xp = x + (((size_t)n * s.H + ih) * s.W + iw) * s.Ci;
+        const float* wp = w + ((size_t)(kh * s.KW + kw) * s.Ci) * s.Co + co;
+        for (int ci = 0; ci < s.Ci; ++ci) acc = fmaf(xp[ci], wp[(size_t)ci * s.Co], acc);
+      }
+    }
+    y[i] = relu ? fmaxf(acc, 0.f) : acc;
+  }
+}
+
+// dx[n,ih,iw,ci] = sum_{kh,kw,co} dy[n,oh,ow,co] * w[kh,kw,ci,co]
+__global__ void conv2d_dgrad_direct_kernel(const float* __restrict__ dy, const float* __restrict__ w,
+                                           float* __restrict__ dx, ConvShape s) {
+  const size_t total = (size_t)s.N * s.H * s.W * s.Ci;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const int ci = i % s.Ci;
+    size_t t = i / s.Ci;
+    const int iw = t % s.W;
+    t /= s.W;
+    const int ih = t % s.H;
+    const int n = t / s.H;
+    float acc = 0.f;
+    for (int kh = 0; kh < s.KH; ++kh) {
+      const int th = ih + s.ph - kh;
+      if (th < 0 || th % s.sh) continue;
+      const int oh = th / s.sh;
+      if (oh >= s.OH) continue;
+      for (int kw = 0; kw < s.KW; ++kw) {
+        const int tw = iw + s.pw - kw;
+        if (tw < 0 || tw % s.sw) continue;
+        const int ow = tw / s.sw;
+        if (ow >= s.OW) continue;
+        const float* dp = dy + (((size_t)n * s.OH + oh) * s.OW + ow) * s.Co;
+        const float* wp = w + ((size_t)(kh * s.KW + kw) * s.Ci + ci) * s.Co;
+        for (int co = 0; co < s.Co; ++co) acc = fmaf(dp[co], wp[co], acc);
+      }
+    }
+    dx[i] = acc;
+  }
+}
+
+// dW[kh,kw,ci,co] += sum_{n,oh,ow} x[n,ih,iw,ci] * dy[n,oh,ow,co]; one CTA per (kh,kw,ci) x co-tile,
+// threads stride over output pixels and reduce through shared memory.
+__global__ void __launch_bounds__(256) conv2d_wgrad_direct_kernel(const float* __restrict__ x,
+                                                                   const float* __restrict__ dy,
+                                                                   float* __restrict__ dw,
+                                                                   ConvShape s) {
+  __shared__ float part[8][33];
+  const int tap = blockIdx.x;  // (kh*KW + kw)*Ci + ci
+  const int ci = tap % s.Ci;
+  const int kw = (tap / s.Ci) % s.KW;
+  const int kh = tap / (s.Ci * s.KW);
+  const int co = blockIdx.y * 32 + (threadIdx.x & 31);
+  const int wy = threadIdx.x >> 5;
+  const size_t npix = (size_t)s.N * s.OH * s.OW;
+  float acc = 0.f;
+  if (co < s.Co)
+    for (size_t p = wy; p < npix; p += 8) {
+      const int ow = p % s.OW;
+      const int oh = (p / s.OW) % s.OH;
+      const int n = p / ((size_t)s.OW * s.OH);
+      const int ih = oh * s.sh - s.ph + kh, iw = ow * s.sw - s.pw + kw;
+      if (ih < 0 || ih >= s.H || iw < 0 || iw >= s.W) continue;
+      acc = fmaf(x[(((size_t)n * s.H + ih) * s.W + iw) * s.Ci + ci], dy[p * s.Co + co], acc);
+    }
+  part[wy][threadIdx.x & 31] = acc;
+  __syncthreads();
+  if (wy == 0 && co < s.Co) {
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += part[k][threadIdx.x];
+    atomicAdd(&dw[(size_t)tap * s.Co + co], t);
+  }
+}
+
+// =======================================================================================
+// CUDA-core GEMM fallback with arbitrary strides (tiny or unaligned problems, e.g. N = 10).
+//   D[m][n] (+)= relu?( sum_k A(m,k) B(k,n) + bias[n] )
+// =======================================================================================
+__global__ void __launch_bounds__(256) sgemm_simt_kernel(const float* __restrict__ A, long long sam,
+                                                          long long sak, const float* __restrict__ Bm,
+                                                          long long sbk, long long sbn,
+                                                          float* __restrict__ D, long long ldd,
+                                                          const float* __restrict__ bias, int M, int N,
+                                                          int K, int relu, int accumulate) {
+  __shared__ float as[32][33], bs[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  const int m0 = blockIdx.y * 32, n0 = blockIdx.x * 32;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int k0 = 0; k0 < K; k0 += 32) {
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int rr = ty + r * 8;
+      const int m = m0 + rr, k = k0 + tx;
+      as[rr][tx] = (m < M && k < K) ? A[m * sam + k * sak] : 0.f;
+      const int kk = k0 + rr, n = n0 + tx;
+      bs[rr][tx] = (kk < K && n < N) ? Bm[kk * sbk + n * sbn] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 32; ++k) {
+      const float bv = bs[k][tx];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) acc[r] = fmaf(as[ty + r * 8][k], bv, acc[r]);
+    }
+    __syncthreads();
+  }
+  const int n = n0 + tx;
+  if (n < N)
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int m = m0 + ty + r * 8;
+      if (m < M) {
+        float v = acc[r] + (bias != nullptr ? bias[n] : 0.f);
+        if (relu) v = fmaxf(v, 0.f);
+        if (accumulate)
+          atomicAdd(&D[m * ldd + n], v);
+        else
+          D[m * ldd + n] = v;
+      }
+    }
+}
+
+// =======================================================================================
+// Single-replica optimizer step: w -= lr * g ; g = 0 ; running metrics += step metrics. [K13]
+// (With more than one replica this work is fused into the all-reduce kernels instead.)
+// =======================================================================================
+__global__ void sgd_apply_kernel(float* __restrict__ w, float* __restrict__ g, size_t n_params,
+                                 size_t n_total, float lr) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n_total;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const float gv = g[i];
+    w[i] = i < n_params ? w[i] - lr * gv : w[i] + gv;  // tail slots accumulate metrics
+    g[i] = 0.f;
+  }
+}
+
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ src, uint16_t* __restrict__ dst,
+                                     size_t n) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x) {
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(0.f), "f"(src[i]));
+    dst[i] = (uint16_t)(r & 0xffff);
+  }
+}
+
+static inline int grid_for(size_t n, int block = 256, int cap = 148 * 8) {
+  size_t g = (n + block - 1) / block;
+  return (int)(g < 1 ? 1 : (g > (size_t)cap ? cap : g));
+}
+
+}  // namespace b2d
+
+using namespace b2d;
+
+// ---------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------
+extern "C" int b2d_conv_c1_pool_fwd(const float* x, const float* w, const float* bias, float* y,
+                                    uint8_t* code, int N, int H, int W, int Co, int KS,
+                                    void* stream) {
+  B2D_REQUIRE(KS == 3 || KS == 5, "conv_c1_pool: kernel size must be 3 or 5 (got %d)", KS);
+  const int OH = H - KS + 1, OW = W - KS + 1, PH = OH / 2, PW = OW / 2;
+  B2D_REQUIRE(PH > 0 && PW > 0, "conv_c1_pool: input too small");
+  // Two bands per image at small batch keeps >= 128 CTAs in flight for batch 64.
+  const int bands = N >= 296 ? 1 : (N >= 148 ? 2 : 4);
+  const int band = ceil_div(PH, bands);
+  const dim3 grid(N, ceil_div(PH, band));
+  const size_t smem = (size_t)(2 * band + KS) * W * sizeof(float);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (KS == 3)
+    conv_c1_pool_fwd_kernel<3><<<grid, 256, smem, st>>>(x, w, bias, y, code, H, W, Co, PH, PW, band);
+  else
+    conv_c1_pool_fwd_kernel<5><<<grid, 256, smem, st>>>(x, w, bias, y, code, H, W, Co, PH, PW, band);
+  count_launch();
+  B2D_CUDA_CHECK(cudaGetLastError());
+  return B2D_OK;
+}
+
+extern "C" int b2d_conv_c1_pool_bwd(const float* x, const float* dy, const uint8_t* code, float* dw,
+                                    float* db, int N, int H, int W, int Co, int KS, void* stream) {
+  B2D_REQUIRE(KS == 3 || KS == 5, "conv_c1_pool: kernel size must be 3 or 5 (got %d)", KS);
+  const int OH = H - KS + 1, OW = W - KS + 1, PH = OH / 2, PW = OW / 2;
+  const int bands = N >= 296 ? 1 : (N >= 148 ? 2 : 4);
+  const int band = ceil_div(PH, bands);
+  const dim3 grid(N, ceil_div(PH, band));
+  const size_t smem = ((size_t)(2 * band + KS) * W + 8 * (KS * KS + 1) * 32) * sizeof(float);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (KS == 3)
+    conv_c1_pool_bwd_kernel<3><<<grid, 256, smem, st>>>(x, dy, code, dw, db, H, W, Co, PH, PW, band);
+  else
+    conv_c1_pool_bwd_kernel<5><<<grid, 256, smem, st>>>(x, dy, code, dw, db, H, W, Co, PH, PW, band);
+  count_launch();
+  B2D_CUDA_CHECK(cudaGetLastError());
+  return B2D_OK;
+}
+
+extern "C" int b2d_dense_xent_head(const float* h, const float* w, const float* bias,
+                                   const int* labels, float* logits_out, float* dh, float* dw,
+                                   float* db, float* metrics, int B, int K, int C, float grad_scale,
+                                   int relu_mask, void* stream) {
+  B2D_REQUIRE(C >= 1 && C <= kHeadMaxC, "dense_xent_head: C must be in [1, %d]", kHeadMaxC);
+  const size_t smem = ((size_t)2 * K * C + kHeadMaxC + 2) * sizeof(float);
+  B2D_REQUIRE(smem <= 200 * 1024, "dense_xent_head: K*C too large for the fused head (K=%d C=%d)", K, C);
+  static bool attr_set = false;
+  if (!attr_set) {
+    B2D_CUDA_CHECK(cudaFuncSetAttribute(dense_xent_head_kernel,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    attr_set = true;
+  }
+  // 8 rows (one per warp) per CTA at small batch; more rows per CTA once the grid is full.
+  const int rows = B <= 8 * 148 ? 8 : ceil_div(B, 148 * 2);
+  dense_xent_head_kernel<<<ceil_div(B, rows), 256, smem, static_cast<cudaStream_t>(stream)>>>(
+      h, w, bias, labels, logits_out, dh, dw, db, metrics, B, K, C, grad_scale, relu_mask, rows);
+  count_launch();
+  B2D_CUDA_CHECK(cudaGetLastError());
+  return B2D_OK;
+}
+
+extern "C" int b2d_softmax_xent(const float* logits, const int* labels, float* dlogits,
+                                float* metrics, int B, int C, float grad_scale, void* stream) {
+  softmax_xent_kernel<<<ceil_div(B * 32, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      logits, labels, dlogits, metrics, B, C, grad_scale);
+  count_launch();
+  B2D_CUDA_CHECK(cudaGetLastError());
+  return B2D_OK;
+}
+
+extern "C" int b2d_maxpool2_fwd(const float* x, float* y, uint8_t* code, int N, int H, int W, int C,
+                                void* stream) {
+  const int PH = H / 2, PW = W / 2;
+  maxpool2_fwd_kernel<<<grid_for((size_t)N * PH * PW * C), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      x, y, code, N, H, W, C, PH, PW);
+  count_launch();
+  B2D_CUDA_CHECK(cudaGetLastError());
+  return B2D_OK;
+}
+
+extern "C" int b2d_maxpool2_bwd(const float* dy, const uint8_t* code, const float* y_pooled, float* dx,
+                                int N, int H, int W, int C, int act_relu, void* stream) {
+  const int PH = H / 2, PW = W / 2;
+  maxpool2_bwd_kernel<<<grid_for((size_t)N * H * W * C), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      dy, code, y_pooled, dx, N, H, W, C, PH, PW, act_relu);
+  count_launch();
+  B2D_CUDA_CHECK(cudaGetLastError());
+  return B2D_OK;
+}
+
+extern "C" int b2d_colsum(const float* dy, float* db, int M, int N, void* stream) {
+  const int rows = max(8, ceil_div(M, 64));
+  const dim3 grid(ceil_div(N, 32), ceil_div(M, rows));
+  colsum_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(dy, db, M, N, rows);
+  count_launch();
+  B2D_CUDA_CHECK(cudaGetLastError());
+  return B2D_OK;
+}
+
+extern "C" int b2d_relu_bwd(const float* dy, const float* y, float* dx, size_t n, void* stream) {
+  relu_bwd_kernel<<<grid_for(n), 256, 0, static_cast<cudaStream_t>(stream)>>>(dy, y, dx, n);
+  count_launch();
+  B2D_CUDA_CHECK(cudaGetLastError());
+  return B2D_OK;
+}
+
+static ConvShape make_shape(int N, int H, int W, int Ci, int Co, int KH, int KW, int sh, int sw,
+                            int ph, int pw) {
+  ConvShape s{N, H, W, Ci, Co, KH, KW, (H + 2 * ph - KH) / sh + 1, (W + 2 * pw - KW) / sw + 1,
+              sh, sw, ph, pw};
+  return s;
+}
+
+extern "C" int b2d_conv2d_fwd_direct(const float* x, const float* w, const float* bias, float* y,
+                                     int N, int H, int W, int Ci, int Co, int KH, int KW, int sh,
+                                     int sw, int ph, int pw, int relu, void* stream) {
+  const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw);
+  conv2d_fwd_direct_kernel<<<grid_for((size_t)N * s.OH * s.OW * Co), 256, 0,
+                             static_cast<cudaStream_t>(stream)>>>(x, w, bias, y, s, relu);
+  count_launch();
+  B2D_CUDA_CHECK(cudaGetLastError());
+  return B2D_OK;
+}
+
+extern "C" int b2d_conv2d_dgrad_direct(const float* dy, const float* w, float* dx, int N, int H, int W,
+                                       int Ci, int Co, int KH, int KW, int sh, int sw, int ph, int pw,
+                                       void* stream) {
+  const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw);
+  conv2d_dgrad_direct_kernel<<<grid_for((size_t)N * H * W * Ci), 256, 0,
+                               static_cast<cudaStream_t>(stream)>>>(dy, w, dx, s);
+  count_launch();
+  B2D_CUDA_CHECK(cudaGetLastError());
+  return B2D_OK;
+}
+
+extern "C" int b2d_conv2d_wgrad_direct(const float* x, const float* dy, float* dw, int N, int H, int W,
+                                       int Ci, int Co, int KH, int KW, int sh, int sw, int ph, int pw,
+                                       void* stream) {
+  const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw);
+  const dim3 grid(KH * KW * Ci, ceil_div(Co, 32));
+  conv2d_wgrad_direct_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, dy, dw, s);
+  count_launch();
+  B2D_CUDA_CHECK(cudaGetLastError());
+  return B2D_OK;
+}
+
+extern "C" int b2d_sgemm_simt(const float* A, int64_t sam, int64_t sak, const float* B, int64_t sbk,
+                              int64_t sbn, float* D, int64_t ldd, const float* bias, int M, int N,
+                              int K, int relu, int accumulate, void* stream) {
+  const dim3 grid(ceil_div(N, 32), ceil_div(M, 32));
+  sgemm_simt_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(A, sam, sak, B, sbk, sbn, D, ldd,
+                                                                        bias, M, N, K, relu, accumulate);
+  count_launch();
+  B2D_CUDA_CHECK(cudaGetLastError());
+  return B2D_OK;
+}
+
+extern "C" int b2d_sgd_apply(float* w, float* g, size_t n_params, size_t n_total, float lr,
+                             void* stream) {
+  sgd_apply_kernel<<<grid_for(n_total), 256, 0, static_cast<cudaStream_t>(stream)>>>(w, g, n_params,
+                                                                                  n_total, lr);
+  count_launch();
+  B2D_CUDA_CHECK(cudaGetLastError());
+  return B2D_OK;
+}
+
+extern "C" int b2d_cast_f32_bf16(const float* src, void* dst, size_t n, void* stream) {
+  cast_f32_bf16_kernel<<<grid_for(n), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      src, static_cast<uint16_t*>(dst), n);
+  count_launch();
+  B2D_CUDA_CHECK(cudaGetLastError());
+  return B2D_OK;
+}

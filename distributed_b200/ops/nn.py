@@ -1,0 +1,140 @@
+"""ctypes wrappers for the non-GEMM sm_100a kernels (csrc/cuda/nn_kernels.cu).
+
+Every function launches exactly one kernel on the current torch CUDA stream, on tensors the
+caller owns; nothing is allocated here.  Layouts follow Keras: NHWC activations, HWIO conv
+kernels, (in, out) Dense kernels (README.md:292-298).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from .._native import cuda_lib as nl
+
+_declared = False
+
+
+def _lib():
+    global _declared
+    lib = nl.lib()
+    if not _declared:
+        vp, i, f, sz, i64 = C.c_void_p, C.c_int, C.c_float, C.c_size_t, C.c_int64
+        lib.b2d_conv_c1_pool_fwd.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, i, vp]
+        lib.b2d_conv_c1_pool_bwd.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, i, vp]
+        lib.b2d_dense_xent_head.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, f, i, vp]
+        lib.b2d_softmax_xent.argtypes = [vp, vp, vp, vp, i, i, f, vp]
+        lib.b2d_maxpool2_fwd.argtypes = [vp, vp, vp, i, i, i, i, vp]
+        lib.b2d_maxpool2_bwd.argtypes = [vp, vp, vp, vp, i, i, i, i, i, vp]
+        lib.b2d_colsum.argtypes = [vp, vp, i, i, vp]
+        lib.b2d_relu_bwd.argtypes = [vp, vp, vp, sz, vp]
+        conv = [i] * 11
+        lib.b2d_conv2d_fwd_direct.argtypes = [vp, vp, vp, vp, *conv, i, vp]
+        lib.b2d_conv2d_dgrad_direct.argtypes = [vp, vp, vp, *conv, vp]
+        lib.b2d_conv2d_wgrad_direct.argtypes = [vp, vp, vp, *conv, vp]
+        lib.b2d_sgemm_simt.argtypes = [vp, i64, i64, vp, i64, i64, vp, i64, vp, i, i, i, i, i, vp]
+        lib.b2d_sgd_apply.argtypes = [vp, vp, sz, sz, f, vp]
+        lib.b2d_cast_f32_bf16.argtypes = [vp, vp, sz, vp]
+        _declared = True
+    return lib
+
+
+def _s():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t):
+    return None if t is None else t.data_ptr()
+
+
+def conv_c1_pool_fwd(x, w, b, y, code):
+    """Conv2D(C_in=1, KxK valid) + bias + ReLU + MaxPool2x2.  x [N,H,W,1], w [K,K,1,Co]."""
+    N, H, W, _ = x.shape
+    KS, Co = w.shape[0], w.shape[3]
+    nl.check(_lib().b2d_conv_c1_pool_fwd(_p(x), _p(w), _p(b), _p(y), _p(code), N, H, W, Co, KS, _s()),
+             "conv_c1_pool_fwd")
+
+
+def conv_c1_pool_bwd(x, dy, code, dw, db):
+    """Accumulates dW [K,K,1,Co] and db [Co] from the pooled-output gradient dy."""
+    N, H, W, _ = x.shape
+    KS, Co = dw.shape[0], dw.shape[3]
+    nl.check(_lib().b2d_conv_c1_pool_bwd(_p(x), _p(dy), _p(code), _p(dw), _p(db), N, H, W, Co, KS, _s()),
+             "conv_c1_pool_bwd")
+
+
+def dense_xent_head(h, w, b, labels, dh, dw, db, metrics, grad_scale, relu_mask, logits=None):
+    """Dense(C<=32) + softmax cross-entropy + every gradient of both, one kernel."""
+    B, K = h.shape
+    Cc = w.shape[1]
+    nl.check(_lib().b2d_dense_xent_head(_p(h), _p(w), _p(b), _p(labels), _p(logits), _p(dh), _p(dw),
+                                        _p(db), _p(metrics), B, K, Cc, float(grad_scale),
+                                        int(relu_mask), _s()), "dense_xent_head")
+
+
+def softmax_xent(logits, labels, dlogits, metrics, grad_scale):
+    B, Cc = logits.shape
+    nl.check(_lib().b2d_softmax_xent(_p(logits), _p(labels), _p(dlogits), _p(metrics), B, Cc,
+                                     float(grad_scale), _s()), "softmax_xent")
+
+
+def maxpool2_fwd(x, y, code):
+    N, H, W, Cc = x.shape
+    nl.check(_lib().b2d_maxpool2_fwd(_p(x), _p(y), _p(code), N, H, W, Cc, _s()), "maxpool2_fwd")
+
+
+def maxpool2_bwd(dy, code, y_pooled, dx, act_relu):
+    N, H, W, Cc = dx.shape
+    nl.check(_lib().b2d_maxpool2_bwd(_p(dy), _p(code), _p(y_pooled), _p(dx), N, H, W, Cc,
+                                     int(act_relu), _s()), "maxpool2_bwd")
+
+
+def colsum(dy2d, db):
+    M, N = dy2d.shape
+    nl.check(_lib().b2d_colsum(_p(dy2d), _p(db), M, N, _s()), "colsum")
+
+
+def relu_bwd(dy, y, dx):
+    nl.check(_lib().b2d_relu_bwd(_p(dy), _p(y), _p(dx), dy.numel(), _s()), "relu_bwd")
+
+
+def _conv_args(x_shape, w_shape, strides, padding):
+    N, H, W, Ci = x_shape
+    KH, KW, _, Co = w_shape
+    return [N, H, W, Ci, Co, KH, KW, strides[0], strides[1], padding[0], padding[1]]
+
+
+def conv2d_fwd_direct(x, w, b, y, strides=(1, 1), padding=(0, 0), relu=False):
+    nl.check(_lib().b2d_conv2d_fwd_direct(_p(x), _p(w), _p(b), _p(y),
+                                          *_conv_args(x.shape, w.shape, strides, padding),
+                                          int(relu), _s()), "conv2d_fwd_direct")
+
+
+def conv2d_dgrad_direct(dy, w, dx, strides=(1, 1), padding=(0, 0)):
+    nl.check(_lib().b2d_conv2d_dgrad_direct(_p(dy), _p(w), _p(dx),
+                                            *_conv_args(dx.shape, w.shape, strides, padding), _s()),
+             "conv2d_dgrad_direct")
+
+
+def conv2d_wgrad_direct(x, dy, dw, strides=(1, 1), padding=(0, 0)):
+    nl.check(_lib().b2d_conv2d_wgrad_direct(_p(x), _p(dy), _p(dw),
+                                            *_conv_args(x.shape, dw.shape, strides, padding), _s()),
+             "conv2d_wgrad_direct")
+
+
+def sgemm_simt(a, b, d, *, trans_a=False, trans_b=False, bias=None, relu=False, accumulate=False):
+    """D = op(A) @ op(B) on CUDA cores; operands are 2-D row-major fp32 tensors."""
+    sam, sak = (a.stride(1), a.stride(0)) if trans_a else (a.stride(0), a.stride(1))
+    sbk, sbn = (b.stride(1), b.stride(0)) if trans_b else (b.stride(0), b.stride(1))
+    M, N = d.shape
+    K = a.shape[0] if trans_a else a.shape[1]
+    nl.check(_lib().b2d_sgemm_simt(_p(a), sam, sak, _p(b), sbk, sbn, _p(d), d.stride(0), _p(bias),
+                                   M, N, K, int(relu), int(accumulate), _s()), "sgemm_simt")
+
+
+def sgd_apply(w, g, n_params, lr):
+    nl.check(_lib().b2d_sgd_apply(_p(w), _p(g), n_params, w.numel(), float(lr), _s()), "sgd_apply")
+
+
+def cast_f32_bf16(src, dst):
+    nl.check(_lib().b2d_cast_f32_bf16(_p(src), _p(dst), src.numel(), _s()), "cast_f32_bf16")
