@@ -10,6 +10,10 @@ if str(ROOT) not in sys.path:
 
 
 def pytest_configure(config):
+    import torch
+    # References must be true fp32: cuDNN / cuBLAS default to TF32 for convolutions.
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
     config.addinivalue_line("markers", "gpu: test needs a real B200 (run with -m gpu on the GPU box)")
     config.addinivalue_line("markers", "multigpu: test needs >= 2 GPUs")
 
