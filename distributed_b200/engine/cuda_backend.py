@@ -1,0 +1,118 @@
+"""CUDA backend: lowers ops to the sm_100a kernels in libb200dist_cuda.so.
+
+Dense layers go to the tcgen05 GEMM core whenever their shapes meet TMA's 16-byte row
+alignment; the tiny/unaligned remainder (e.g. an unfused Dense(10)) uses the CUDA-core GEMM.
+Every callable launches on the *current* torch stream, so the executor can capture them.
+"""
+from __future__ import annotations
+
+import torch
+
+from ..ops import nn
+from ..ops.gemm import GemmPlan
+
+_HEAD_MAX_C = 32
+_HEAD_SMEM = 200 * 1024
+
+
+class CudaBackend:
+    name = "cuda"
+    supports_conv_c1_pool = True
+
+    def __init__(self, device):
+        self.device = torch.device(device)
+        self.plans = []     # keep GemmPlans (TMA descriptors) alive
+
+    def alloc(self, shape, dtype=torch.float32):
+        return torch.zeros(shape, dtype=dtype, device=self.device)
+
+    def supports_fused_head(self, k_in, units):
+        return units <= _HEAD_MAX_C and (2 * k_in * units + _HEAD_MAX_C + 2) * 4 <= _HEAD_SMEM
+
+    @staticmethod
+    def _tc_ok(*dims):
+        return all(d % 4 == 0 for d in dims)
+
+    def describe_conv(self, layer):
+        return "direct conv (CUDA cores)"
+
+    def describe_dense(self, b, k, n):
+        return "tcgen05 tf32 GEMM" if self._tc_ok(k, n) else "CUDA-core GEMM"
+
+    def _plan(self, *a, **kw):
+        p = GemmPlan(*a, **kw)
+        self.plans.append(p)
+        return p.run
+
+    # ---- fused first layer -----------------------------------------------------------
+    def conv_c1_pool_fwd(self, x, w, b, y, code):
+        return lambda: nn.conv_c1_pool_fwd(x, w, b, y, code)
+
+    def conv_c1_pool_bwd(self, x, dy, code, dw, db):
+        return lambda: nn.conv_c1_pool_bwd(x, dy, code, dw, db)
+
+    # ---- general conv (direct fallback; implicit-GEMM path plugs in here) --------------
+    def conv2d_fwd(self, x, w, b, y, strides, pad, relu):
+        return lambda: nn.conv2d_fwd_direct(x, w, b, y, strides, pad, relu)
+
+    def conv2d_wgrad(self, x, dy, dw, db, strides, pad):
+        dy2 = dy.view(-1, dy.shape[-1])
+
+        def run():
+            nn.conv2d_wgrad_direct(x, dy, dw, strides, pad)
+            if db is not None:
+                nn.colsum(dy2, db)
+        return run
+
+    def conv2d_dgrad(self, dy, w, dx, strides, pad, mask=None):
+        def run():
+            nn.conv2d_dgrad_direct(dy, w, dx, strides, pad)
+            if mask is not None:
+                nn.relu_bwd(dx, mask, dx)
+        return run
+
+    def maxpool2_fwd(self, x, y, code):
+        return lambda: nn.maxpool2_fwd(x, y, code)
+
+    def maxpool2_bwd(self, dy, code, y, dx, act_relu):
+        return lambda: nn.maxpool2_bwd(dy, code, y, dx, act_relu)
+
+    # ---- dense ------------------------------------------------------------------------
+    def dense_fwd(self, x, w, b, y, relu):
+        k, n = w.shape
+        if self._tc_ok(k, n):
+            return self._plan(x, w, y, b_mn_major=True, bias=b, relu=relu)
+        return lambda: nn.sgemm_simt(x, w, y, bias=b, relu=relu)
+
+    def dense_wgrad(self, x, dy, dw, db):
+        k, n = dw.shape
+        if self._tc_ok(k, n):
+            gemm = self._plan(x, dy, dw, a_mn_major=True, b_mn_major=True, accumulate=True)
+        else:
+            def gemm():
+                nn.sgemm_simt(x, dy, dw, trans_a=True, accumulate=True)
+
+        def run():
+            gemm()
+            if db is not None:
+                nn.colsum(dy, db)
+        return run
+
+    def dense_dgrad(self, dy, w, dx, mask=None):
+        k, n = w.shape
+        if self._tc_ok(k, n):
+            return self._plan(dy, w, dx, mask=mask)        # dx = dy . W^T, W rows are K-major
+        def run():
+            nn.sgemm_simt(dy, w, dx, trans_b=True)
+            if mask is not None:
+                nn.relu_bwd(dx, mask, dx)
+        return run
+
+    def dense_xent_head(self, h, w, b, labels, dh, dw, db, metrics, scale, relu_mask, logits):
+        return lambda: nn.dense_xent_head(h, w, b, labels, dh, dw, db, metrics, scale, relu_mask, logits)
+
+    def softmax_xent(self, logits, labels, dlogits, metrics, scale):
+        return lambda: nn.softmax_xent(logits, labels, dlogits, metrics, scale)
+
+    def sgd_apply(self, params, grads, n_params, lr):
+        return lambda: nn.sgd_apply(params, grads, n_params, lr)

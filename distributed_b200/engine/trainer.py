@@ -1,0 +1,258 @@
+"""Trainer: owns the arenas, the lowered step and the step loop of one compiled model.
+
+CUDA: the step (forward, loss, backward, fused all-reduce + SGD) is captured into CUDA graphs
+by the native executor (csrc/runtime/executor.cpp) and replayed from a C++ loop that also
+prefetches the next batch on a copy stream and streams the metric sums back to pinned host
+memory — no Python, no host sync inside the loop.
+CPU: the same lowered program runs op by op through the C++ CPU backend.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import time
+
+import numpy as np
+import torch
+
+from .arena import ArenaLayout, TAIL
+from .lowering import lower
+
+
+def _declare_exec(lib):
+    if getattr(lib, "_exec_declared", False):
+        return
+    vp, i, i64, sz = C.c_void_p, C.c_int, C.c_int64, C.c_size_t
+    lib.b2d_exec_create.argtypes = [C.POINTER(vp)]
+    lib.b2d_exec_destroy.argtypes = [vp]
+    lib.b2d_exec_destroy.restype = None
+    lib.b2d_exec_stream.argtypes = [vp]
+    lib.b2d_exec_stream.restype = vp
+    lib.b2d_exec_set_io.argtypes = [vp, i, vp, sz, vp, sz]
+    lib.b2d_exec_set_metrics.argtypes = [vp, vp, sz, vp, i]
+    lib.b2d_exec_begin_capture.argtypes = [vp]
+    lib.b2d_exec_end_capture.argtypes = [vp, i]
+    lib.b2d_exec_graph_nodes.argtypes = [vp, i]
+    lib.b2d_exec_graph_nodes.restype = C.c_uint64
+    lib.b2d_exec_run.argtypes = [vp, vp, sz, vp, sz, i64, i64, i64, i, C.POINTER(C.c_float)]
+    lib.b2d_exec_sync.argtypes = [vp]
+    lib.b2d_exec_steps_done.argtypes = [vp]
+    lib.b2d_exec_steps_done.restype = C.c_uint64
+    lib._exec_declared = True
+
+
+class Trainer:
+    def __init__(self, model, strategy, batch_per_replica: int, input_shape, use_graph: bool = True):
+        self.model = model
+        self.strategy = strategy
+        self.batch = int(batch_per_replica)
+        self.input_shape = tuple(input_shape)          # (H, W, C)
+        self.layers = model.layers
+        self.layout = ArenaLayout(self.layers)
+        self.lr = float(model.optimizer.learning_rate)
+        self.backend_name = strategy.backend_name
+        if self.backend_name == "cuda":
+            from .cuda_backend import CudaBackend
+            torch.cuda.set_device(strategy.device)
+            self.be = CudaBackend(strategy.device)
+        else:
+            from .cpu_backend import CpuBackend
+            self.be = CpuBackend()
+        self.comm = strategy.make_comm(self.layout.n_total, self.be)
+        self.params = self.comm.alloc(self.layout.n_total, self.be)
+        self.grads = self.comm.alloc(self.layout.n_total, self.be)
+        init = torch.from_numpy(self.layout.initial_values(self.layers, strategy.seed))
+        self.params.copy_(init)
+        self.grads.zero_()
+        if self.comm.world > 1 and not self.comm.all_equal(self.params):
+            raise RuntimeError("replicas were not initialised identically (mirrored variables differ)")
+        self.use_graph = bool(use_graph and self.backend_name == "cuda" and self.comm.capturable)
+        self._exec = None
+        self._build()
+
+    # ------------------------------------------------------------------------------
+    def _io_buffers(self):
+        x = self.be.alloc((self.batch, *self.input_shape))
+        y = self.be.alloc((self.batch,), torch.int32)
+        return x, y
+
+    def _build(self):
+        lay, be = self.layout, self.be
+        self.x_in, self.y_in, self.progs, self.updates = [], [], [], []
+        n_slots = 2 if self.use_graph else 1
+        for _ in range(n_slots):
+            x, y = self._io_buffers()
+            self.x_in.append(x)
+            self.y_in.append(y)
+        self.x_bytes = self.x_in[0].numel() * 4
+        self.y_bytes = self.y_in[0].numel() * 4
+        if self.backend_name != "cuda":
+            self.progs.append(lower(self.layers, self.batch, be, lay, self.params, self.grads,
+                                    self.x_in[0], self.y_in[0]))
+            self.updates.append(self.comm.make_update(be, self.params, self.grads, lay.n_params, self.lr))
+            return
+        from .._native import cuda_lib as nl
+        lib = nl.lib()
+        _declare_exec(lib)
+        self._lib = lib
+        h = C.c_void_p()
+        nl.check(lib.b2d_exec_create(C.byref(h)), "b2d_exec_create")
+        self._exec = h
+        self.stream = torch.cuda.ExternalStream(lib.b2d_exec_stream(h), device=self.be.device)
+        # metrics ring: pinned host memory the executor fills after every step
+        self.ring_len = 4096
+        self.metrics_host = torch.zeros((self.ring_len, TAIL), dtype=torch.float32).pin_memory()
+        tail = self.params[lay.n_params:lay.n_total]
+        nl.check(lib.b2d_exec_set_metrics(h, tail.data_ptr(), TAIL * 4, self.metrics_host.data_ptr(),
+                                          self.ring_len), "b2d_exec_set_metrics")
+        torch.cuda.synchronize(self.be.device)
+        with torch.cuda.stream(self.stream):
+            for slot in range(n_slots):
+                prog = lower(self.layers, self.batch, be, lay, self.params, self.grads,
+                             self.x_in[slot], self.y_in[slot])
+                upd = self.comm.make_update(be, self.params, self.grads, lay.n_params, self.lr)
+                self.progs.append(prog)
+                self.updates.append(upd)
+                nl.check(lib.b2d_exec_set_io(h, slot, self.x_in[slot].data_ptr(), self.x_bytes,
+                                             self.y_in[slot].data_ptr(), self.y_bytes), "b2d_exec_set_io")
+            if self.use_graph:
+                # warm every kernel once outside capture (module load, smem attributes), on zero
+                # inputs with the update skipped so the weights are untouched
+                self.progs[0].run()
+                self.grads.zero_()
+                self.stream.synchronize()
+                for slot in range(n_slots):
+                    nl.check(lib.b2d_exec_begin_capture(h), "b2d_exec_begin_capture")
+                    self.progs[slot].run()
+                    self.updates[slot]()
+                    nl.check(lib.b2d_exec_end_capture(h, slot), "b2d_exec_end_capture")
+                self.kernels_per_step = int(lib.b2d_exec_graph_nodes(h, 0))
+            else:
+                self.kernels_per_step = None
+        self.stream.synchronize()
+
+    # ------------------------------------------------------------------------------
+    def describe(self) -> list[str]:
+        return list(self.progs[0].description)
+
+    def run_steps(self, x_src, y_src, first_step: int, steps_in_src: int, n_steps: int,
+                  global_batch: int, timed: bool = False):
+        """Run ``n_steps`` steps.  ``x_src`` [S,H,W,C] fp32 and ``y_src`` [S] int32 are pinned
+        host or device tensors; step t of this replica reads rows
+        ``[(t % steps_in_src) * global_batch + rank * B, ... + B)``.  Returns elapsed ms if timed."""
+        B, r = self.batch, self.comm.rank
+        row = int(np.prod(self.input_shape))
+        if self._exec is not None and self.use_graph:
+            el = C.c_float(0.0)
+            xs = x_src.data_ptr() + r * B * row * 4
+            ys = y_src.data_ptr() + r * B * 4
+            from .._native import cuda_lib as nl
+            nl.check(self._lib.b2d_exec_run(self._exec, xs, global_batch * row * 4, ys, global_batch * 4,
+                                            first_step, steps_in_src, n_steps, 1,
+                                            C.byref(el) if timed else None), "b2d_exec_run")
+            return el.value if timed else None
+        # eager loops (CPU backend; CUDA with a non-capturable communicator)
+        t0 = time.perf_counter()
+        cuda = self.backend_name == "cuda"
+        ctx = torch.cuda.stream(self.stream) if cuda else _null()
+        if cuda and timed:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with ctx:
+            if cuda and timed:
+                e0.record()
+            for t in range(n_steps):
+                s = (first_step + t) % steps_in_src
+                lo = s * global_batch + r * B
+                self.x_in[0].copy_(x_src[lo:lo + B], non_blocking=True)
+                self.y_in[0].copy_(y_src[lo:lo + B], non_blocking=True)
+                self.progs[0].run()
+                self.updates[0]()
+            if cuda and timed:
+                e1.record()
+                e1.synchronize()
+                return e0.elapsed_time(e1)
+            if cuda:
+                self.stream.synchronize()
+        return (time.perf_counter() - t0) * 1e3 if timed else None
+
+    def sync(self):
+        if self._exec is not None:
+            from .._native import cuda_lib as nl
+            nl.check(self._lib.b2d_exec_sync(self._exec), "b2d_exec_sync")
+
+    def steps_done(self) -> int:
+        return int(self._lib.b2d_exec_steps_done(self._exec)) if self._exec is not None else 0
+
+    def metric_sums(self) -> tuple[float, float, float]:
+        """Running (loss_sum, correct, samples) since the last reset, summed over replicas."""
+        self.sync()
+        t = self.params[self.layout.n_params:self.layout.n_total].detach().cpu()
+        return float(t[0]), float(t[1]), float(t[2])
+
+    def step_metrics(self, n_last: int) -> np.ndarray:
+        """The last ``n_last`` per-step snapshots of the running sums (CUDA graph mode)."""
+        if self._exec is None or not self.use_graph:
+            return np.zeros((0, TAIL), np.float32)
+        self.sync()
+        done = self.steps_done()
+        n = min(n_last, done, self.ring_len)
+        idx = [(done - n + k) % self.ring_len for k in range(n)]
+        return self.metrics_host.numpy()[idx].copy()
+
+    def reset_metrics(self):
+        self.sync()
+        self.params[self.layout.n_params:self.layout.n_total].zero_()
+        if self.backend_name == "cuda":
+            torch.cuda.synchronize(self.be.device)
+        self.comm.barrier()
+
+    def get_weights(self) -> list[np.ndarray]:
+        self.sync()
+        flat = self.params.detach().cpu()
+        return [self.layout.view(flat, s).numpy().copy() for s in self.layout.slots]
+
+    def set_weights(self, arrays):
+        self.sync()
+        assert len(arrays) == len(self.layout.slots), "wrong number of weight arrays"
+        flat = self.params.detach().cpu().clone()
+        for s, a in zip(self.layout.slots, arrays):
+            a = np.asarray(a, np.float32)
+            if tuple(a.shape) != s.shape:
+                raise ValueError(f"{s.name}: expected shape {s.shape}, got {a.shape}")
+            flat[s.offset:s.offset + s.size] = torch.from_numpy(a.reshape(-1))
+        self.params.copy_(flat)
+        if self.backend_name == "cuda":
+            torch.cuda.synchronize(self.be.device)
+
+    def forward_logits(self, x: torch.Tensor) -> torch.Tensor:
+        """Inference on one batch of exactly ``batch`` rows (used by predict / evaluate)."""
+        if not hasattr(self, "_infer"):
+            xi, yi = self._io_buffers()
+            ctx = torch.cuda.stream(self.stream) if self.backend_name == "cuda" else _null()
+            with ctx:
+                self._infer = (xi, lower(self.layers, self.batch, self.be, self.layout, self.params,
+                                         self.grads, xi, yi, training=False))
+        xi, prog = self._infer
+        ctx = torch.cuda.stream(self.stream) if self.backend_name == "cuda" else _null()
+        with ctx:
+            xi.copy_(x)
+            for f in prog.forward:
+                f()
+            out = prog.logits.detach().clone()
+        if self.backend_name == "cuda":
+            self.stream.synchronize()
+        return out.cpu()
+
+    def close(self):
+        if self._exec is not None:
+            self.sync()
+            self._lib.b2d_exec_destroy(self._exec)
+            self._exec = None
+        self.comm.close()
+
+
+class _null:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False

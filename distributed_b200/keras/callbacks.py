@@ -1,0 +1,33 @@
+"""Callbacks.  The reference passes none and TensorFlow warns about the missing
+``ModelCheckpoint`` (README.md:400); it is provided here so a run can actually be resumed."""
+from __future__ import annotations
+
+
+class Callback:
+    model = None
+
+    def set_model(self, model):
+        self.model = model
+
+    def on_train_begin(self, logs=None): pass
+    def on_train_end(self, logs=None): pass
+    def on_epoch_begin(self, epoch, logs=None): pass
+    def on_epoch_end(self, epoch, logs=None): pass
+
+
+class ModelCheckpoint(Callback):
+    """Saves the weights (Keras layer order) after every epoch; only the chief writes."""
+
+    def __init__(self, filepath, save_weights_only=True, save_freq="epoch", chief_only=True):
+        self.filepath = str(filepath)
+        self.chief_only = chief_only
+
+    def on_epoch_end(self, epoch, logs=None):
+        if self.chief_only and self.model._strategy.rank != 0:
+            return
+        path = self.filepath.format(epoch=epoch + 1, **(logs or {}))
+        self.model.save_weights(path)
+
+
+class History(Callback):
+    pass

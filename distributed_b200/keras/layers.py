@@ -1,0 +1,228 @@
+"""Keras-style layer objects (README.md:292-298; R equivalents README.md:58-68).
+
+Layers here are *descriptions*: hyper-parameters, shape inference and parameter specs in
+Keras' own order and layouts (Conv2D kernel HWIO then bias; Dense kernel (in, out) then bias;
+activations NHWC; Flatten in H, W, C order).  The numerical work happens in the engine, which
+lowers a stack of layers to fused sm_100a kernels (or to the C++ CPU backend).
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+
+import numpy as np
+
+_ACTIVATIONS = (None, "linear", "relu")
+
+
+def _pair(v) -> tuple[int, int]:
+    if isinstance(v, (tuple, list)):
+        assert len(v) == 2
+        return int(v[0]), int(v[1])
+    return int(v), int(v)
+
+
+def _norm_activation(a):
+    if callable(a):
+        a = getattr(a, "__name__", None)
+    if a not in _ACTIVATIONS:
+        raise ValueError(f"activation {a!r} is not supported (use None or 'relu')")
+    return None if a == "linear" else a
+
+
+@dataclass
+class ParamSpec:
+    name: str                      # Keras weight name, e.g. "conv2d/kernel:0"
+    shape: tuple[int, ...]
+    init: str                      # "glorot_uniform" | "zeros" | "ones"
+    fan_in: int = 0
+    fan_out: int = 0
+    trainable: bool = True
+
+    @property
+    def size(self) -> int:
+        return int(np.prod(self.shape))
+
+
+class Layer:
+    """Base class; subclasses define ``compute_output_shape`` and ``param_specs``."""
+
+    _counters: dict[str, int] = {}
+
+    def __init__(self, name: str | None = None, input_shape=None, **kwargs):
+        if kwargs:
+            raise TypeError(f"unsupported arguments for {type(self).__name__}: {sorted(kwargs)}")
+        self._given_name = name
+        self.name = name  # finalised by the model (conv2d, conv2d_1, ... per model)
+        self.input_shape_arg = tuple(input_shape) if input_shape is not None else None
+        self.input_shape: tuple[int, ...] | None = None    # without batch dimension
+        self.output_shape: tuple[int, ...] | None = None
+        self.built = False
+
+    base_name = "layer"
+    activation = None
+
+    def build(self, input_shape: tuple[int, ...]) -> tuple[int, ...]:
+        self.input_shape = tuple(int(d) for d in input_shape)
+        self.output_shape = self.compute_output_shape(self.input_shape)
+        self.built = True
+        return self.output_shape
+
+    def compute_output_shape(self, input_shape):
+        return input_shape
+
+    def param_specs(self) -> list[ParamSpec]:
+        return []
+
+    def count_params(self) -> int:
+        return sum(p.size for p in self.param_specs())
+
+    def get_config(self) -> dict:
+        return {"name": self.name}
+
+    def __repr__(self):
+        return f"<{type(self).__name__} {self.name} {self.input_shape}->{self.output_shape}>"
+
+
+class InputLayer(Layer):
+    base_name = "input"
+
+    def __init__(self, input_shape=None, shape=None, **kw):
+        super().__init__(input_shape=input_shape if input_shape is not None else shape, **kw)
+
+
+class Conv2D(Layer):
+    """2-D convolution, NHWC, kernel HWIO (README.md:293: ``Conv2D(32, 3, activation='relu')``)."""
+    base_name = "conv2d"
+
+    def __init__(self, filters, kernel_size, strides=(1, 1), padding="valid", activation=None,
+                 use_bias=True, kernel_initializer="glorot_uniform", bias_initializer="zeros", **kw):
+        super().__init__(**kw)
+        self.filters = int(filters)
+        self.kernel_size = _pair(kernel_size)
+        self.strides = _pair(strides)
+        padding = padding.lower()
+        if padding not in ("valid", "same"):
+            raise ValueError("padding must be 'valid' or 'same'")
+        self.padding = padding
+        self.activation = _norm_activation(activation)
+        self.use_bias = bool(use_bias)
+        self.kernel_initializer = kernel_initializer
+        self.bias_initializer = bias_initializer
+
+    def pad_amounts(self, input_shape=None) -> tuple[int, int]:
+        """Symmetric zero padding (top/left); 'same' with odd kernels and these strides."""
+        if self.padding == "valid":
+            return 0, 0
+        H, W, _ = input_shape or self.input_shape
+        out = []
+        for size, k, s in ((H, self.kernel_size[0], self.strides[0]), (W, self.kernel_size[1], self.strides[1])):
+            o = math.ceil(size / s)
+            total = max((o - 1) * s + k - size, 0)
+            out.append(total // 2)       # TF puts the extra pixel at the end; begin = total // 2
+        return out[0], out[1]
+
+    def compute_output_shape(self, input_shape):
+        if len(input_shape) != 3:
+            raise ValueError(f"Conv2D expects (H, W, C) inputs, got {input_shape}")
+        H, W, _ = input_shape
+        (kh, kw), (sh, sw) = self.kernel_size, self.strides
+        if self.padding == "valid":
+            oh, ow = (H - kh) // sh + 1, (W - kw) // sw + 1
+        else:
+            oh, ow = math.ceil(H / sh), math.ceil(W / sw)
+        if oh <= 0 or ow <= 0:
+            raise ValueError(f"Conv2D {self.name}: kernel {self.kernel_size} larger than input {input_shape}")
+        return (oh, ow, self.filters)
+
+    def param_specs(self):
+        ci = self.input_shape[2]
+        kh, kw = self.kernel_size
+        specs = [ParamSpec(f"{self.name}/kernel:0", (kh, kw, ci, self.filters), self.kernel_initializer,
+                           fan_in=kh * kw * ci, fan_out=kh * kw * self.filters)]
+        if self.use_bias:
+            specs.append(ParamSpec(f"{self.name}/bias:0", (self.filters,), self.bias_initializer))
+        return specs
+
+
+class MaxPooling2D(Layer):
+    """Max pooling; the default (2, 2) window / stride 2 / 'valid' is what README.md:294 uses."""
+    base_name = "max_pooling2d"
+
+    def __init__(self, pool_size=(2, 2), strides=None, padding="valid", **kw):
+        super().__init__(**kw)
+        self.pool_size = _pair(pool_size)
+        self.strides = _pair(strides) if strides is not None else self.pool_size
+        if padding.lower() != "valid":
+            raise ValueError("MaxPooling2D supports padding='valid' only")
+        if self.pool_size != (2, 2) or self.strides != (2, 2):
+            raise ValueError("MaxPooling2D supports pool_size=2, strides=2 (the Keras default) only")
+
+    def compute_output_shape(self, input_shape):
+        H, W, C = input_shape
+        return (H // 2, W // 2, C)
+
+
+class Flatten(Layer):
+    """Row-major flatten of (H, W, C) — a view; no data moves (README.md:295)."""
+    base_name = "flatten"
+
+    def compute_output_shape(self, input_shape):
+        return (int(np.prod(input_shape)),)
+
+
+class Dense(Layer):
+    """Fully connected layer, kernel (in, out) (README.md:296-297)."""
+    base_name = "dense"
+
+    def __init__(self, units, activation=None, use_bias=True, kernel_initializer="glorot_uniform",
+                 bias_initializer="zeros", **kw):
+        super().__init__(**kw)
+        self.units = int(units)
+        self.activation = _norm_activation(activation)
+        self.use_bias = bool(use_bias)
+        self.kernel_initializer = kernel_initializer
+        self.bias_initializer = bias_initializer
+
+    def compute_output_shape(self, input_shape):
+        if len(input_shape) != 1:
+            raise ValueError(f"Dense expects flat inputs, got {input_shape}; add a Flatten layer")
+        return (self.units,)
+
+    def param_specs(self):
+        k = self.input_shape[0]
+        specs = [ParamSpec(f"{self.name}/kernel:0", (k, self.units), self.kernel_initializer,
+                           fan_in=k, fan_out=self.units)]
+        if self.use_bias:
+            specs.append(ParamSpec(f"{self.name}/bias:0", (self.units,), self.bias_initializer))
+        return specs
+
+
+class Activation(Layer):
+    base_name = "activation"
+
+    def __init__(self, activation, **kw):
+        super().__init__(**kw)
+        self.activation = _norm_activation(activation)
+
+
+class ReLU(Activation):
+    base_name = "re_lu"
+
+    def __init__(self, **kw):
+        super().__init__("relu", **kw)
+
+
+def initialize(spec: ParamSpec, rng: np.random.Generator) -> np.ndarray:
+    """Keras initialisers: glorot_uniform = U(-l, l), l = sqrt(6 / (fan_in + fan_out))."""
+    if spec.init in ("zeros", "Zeros"):
+        return np.zeros(spec.shape, np.float32)
+    if spec.init in ("ones", "Ones"):
+        return np.ones(spec.shape, np.float32)
+    if spec.init in ("glorot_uniform", "GlorotUniform"):
+        limit = math.sqrt(6.0 / max(1, spec.fan_in + spec.fan_out))
+        return rng.uniform(-limit, limit, size=spec.shape).astype(np.float32)
+    if spec.init in ("he_normal", "HeNormal"):
+        std = math.sqrt(2.0 / max(1, spec.fan_in))
+        return (rng.standard_normal(size=spec.shape) * std).astype(np.float32)
+    raise ValueError(f"unknown initializer {spec.init!r}")

@@ -1,0 +1,79 @@
+"""Multi-worker training on the CPU backend, world_size 2 (BASELINE.json config 1):
+the README's distributed flow with a localhost TF_CONFIG (README.md:318-393)."""
+import json
+
+import numpy as np
+import pytest
+
+from distributed_b200.launch import barrier_apply
+
+
+def _train(ctx, num_workers, epochs=3, steps=5, per_worker=64, export_dir=None, seed_data=0):
+    """What each README worker runs: TF_CONFIG -> strategy -> scope -> fit."""
+    import os
+    os.environ["B200DIST_BACKEND"] = "cpu"
+    os.environ["TF_CONFIG"] = json.dumps(ctx.tf_config(base_port=int(ctx.address[0].split(":")[1]) % 20000 + 20000))
+    import numpy as np
+    import distributed_b200 as tf
+    strategy = tf.distribute.experimental.MultiWorkerMirroredStrategy()
+    batch_size = per_worker * num_workers
+    rng = np.random.default_rng(seed_data)
+    x = rng.random((batch_size * steps * epochs, 28, 28, 1))
+    y = rng.integers(0, 10, len(x))
+    with strategy.scope():
+        model = tf.models.mnist_cnn(learning_rate=0.01)
+    h = model.fit(x, y, batch_size=batch_size, epochs=epochs, steps_per_epoch=steps, verbose=0)
+    w = model.get_weights()
+    digest = float(sum(np.abs(a).astype(np.float64).sum() for a in w))
+    if export_dir is not None:
+        model.save(os.path.join(export_dir, f"trained-{ctx.partition}.hdf5"))
+    return json.dumps({"loss": h.history["loss"], "acc": h.history["accuracy"], "digest": digest,
+                       "max_acc": repr(max(h.history["accuracy"])), "n": strategy.num_replicas_in_sync})
+
+
+def test_two_workers_report_identical_metrics_and_weights(tmp_path):
+    out = barrier_apply(lambda ctx: _train(ctx, 2, export_dir=str(tmp_path)), 2, timeout=300)
+    r = [json.loads(s) for s in out]
+    assert r[0]["n"] == 2
+    assert r[0]["loss"] == r[1]["loss"] and r[0]["acc"] == r[1]["acc"]       # N ranks, one value (README.md:229-231)
+    assert r[0]["max_acc"] == r[1]["max_acc"]
+    assert r[0]["digest"] == r[1]["digest"]                                   # mirrored weights, bit for bit
+    assert abs(r[0]["loss"][0] - np.log(10)) < 0.15                           # starts near ln 10 (README.md:413)
+    for a in r[0]["acc"]:                                                     # accuracy = integer / (5 * 128)
+        assert abs(a * 640 - round(a * 640)) < 1e-3
+    # every worker saved its own file; they hold the same model (README.md:237-240)
+    import distributed_b200 as tf
+    w0 = tf.keras.models.load_model(tmp_path / "trained-0.hdf5").get_weights()
+    w1 = tf.keras.models.load_model(tmp_path / "trained-1.hdf5").get_weights()
+    assert all(np.array_equal(a, b) for a, b in zip(w0, w1))
+
+
+def test_two_workers_equal_one_worker_with_the_global_batch():
+    """N ranks x batch 64 == 1 rank x batch 64N on the same global data order (sync-DP maths)."""
+    two = [json.loads(s) for s in barrier_apply(lambda ctx: _train(ctx, 2, epochs=1, steps=3), 2, timeout=300)]
+    one = [json.loads(s) for s in barrier_apply(lambda ctx: _train(ctx, 1, epochs=1, steps=3, per_worker=128), 1,
+                                                timeout=300)]
+    assert abs(two[0]["loss"][0] - one[0]["loss"][0]) < 1e-4
+    assert abs(two[0]["digest"] - one[0]["digest"]) < 1e-2 * 1e-3 * one[0]["digest"] + 1e-3
+
+
+def _shm_allreduce(ctx):
+    import numpy as np
+    import torch
+    from distributed_b200.parallel.comm import ShmComm
+    c = ShmComm("t" + ctx.address[0].split(":")[1], ctx.partition, len(ctx.address), 1 << 16)
+    out = []
+    for n in (1, 7, 1000, 4099):
+        t = torch.arange(n, dtype=torch.float32) * (ctx.partition + 1)
+        c.allreduce(t)
+        out.append(bool(torch.equal(t, torch.arange(n, dtype=torch.float32) * 6)))
+    same = c.all_equal(torch.ones(10))
+    diff = c.all_equal(torch.full((10,), float(ctx.partition)))
+    c.close()
+    return json.dumps([out, same, diff])
+
+
+def test_shm_allreduce_three_ranks_odd_sizes():
+    res = [json.loads(s) for s in barrier_apply(_shm_allreduce, 3, timeout=120)]
+    for out, same, diff in res:
+        assert all(out) and same is True and diff is False

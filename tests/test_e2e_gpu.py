@@ -1,0 +1,57 @@
+"""End-to-end on one B200: the README model trained by the CUDA engine (graph replay) must
+track the C++ CPU backend step for step (tf32 tolerance on the dense layers)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _fit(backend, x, y, epochs=2, steps=5, lr=0.05, model="mnist"):
+    import distributed_b200 as tf
+    from distributed_b200.parallel.strategy import OneDeviceStrategy
+    strat = OneDeviceStrategy(backend=backend)
+    with strat.scope():
+        m = tf.models.mnist_cnn(learning_rate=lr) if model == "mnist" else tf.models.scaled_cnn(learning_rate=lr)
+    h = m.fit(x, y, batch_size=64, epochs=epochs, steps_per_epoch=steps, verbose=0)
+    return m, h
+
+
+def test_cuda_fit_matches_cpu_backend():
+    rng = np.random.default_rng(0)
+    x = rng.random((640, 28, 28, 1)).astype(np.float32)
+    y = rng.integers(0, 10, 640)
+    mc, hc = _fit("cpu", x, y)
+    mg, hg = _fit("cuda", x, y)
+    assert mg._trainer.use_graph and mg._trainer.kernels_per_step <= 8
+    for a, b in zip(hc.history["loss"], hg.history["loss"]):
+        assert abs(a - b) < 2e-3, (hc.history, hg.history)
+    # near-tied random-init logits flip under tf32 rounding: allow a few of the 320 samples
+    assert hc.history["accuracy"] == pytest.approx(hg.history["accuracy"], abs=8 / 320)
+    for wc, wg, name in zip(mc.get_weights(), mg.get_weights(), mc.weight_names()):
+        assert np.allclose(wc, wg, atol=5e-4), (name, np.abs(wc - wg).max())
+
+
+def test_cuda_generic_path_scaled_cnn_matches_cpu():
+    rng = np.random.default_rng(1)
+    x = rng.random((128, 28, 28, 1)).astype(np.float32)
+    y = rng.integers(0, 10, 128)
+    mc, hc = _fit("cpu", x, y, epochs=1, steps=2, lr=0.01, model="scaled")
+    mg, hg = _fit("cuda", x, y, epochs=1, steps=2, lr=0.01, model="scaled")
+    assert abs(hc.history["loss"][0] - hg.history["loss"][0]) < 5e-3
+    for wc, wg, name in zip(mc.get_weights(), mg.get_weights(), mc.weight_names()):
+        assert np.allclose(wc, wg, atol=1e-3), (name, np.abs(wc - wg).max())
+
+
+def test_predict_and_save_load_roundtrip(tmp_path):
+    import distributed_b200 as tf
+    rng = np.random.default_rng(2)
+    x = rng.random((128, 28, 28, 1)).astype(np.float32)
+    y = rng.integers(0, 10, 128)
+    m, _ = _fit("cuda", x, y, epochs=1, steps=2)
+    p = m.predict(x[:100], batch_size=64)
+    assert p.shape == (100, 10)
+    m.save(tmp_path / "trained-0.hdf5")
+    m2 = tf.keras.models.load_model(tmp_path / "trained-0.hdf5")
+    m2.compile(loss=tf.keras.losses.SparseCategoricalCrossentropy(from_logits=True),
+               optimizer=tf.keras.optimizers.SGD(0.001), metrics=["accuracy"])
+    assert np.allclose(m2.predict(x[:100], batch_size=64), p, atol=2e-3)

@@ -1,0 +1,110 @@
+"""Keras-style front end: shape inference, parameter layout, fit/History contract."""
+import numpy as np
+import pytest
+
+import distributed_b200 as tf
+from distributed_b200.engine.arena import ArenaLayout
+
+
+def _readme_model():
+    model = tf.keras.Sequential([
+        tf.keras.layers.Conv2D(32, 3, activation='relu', input_shape=(28, 28, 1)),
+        tf.keras.layers.MaxPooling2D(),
+        tf.keras.layers.Flatten(),
+        tf.keras.layers.Dense(64, activation='relu'),
+        tf.keras.layers.Dense(10)
+    ])
+    model.compile(loss=tf.keras.losses.SparseCategoricalCrossentropy(from_logits=True),
+                  optimizer=tf.keras.optimizers.SGD(learning_rate=0.001), metrics=['accuracy'])
+    return model
+
+
+def test_shapes_params_and_keras_weight_order():
+    m = _readme_model()
+    shapes = [l.output_shape for l in m.layers]
+    assert shapes == [(26, 26, 32), (13, 13, 32), (5408,), (64,), (10,)]
+    assert m.count_params() == 347146
+    names = m.weight_names()
+    assert names == ["conv2d/kernel:0", "conv2d/bias:0", "dense/kernel:0", "dense/bias:0",
+                     "dense_1/kernel:0", "dense_1/bias:0"]                          # 6 tensors (README.md:403)
+    w = m.get_weights()
+    assert [a.shape for a in w] == [(3, 3, 1, 32), (32,), (5408, 64), (64,), (64, 10), (10,)]
+    lim = np.sqrt(6 / (9 + 9 * 32))
+    assert np.abs(w[0]).max() <= lim and np.abs(w[0]).max() > 0.5 * lim and not w[1].any()
+    lay = ArenaLayout(m.layers)
+    assert lay.count == 347146 and lay.n_total == lay.n_params + 4
+
+
+def test_same_padding_and_strides_shape_inference():
+    m = tf.keras.Sequential([tf.keras.layers.Conv2D(8, 7, strides=2, padding="same", input_shape=(224, 224, 3)),
+                             tf.keras.layers.Conv2D(16, 3, padding="same")])
+    assert m.layers[0].output_shape == (112, 112, 8) and m.layers[1].output_shape == (112, 112, 16)
+    assert m.layers[0].pad_amounts() == (2, 2) and m.layers[1].pad_amounts() == (1, 1)
+
+
+def test_fit_contract_local_cpu():
+    m = _readme_model()
+    rng = np.random.default_rng(0)
+    x = rng.random((1000, 28, 28, 1))                      # float64, like x_train / 255.0
+    y = rng.integers(0, 10, 1000)
+    hist = m.fit(x, y, batch_size=64, epochs=3, steps_per_epoch=5, verbose=0)
+    assert list(hist.history) == ["loss", "accuracy"] and len(hist.history["loss"]) == 3
+    assert abs(hist.history["loss"][0] - np.log(10)) < 0.15          # starts near ln 10 (README.md:309)
+    for a in hist.history["accuracy"]:                               # accuracy = integer / 320
+        assert abs(a * 320 - round(a * 320)) < 1e-3
+    assert hist.metrics is hist.history and max(hist.metrics["accuracy"]) <= 1.0
+
+
+def test_training_reduces_loss_on_learnable_data():
+    (x, y), _ = tf.keras.datasets.mnist.synthetic(2048, 16, seed=3)
+    x = x.reshape(len(x), 28, 28, 1) / 255.0
+    m = tf.keras.Sequential([tf.keras.layers.Conv2D(8, 3, activation="relu", input_shape=(28, 28, 1)),
+                             tf.keras.layers.MaxPooling2D(), tf.keras.layers.Flatten(),
+                             tf.keras.layers.Dense(32, activation="relu"), tf.keras.layers.Dense(10)])
+    m.compile(loss=tf.keras.losses.SparseCategoricalCrossentropy(from_logits=True),
+              optimizer=tf.keras.optimizers.SGD(learning_rate=0.05), metrics=["accuracy"])
+    h = m.fit(x, y, batch_size=64, epochs=4, verbose=0)
+    assert h.history["loss"][-1] < 0.5 * h.history["loss"][0]
+    assert h.history["accuracy"][-1] > 0.8
+    loss, acc = m.evaluate(x[:256], y[:256], batch_size=64)
+    assert acc > 0.8
+
+
+def test_fit_matches_pytorch_autograd_reference():
+    """One SGD step of the engine == one SGD step of the same model written in PyTorch."""
+    import torch
+    import torch.nn.functional as F
+    m = _readme_model()
+    rng = np.random.default_rng(1)
+    x = rng.random((64, 28, 28, 1)).astype(np.float32)
+    y = rng.integers(0, 10, 64)
+    w0 = [torch.tensor(a, requires_grad=True) for a in m.get_weights()]
+    m.fit(x, y, batch_size=64, epochs=1, steps_per_epoch=1, verbose=0)
+    w1 = m.get_weights()
+    xt = torch.from_numpy(x).permute(0, 3, 1, 2)
+    h = F.relu(F.conv2d(xt, w0[0].permute(3, 2, 0, 1), w0[1]))
+    h = F.max_pool2d(h, 2).permute(0, 2, 3, 1).reshape(64, -1)          # Flatten in H, W, C order
+    h = F.relu(h @ w0[2] + w0[3])
+    loss = F.cross_entropy(h @ w0[4] + w0[5], torch.from_numpy(y))
+    loss.backward()
+    for a0, a1 in zip(w0, w1):
+        ref = (a0 - 0.001 * a0.grad).detach().numpy()
+        assert np.allclose(a1, ref, atol=1e-6), np.abs(a1 - ref).max()
+    assert abs(m.history.history["loss"][0] - loss.item()) < 1e-4
+
+
+def test_errors():
+    with pytest.raises(NotImplementedError):
+        tf.keras.losses.SparseCategoricalCrossentropy(from_logits=False)
+    with pytest.raises(NotImplementedError):
+        tf.keras.optimizers.SGD(momentum=0.9)
+    m = _readme_model()
+    with pytest.raises(ValueError):
+        m.fit(np.zeros((10, 28, 28, 1)), np.zeros(10), batch_size=64, verbose=0)
+
+
+def test_version_and_datasets():
+    assert tf.utils.tf_version() == "2.0" and tf.__version__.startswith("2.0")
+    (xtr, ytr), (xte, yte) = tf.keras.datasets.mnist.load_data()
+    assert xtr.shape == (60000, 28, 28) and ytr.shape == (60000,) and xte.shape == (10000, 28, 28)
+    assert xtr.dtype == np.uint8 and int(ytr.max()) == 9
