@@ -1,0 +1,229 @@
+#!/usr/bin/env python
+"""Headline benchmark: training throughput (images/s) of the README's MNIST CNN under the
+multi-worker mirrored strategy, global batch 64 x N, on N B200s of one node
+(BASELINE.json metric / config 2; model README.md:292-302).
+
+    python bench.py --gpus 1 --steps 300 --warmup 20
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
+        --master-port 29500 bench.py --gpus 8 --steps 300 --warmup 20
+
+Prints ONE JSON line on rank 0.  `value` is the whole-job images/s, timed on the device with
+CUDA events around exactly K steps (barrier + synchronize on both sides, max over ranks).
+Inputs: every step reads a fresh batch out of a 60000-image synthetic MNIST-shaped data set
+(188 MB fp32, larger than the 126 MB L2), resident on the device for `value` and in pinned
+host memory for `e2e` (per-step H2D copy of the batch, per-step D2H read of the metric sums,
+through the public `model.fit`).
+
+--impl reference : the reference repository is a README with no installable code, so this arm
+                   reports {"impl": "reference", "unavailable": ...}.
+--impl torch     : the stock-PyTorch baseline (cuDNN/cuBLAS + DDP/NCCL) for the same model.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+
+# ----------------------------------------------------------------------------------------
+class ClockSampler:
+    """Samples SM clocks and throttle reasons with nvidia-smi while the timed region runs."""
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int, period_ms: int = 100):
+        self.index, self.period_ms = index, period_ms
+        self.rows: list[list[str]] = []
+        self.proc = None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                 "-i", str(self.index), "-lms", str(self.period_ms)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) >= 7:
+                self.rows.append(parts)
+
+    def __exit__(self, *a):
+        if self.proc is not None:
+            time.sleep(self.period_ms / 1000.0)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+        return False
+
+    def summary(self) -> dict:
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        sm = sorted(float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit())
+        mx = max((float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()), default=None)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def _dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", str(rank)))
+    return rank, world, local
+
+
+def _max_over_ranks(value: float, world: int) -> float:
+    if world == 1:
+        return value
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([value], dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t[0])
+
+
+def _barrier(world: int):
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+
+
+# ----------------------------------------------------------------------------------------
+def run_ours(args) -> dict:
+    import numpy as np
+    import torch
+    import distributed_b200 as tf
+    from distributed_b200._native import cuda_lib
+
+    rank, world, local = _dist_env()
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run"
+    torch.cuda.set_device(local)
+    per_gpu = args.batch_per_gpu
+    global_batch = per_gpu * world
+    if world > 1:
+        strategy = tf.distribute.experimental.MultiWorkerMirroredStrategy()
+        strategy._ensure_group()
+    else:
+        strategy = tf.distribute.OneDeviceStrategy()
+    with strategy.scope():
+        model = tf.models.mnist_cnn() if args.model == "mnist_cnn" else tf.models.scaled_cnn()
+
+    # synthetic data of MNIST shape: N_IMAGES x 28 x 28 x 1 fp32 (> L2), labels int32
+    n_images = args.dataset_images - args.dataset_images % global_batch
+    g = torch.Generator().manual_seed(0)
+    x_host = torch.rand((n_images, 28, 28, 1), generator=g, dtype=torch.float32).pin_memory()
+    y_host = torch.randint(0, 10, (n_images,), generator=g, dtype=torch.int32).pin_memory()
+    steps_in_src = n_images // global_batch
+
+    # --- warm-up through the public API (builds the trainer, captures the step graphs) ---
+    model.fit(x_host, y_host, batch_size=global_batch, epochs=1, steps_per_epoch=max(args.warmup, 3), verbose=0)
+    trainer = model._trainer
+    x_dev, y_dev = x_host.to(trainer.be.device), y_host.to(trainer.be.device)
+    torch.cuda.synchronize()
+
+    # --- device-timed region: exactly K steps, CUDA events on the launching stream --------
+    launches0 = cuda_lib.launch_count()
+    _barrier(world)
+    torch.cuda.synchronize()
+    with ClockSampler(local) as clocks:
+        ms = trainer.run_steps(x_dev, y_dev, model._global_step, steps_in_src, args.steps, global_batch, timed=True)
+        torch.cuda.synchronize()
+    _barrier(world)
+    launches = cuda_lib.launch_count() - launches0
+    model._global_step += args.steps
+    ms = _max_over_ranks(ms, world)
+    value = args.steps * global_batch / (ms / 1e3)
+
+    # --- end to end through model.fit: per-step H2D from pinned memory + per-step D2H -------
+    _barrier(world)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    hist = model.fit(x_host, y_host, batch_size=global_batch, epochs=1, steps_per_epoch=args.steps, verbose=0)
+    torch.cuda.synchronize()
+    e2e_s = _max_over_ranks(time.perf_counter() - t0, world)
+    e2e = args.steps * global_batch / e2e_s
+
+    out = {
+        "metric": "images/sec (device-timed, max over ranks)", "value": value, "unit": "images/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "tf32 (fp32 storage, fp32 accumulate; first conv in fp32)", "data": "synthetic",
+        "impl": "distributed_b200",
+        "config": {"model": "README MNIST CNN (conv32-3x3/maxpool/dense64/dense10, SGD lr=1e-3)"
+                   if args.model == "mnist_cnn" else "scaled CNN (conv64/conv128/dense1024)",
+                   "global_batch": global_batch, "batch_per_gpu": per_gpu, "input": "28x28x1",
+                   "parallelism": f"dp{world}",
+                   "all_reduce": trainer.comm.description,
+                   "l2_policy": f"inputs larger than L2: each step reads a fresh batch of a {n_images}-image "
+                                f"({n_images * 3136 / 1e6:.0f} MB) data set",
+                   "kernels_per_step": trainer.kernels_per_step, "cuda_graph": trainer.use_graph},
+        "clocks": clocks.summary(),
+        "e2e": {"value": e2e, "unit": "images/s", "h2d_bytes_per_step": per_gpu * 3136 + per_gpu * 4,
+                "d2h_bytes_per_step": 16, "ms_per_step": 1e3 * e2e_s / args.steps,
+                "api": "model.fit(x_pinned, y_pinned, batch_size, epochs=1, steps_per_epoch=K)"},
+        "gpu_launches": int(launches),
+        "final_loss": hist.history["loss"][-1],
+    }
+    return out if rank == 0 else {}
+
+
+def run_reference(args) -> dict:
+    return {"impl": "reference",
+            "unavailable": "reference repo is a README + LICENSE with no installable code (pip install of "
+                           "/root/reference fails: no setup.py/pyproject); it depends on TensorFlow 2.0, "
+                           "which is not in the offline wheelhouse"}
+
+
+def run_torch(args) -> dict:
+    from baseline.torch_baseline import run
+    return run(args, ClockSampler, _dist_env, _max_over_ranks, _barrier)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=300)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "torch"])
+    ap.add_argument("--model", default="mnist_cnn", choices=["mnist_cnn", "scaled_cnn"])
+    ap.add_argument("--batch-per-gpu", type=int, default=64)
+    ap.add_argument("--dataset-images", type=int, default=60000)
+    ap.add_argument("--torch-graph", action="store_true", help="torch baseline: capture the step in a CUDA graph")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        out = run_reference(args)
+        if int(os.environ.get("RANK", "0")) == 0:
+            print(json.dumps(out), flush=True)
+        return
+    out = run_torch(args) if args.impl == "torch" else run_ours(args)
+    if out:
+        print(json.dumps(out), flush=True)
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

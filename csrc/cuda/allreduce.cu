@@ -1,0 +1,225 @@
+// allreduce.cu — the communication-bound hot path: cross-replica gradient all-reduce FUSED with
+// the 1/num_workers averaging and the SGD update, over NVLink peer memory (sm_100a).
+//
+// Every rank holds a weight arena W_r and a gradient arena G_r in symmetric memory: every GPU
+// can load/store every peer's arenas directly through NVSwitch (csrc/runtime/symm.cpp).
+// One kernel per step replaces "batch_all_reduce: 6 all-reduces" + 4 metric all-reduces + the
+// optimizer (README.md:403-407, 302).  Three algorithms, chosen per message size:
+//
+//   one-shot   every rank reads all peers' G, sums in rank order (bit-identical everywhere),
+//              updates its own W.                          traffic/GPU: (N-1) S in
+//   two-shot   rank r owns shard r: reads shard r of every G, averages, applies SGD, and writes
+//              the *updated weights* into every peer's W — the all-gather carries weights, so
+//              no optimizer pass exists at all.            traffic/GPU: (N-1)/N S in + out
+//   NVLS       like two-shot, but the switch does the sum (multimem.ld_reduce) and the
+//              broadcast (multimem.st).                     traffic/GPU: S/N in + S/N out
+//
+// Elements >= n_params are the metric tail slots (loss sum, correct count, ...): they are
+// summed, not averaged, and *added* to the running sums kept in W's tail.
+// After the update each rank zeroes its own G, so the next backward can accumulate into it.
+//
+// Cross-GPU barriers are per block: block b of every rank meets block b of every other rank
+// on monotone epoch counters in the peers' signal pads (st.release.sys / ld.acquire.sys).
+#include "host_common.h"
+#include "ptx.cuh"
+
+namespace b2d {
+
+constexpr int kMaxRanks = 8;
+constexpr int kArThreads = 512;
+constexpr int kMaxArBlocks = 64;  // signal pad: kMaxArBlocks * kMaxRanks words per rank
+
+struct ArArgs {
+  float* w[kMaxRanks];        // weight arenas (peer-mapped); w[rank] is local
+  float* g[kMaxRanks];        // gradient arenas
+  uint32_t* sig[kMaxRanks];   // signal pads
+  uint32_t* epoch[kMaxRanks]; // per-rank local barrier epochs (only [rank] is used; all set in emulation)
+  float* w_mc;                // NVLS multicast views (null when not bound)
+  float* g_mc;
+  float* out[kMaxRanks];      // plain all-reduce (no SGD): destination buffers
+  long long n_params4;        // float4 count of the SGD range
+  long long n_total4;         // float4 count of the whole arena
+  float scale;                // lr / world
+  int rank, world;
+  int emulate;                // 1: blockIdx.y is the rank (single-GPU cooperative test mode)
+  int plain;                  // 1: out = sum(g), no SGD, no zeroing
+};
+
+// Block-level barrier across ranks.  All threads of the block call it.
+__device__ __forceinline__ void rank_barrier(const ArArgs& a, int rank, uint32_t* s_epoch) {
+  __syncthreads();  // every thread's earlier accesses are ordered before the release below
+  const int b = blockIdx.x;
+  if (threadIdx.x == 0) {
+    uint32_t* ep = a.epoch[rank] + b;
+    *s_epoch = *ep + 1;
+    *ep = *s_epoch;
+  }
+  __syncthreads();
+  const uint32_t e = *s_epoch;
+  if (threadIdx.x < a.world) {
+    const int p = threadIdx.x;
+    st_release_sys(a.sig[p] + b * kMaxRanks + rank, e);
+    const uint32_t* mine = a.sig[rank] + b * kMaxRanks + p;
+    long long spins = 0;
+    while (static_cast<int32_t>(ld_acquire_sys(mine) - e) < 0) {
+      if (++spins > (1ll << 31)) {  // a peer died: fail loudly instead of hanging the GPU forever
+        printf("b200dist: rank %d block %d timed out waiting for rank %d (epoch %u)\n", rank, b, p, e);
+        __trap();
+      }
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ float4 f4_add(float4 a, float4 b) {
+  return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+}
+
+__device__ __forceinline__ float4 apply_update(float4 w, float4 s, bool is_param, float scale) {
+  if (is_param) return make_float4(w.x - scale * s.x, w.y - scale * s.y, w.z - scale * s.z, w.w - scale * s.w);
+  return f4_add(w, s);  // metric tail: running sums
+}
+
+enum ArAlgo : int { kOneShot = 0, kTwoShot = 1, kNvls = 2 };
+
+template <int ALGO>
+__global__ void __launch_bounds__(kArThreads) allreduce_sgd_kernel(const ArArgs a) {
+  __shared__ uint32_t s_epoch;
+  const int rank = a.emulate ? blockIdx.y : a.rank;
+  const int world = a.world;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+
+  rank_barrier(a, rank, &s_epoch);  // A: every replica's gradients are complete
+
+  if (ALGO == kOneShot) {
+    float4* wl = reinterpret_cast<float4*>(a.plain ? a.out[rank] : a.w[rank]);
+    for (long long i = t0; i < a.n_total4; i += stride) {
+      float4 acc = zero;
+#pragma unroll 1
+      for (int p = 0; p < world; ++p)  // fixed rank order: identical bits on every replica
+        acc = f4_add(acc, ld_nc_na_f4(reinterpret_cast<const float4*>(a.g[p]) + i));
+      wl[i] = a.plain ? acc : apply_update(wl[i], acc, i < a.n_params4, a.scale);
+    }
+  } else {
+    const long long per = (a.n_total4 + world - 1) / world;
+    const long long s0 = min(a.n_total4, per * rank), s1 = min(a.n_total4, s0 + per);
+    for (long long i = s0 + t0; i < s1; i += stride) {
+      float4 acc;
+      if (ALGO == kNvls) {
+        acc = multimem_ld_reduce_add_f4(reinterpret_cast<const float4*>(a.g_mc) + i);
+      } else {
+        acc = zero;
+#pragma unroll 1
+        for (int p = 0; p < world; ++p)
+          acc = f4_add(acc, ld_nc_na_f4(reinterpret_cast<const float4*>(a.g[p]) + i));
+      }
+      float4 v = acc;
+      if (!a.plain) v = apply_update(reinterpret_cast<const float4*>(a.w[rank])[i], acc, i < a.n_params4, a.scale);
+      if (ALGO == kNvls) {
+        multimem_st_f4(reinterpret_cast<float4*>(a.plain ? a.g_mc : a.w_mc) + i, v);
+      } else {
+#pragma unroll 1
+        for (int p = 0; p < world; ++p)
+          st_na_f4(reinterpret_cast<float4*>(a.plain ? a.g[p] : a.w[p]) + i, v);
+      }
+    }
+  }
+
+  rank_barrier(a, rank, &s_epoch);  // B: all reads of G and all writes of W have completed
+
+  if (!a.plain) {
+    // zero the stripes of my G that block b of some rank has just consumed
+    float4* gl = reinterpret_cast<float4*>(a.g[rank]);
+    if (ALGO == kOneShot) {
+      for (long long i = t0; i < a.n_total4; i += stride) gl[i] = zero;
+    } else {
+      const long long per = (a.n_total4 + world - 1) / world;
+      for (int q = 0; q < world; ++q) {
+        const long long s0 = min(a.n_total4, per * q), s1 = min(a.n_total4, s0 + per);
+        for (long long i = s0 + t0; i < s1; i += stride) gl[i] = zero;
+      }
+    }
+  }
+}
+
+}  // namespace b2d
+
+using namespace b2d;
+
+struct b2d_allreduce_desc {
+  void* w[kMaxRanks];
+  void* g[kMaxRanks];
+  void* sig[kMaxRanks];
+  void* epoch[kMaxRanks];
+  void* out[kMaxRanks];
+  void* w_mc;
+  void* g_mc;
+  int64_t n_params;  // floats, multiple of 4
+  int64_t n_total;   // floats, multiple of 4
+  float lr;
+  int rank, world;
+  int algo;     // 0 one-shot, 1 two-shot, 2 NVLS, -1 automatic
+  int emulate;  // all ranks in one cooperative launch on this GPU (tests)
+  int plain;    // plain sum all-reduce: one-shot writes out[], two-shot/NVLS are in place on g
+  int blocks;   // 0 = automatic
+};
+
+extern "C" size_t b2d_allreduce_signal_bytes(void) {
+  return sizeof(uint32_t) * kMaxArBlocks * kMaxRanks;
+}
+extern "C" size_t b2d_allreduce_epoch_bytes(void) { return sizeof(uint32_t) * kMaxArBlocks; }
+
+// Size-based dispatch: below the crossover the single pass of one-shot wins on latency; above
+// it the (N-1)/N traffic of two-shot (or S/N of NVLS) wins on bandwidth.
+extern "C" int b2d_allreduce_pick_algo(int64_t n_total_floats, int world, int have_multicast) {
+  const int64_t bytes = n_total_floats * 4;
+  if (world <= 2 || bytes <= (256 << 10) / world * 2) return kOneShot;
+  if (have_multicast && bytes >= (1 << 20)) return kNvls;
+  return kTwoShot;
+}
+
+extern "C" int b2d_allreduce_sgd(const b2d_allreduce_desc* d, void* stream) {
+  B2D_REQUIRE(d != nullptr, "allreduce_sgd: null descriptor");
+  B2D_REQUIRE(d->world >= 1 && d->world <= kMaxRanks, "allreduce_sgd: world must be in [1, %d]", kMaxRanks);
+  B2D_REQUIRE(d->n_total % 4 == 0 && d->n_params % 4 == 0 && d->n_params <= d->n_total,
+              "allreduce_sgd: sizes must be multiples of 4 floats");
+  int algo = d->algo;
+  if (algo < 0) algo = b2d_allreduce_pick_algo(d->n_total, d->world, d->g_mc != nullptr);
+  B2D_REQUIRE(algo != kNvls || (d->g_mc != nullptr && (d->plain || d->w_mc != nullptr)),
+              "allreduce_sgd: NVLS requested but no multicast mapping is bound");
+  ArArgs a{};
+  for (int p = 0; p < d->world; ++p) {
+    a.w[p] = static_cast<float*>(d->w[p]);
+    a.g[p] = static_cast<float*>(d->g[p]);
+    a.sig[p] = static_cast<uint32_t*>(d->sig[p]);
+    a.epoch[p] = static_cast<uint32_t*>(d->epoch[p]);
+    a.out[p] = static_cast<float*>(d->out[p]);
+  }
+  a.w_mc = static_cast<float*>(d->w_mc), a.g_mc = static_cast<float*>(d->g_mc);
+  a.n_params4 = d->n_params / 4, a.n_total4 = d->n_total / 4;
+  a.scale = d->lr / static_cast<float>(d->world);
+  a.rank = d->rank, a.world = d->world, a.emulate = d->emulate, a.plain = d->plain;
+
+  const long long work4 = algo == kOneShot ? a.n_total4 : (a.n_total4 + d->world - 1) / d->world;
+  int blocks = d->blocks > 0 ? d->blocks
+                             : static_cast<int>(std::min<long long>(
+                                   kMaxArBlocks, std::max<long long>(1, (work4 + kArThreads * 4 - 1) / (kArThreads * 4))));
+  blocks = std::min(blocks, kMaxArBlocks);
+  void (*kern)(const ArArgs) = algo == kOneShot  ? allreduce_sgd_kernel<kOneShot>
+                               : algo == kTwoShot ? allreduce_sgd_kernel<kTwoShot>
+                                                  : allreduce_sgd_kernel<kNvls>;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (d->emulate) {
+    // All ranks in one launch: the blocks wait on one another, so they must be co-resident.
+    void* params[] = {&a};
+    B2D_CUDA_CHECK(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(kern), dim3(blocks, d->world),
+                                               dim3(kArThreads), params, 0, st));
+  } else {
+    kern<<<blocks, kArThreads, 0, st>>>(a);
+    B2D_CUDA_CHECK(cudaGetLastError());
+  }
+  count_launch();
+  return B2D_OK;
+}

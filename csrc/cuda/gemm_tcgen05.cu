@@ -12,6 +12,7 @@
 //
 // Reference behaviour: Dense layers of the README model (README.md:296-297); the reference
 // itself ships no kernels.
+#include <cstdlib>
 #include <new>
 
 #include "host_common.h"
@@ -285,8 +286,13 @@ int encode_tmap_2d(CUtensorMap* tm, int dtype, const void* base, uint64_t inner,
   const cuuint64_t strides[1] = {row_stride_bytes};
   const cuuint32_t box[2] = {box_inner, box_outer};
   const cuuint32_t estr[2] = {1, 1};
+  // fp32 operands are loaded as TFLOAT32: the TMA unit rounds them to tf32 on the way into
+  // shared memory (round-to-nearest) instead of the MMA truncating the low mantissa bits.
+  // B2D_TF32_TRUNCATE=1 keeps the raw fp32 bits (for A/B comparison of the rounding mode).
+  static const bool truncate = getenv("B2D_TF32_TRUNCATE") != nullptr;
   const CUtensorMapDataType dt =
-      dtype == B2D_F32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+      dtype == B2D_F32 ? (truncate ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_TFLOAT32)
+                       : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   // MN-major fp32 tiles are consumed with the 32 B-chunk swizzle (see GemmCfg::MN_LAYOUT).
   const CUtensorMapSwizzle sw = (mn_major && dtype == B2D_F32) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
                                                                : CU_TENSOR_MAP_SWIZZLE_128B;

@@ -156,7 +156,15 @@ class Sequential(Model):
 
     @staticmethod
     def _as_host_tensors(x, y, n_rows, pin):
-        """fp32 NHWC samples and int32 labels for the first ``n_rows`` rows (pinned for CUDA)."""
+        """fp32 NHWC samples and int32 labels for the first ``n_rows`` rows (pinned for CUDA).
+
+        Tensors that are already fp32 / int32, contiguous and (for CUDA) pinned are used in
+        place, so a caller who keeps the data set in pinned memory pays no conversion per fit.
+        """
+        if isinstance(x, torch.Tensor) and isinstance(y, torch.Tensor) and x.dtype == torch.float32 \
+                and y.dtype == torch.int32 and x.dim() == 4 and x.is_contiguous() and y.is_contiguous() \
+                and not x.is_cuda and (not pin or (x.is_pinned() and y.is_pinned())):
+            return x[:n_rows], y[:n_rows]
         xt = torch.as_tensor(np.ascontiguousarray(np.asarray(x[:n_rows]), dtype=np.float32))
         if xt.dim() == 3:
             xt = xt.unsqueeze(-1)
