@@ -478,3 +478,132 @@ extern "C" int b2d_gemm_plan_run(const b2d_gemm_plan* p, void* stream) {
 }
 
 extern "C" void b2d_gemm_plan_destroy(b2d_gemm_plan* p) { delete p; }
+
+// ---------------------------------------------------------------------------------------
+// b2d_gemm_noalloc — the same GEMM for callers that must not allocate device memory.
+//
+// Some users of this library cannot call cudaMalloc at the point where they need a GEMM:
+// a host application that has handed the whole GPU to its own memory pool (so a driver
+// allocation would fail, or would fragment a budget somebody else accounts for), a plug-in
+// running inside another runtime's callback where driver allocations are forbidden, or a
+// latency-critical loop that cannot afford the device-wide synchronisation an allocation
+// implies while other streams are busy.  The regular entry points push the split-K scratch
+// (fp32 partial sums + tile counters) onto the caller; this one keeps it inside the library, in
+// a fixed array that is part of the module image.
+//
+// Consequences the caller has to know about:
+//   * Every GPU that loads this library carries the array (1 MiB + 1 KiB) until the process
+//     exits, whether or not the entry point is ever used.
+//   * The scratch is sized at compile time.  A problem whose split-K rendezvous needs more than
+//     kStaticWorkspaceFloats partial sums or kStaticCounterWords output tiles is rejected with
+//     B2D_ERR_LIMIT (use b2d_gemm_plan_create with your own workspace instead).
+//   * All calls on a device share the one array.  Each call clears the part it is about to use
+//     (stream-ordered, before the kernel), so leftovers of an earlier call never leak in — but
+//     two calls that are in flight on the GPU at the same time (different streams, or the same
+//     call from two host threads) race on it and produce garbage.  Serialise them.
+//   * The first call on each device looks up the array's device address.  Make that first call
+//     with the intended device current, and before any stream capture is begun.
+// Nothing in here calls cudaMalloc / cudaFree or any allocating routine, on the host or the
+// device; the descriptor, tensor maps and launch arguments live on the caller's stack.
+// ---------------------------------------------------------------------------------------
+#include <mutex>
+
+constexpr size_t kStaticCounterWords = 256;            // one counter per output tile
+constexpr size_t kStaticWorkspaceFloats = 256 * 1024;  // 1 MiB of fp32 partial sums
+
+// In host code this name is only a handle for cudaGetSymbolAddress — it is NOT a device
+// pointer and must never be passed to a kernel directly.
+static __device__ __align__(256) float b2d_gemm_static_scratch[kStaticCounterWords + kStaticWorkspaceFloats];
+
+namespace {
+
+constexpr int kMaxDevices = 64;
+float* g_static_scratch_addr[kMaxDevices] = {};
+std::mutex g_static_scratch_mu;
+
+// Device address of the scratch array on the current device (resolved once per device).
+int static_scratch_for_current_device(float** out) {
+  int dev = -1;
+  B2D_CUDA_CHECK(cudaGetDevice(&dev));
+  B2D_REQUIRE(dev >= 0 && dev < kMaxDevices, "gemm_noalloc: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_static_scratch_mu);
+  if (g_static_scratch_addr[dev] == nullptr) {
+    void* p = nullptr;
+    B2D_CUDA_CHECK(cudaGetSymbolAddress(&p, b2d_gemm_static_scratch));
+    B2D_REQUIRE(p != nullptr, "gemm_noalloc: cudaGetSymbolAddress returned a null address");
+    g_static_scratch_addr[dev] = static_cast<float*>(p);
+  }
+  *out = g_static_scratch_addr[dev];
+  return B2D_OK;
+}
+
+}  // namespace
+
+extern "C" size_t b2d_gemm_noalloc_max_workspace_floats(void) { return kStaticWorkspaceFloats; }
+extern "C" size_t b2d_gemm_noalloc_max_tiles(void) { return kStaticCounterWords; }
+
+extern "C" int b2d_gemm_noalloc(const b2d_gemm_desc* desc, void* stream) {
+  B2D_REQUIRE(desc != nullptr, "gemm_noalloc: null descriptor");
+  const b2d_gemm_desc& d = *desc;
+  b2d_gemm_geometry g;
+  int rc = resolve(d, &g);
+  if (rc != B2D_OK) return rc;
+  B2D_REQUIRE(d.A && d.B && d.D, "gemm_noalloc: null operand pointer");
+  B2D_REQUIRE((reinterpret_cast<uintptr_t>(d.A) % 16) == 0 && (reinterpret_cast<uintptr_t>(d.B) % 16) == 0 &&
+                  (reinterpret_cast<uintptr_t>(d.D) % 16) == 0,
+              "gemm_noalloc: operand pointers must be 16-byte aligned");
+  const bool finalize = g.splits > 1 && !d.accumulate;
+  const size_t ws_floats = finalize ? static_cast<size_t>(g.m_tiles) * kBlockM * g.n_tiles * g.block_n : 0;
+  const size_t tiles = finalize ? static_cast<size_t>(g.m_tiles) * g.n_tiles : 0;
+  if (ws_floats > kStaticWorkspaceFloats || tiles > kStaticCounterWords) {
+    set_error("gemm_noalloc: this problem's split-K scratch (%zu partial sums, %zu tiles) exceeds the "
+              "built-in maximum (%zu partial sums, %zu tiles); use b2d_gemm_plan_create with a "
+              "caller-provided workspace",
+              ws_floats, tiles, kStaticWorkspaceFloats, kStaticCounterWords);
+    return B2D_ERR_LIMIT;
+  }
+  float* scratch = nullptr;
+  rc = static_scratch_for_current_device(&scratch);
+  if (rc != B2D_OK) return rc;
+  uint32_t* counters = reinterpret_cast<uint32_t*>(scratch);
+  float* workspace = scratch + kStaticCounterWords;
+
+  b2d_gemm_plan plan;  // on the stack: no host allocation either
+  const int es = d.dtype == B2D_F32 ? 4 : 2;
+  const uint32_t block_k = 128 / es, atom = 128 / es;
+  if (!d.a_mn_major)
+    rc = encode_tmap_2d(&plan.args.tmA, d.dtype, d.A, d.K, d.M, d.lda * es, block_k, kBlockM, false);
+  else
+    rc = encode_tmap_2d(&plan.args.tmA, d.dtype, d.A, d.M, d.K, d.lda * es, atom, block_k, true);
+  if (rc != B2D_OK) return rc;
+  if (!d.b_mn_major)
+    rc = encode_tmap_2d(&plan.args.tmB, d.dtype, d.B, d.K, d.N, d.ldb * es, block_k, g.block_n, false);
+  else
+    rc = encode_tmap_2d(&plan.args.tmB, d.dtype, d.B, d.N, d.K, d.ldb * es, atom, block_k, true);
+  if (rc != B2D_OK) return rc;
+  GemmArgs& a = plan.args;
+  a.D = d.D, a.bias = d.bias, a.mask = d.mask, a.ws = workspace, a.counters = counters;
+  a.ldd = d.ldd, a.ldmask = d.ldmask, a.ldws = static_cast<long long>(g.n_tiles) * g.block_n;
+  a.M = d.M, a.N = d.N, a.K = d.K;
+  a.kb_total = g.k_blocks, a.kb_per_split = ceil_div(g.k_blocks, g.splits), a.splits = g.splits;
+  a.flags = (d.relu ? kFlagRelu : 0) | (d.accumulate ? kFlagAccumulate : 0) |
+            (finalize ? kFlagFinalize : 0) | (d.out_dtype == B2D_BF16 ? kFlagOutBf16 : 0);
+  if (d.dtype == B2D_F32)
+    select_major<MmaKind::TF32>(d.a_mn_major, d.b_mn_major, g.block_n, &plan.kernel, &plan.smem_bytes);
+  else
+    select_major<MmaKind::F16>(d.a_mn_major, d.b_mn_major, g.block_n, &plan.kernel, &plan.smem_bytes);
+  B2D_CUDA_CHECK(cudaFuncSetAttribute(reinterpret_cast<const void*>(plan.kernel),
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, plan.smem_bytes));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (finalize) {
+    // The rendezvous needs zeroed counters and partial sums.  The array still holds whatever
+    // the previous call (possibly a different shape, possibly aborted) left behind.
+    B2D_CUDA_CHECK(cudaMemsetAsync(counters, 0, tiles * sizeof(uint32_t), st));
+    B2D_CUDA_CHECK(cudaMemsetAsync(workspace, 0, ws_floats * sizeof(float), st));
+  }
+  const dim3 grid(g.m_tiles, g.n_tiles, g.splits);
+  plan.kernel<<<grid, 256, plan.smem_bytes, st>>>(plan.args);
+  count_launch();
+  B2D_CUDA_CHECK(cudaGetLastError());
+  return B2D_OK;
+}

@@ -87,6 +87,21 @@ int b2d_gemm_plan_create(const b2d_gemm_desc* desc, b2d_gemm_plan** out);
 int b2d_gemm_plan_run(const b2d_gemm_plan* plan, void* stream);
 void b2d_gemm_plan_destroy(b2d_gemm_plan* plan);
 
+/* The same GEMM for callers that cannot allocate device memory (a host that has given the
+ * whole GPU to its own pool, a plug-in inside another runtime's callback, a latency-critical
+ * loop that cannot take an allocation's device-wide synchronisation).  desc->workspace and
+ * desc->counters are ignored: the split-K scratch is a fixed array inside the library
+ * (b2d_gemm_noalloc_max_workspace_floats() partial sums = 1 MiB, b2d_gemm_noalloc_max_tiles()
+ * output tiles), present on every GPU that loads the library until the process exits.
+ * Problems whose rendezvous needs more return B2D_ERR_LIMIT.  The call allocates nothing, on
+ * host or device.  All calls on a device share the array: each clears what it will use before
+ * its kernel, but calls that overlap on the GPU race.  The first call on a device resolves the
+ * array's address; make it with that device current and before any stream capture.
+ * This entry point has no counterpart in the reference. */
+int b2d_gemm_noalloc(const b2d_gemm_desc* desc, void* stream);
+size_t b2d_gemm_noalloc_max_workspace_floats(void);
+size_t b2d_gemm_noalloc_max_tiles(void);
+
 #ifdef __cplusplus
 }
 #endif
