@@ -146,94 +146,151 @@ __global__ void __launch_bounds__(256) conv_c1_pool_bwd_kernel(
 
 // =======================================================================================
 // Classifier head: logits = h.W + b ; softmax cross-entropy ; all gradients.   [K4+K5+K6]
-//   one warp per batch row; W (K x C) lives in shared memory; dW/db partials are accumulated
-//   in shared memory and flushed with one global atomic per element per CTA.
+//   Phase 1 — one warp per batch row (8 rows per pass): logits by warp-reduced dot products
+//   against W in shared memory, softmax, dz, and dh = dz.W^T (ReLU-masked) written straight out.
+//   Phase 2 — the whole CTA turns the pass's 8 (h, dz) rows into dW / db partial sums held in
+//   registers (each thread owns fixed (k, c) outputs), so no shared-memory atomics exist; one
+//   global atomic per output per CTA at the end.  Optionally also accumulates the bias gradient
+//   of the layer that produced h (column sums of dh), saving that layer a kernel.
 //   metrics[0] += sum of per-row losses, metrics[1] += #correct, metrics[2] += #rows.
-//   dh[r,k] = (sum_c dz[r,c] W[k,c]) * (h[r,k] > 0 if relu_mask)
 // =======================================================================================
 constexpr int kHeadMaxC = 32;
+constexpr int kHeadRows = 8;          // rows per pass = warps per CTA
+constexpr int kHeadMaxOut = 48;       // dW outputs per thread: K*C <= 48*256
+constexpr int kHeadMaxKPerThread = 8; // dh column sums per thread: K <= 8*256
 
 __global__ void __launch_bounds__(256) dense_xent_head_kernel(
     const float* __restrict__ h, const float* __restrict__ w, const float* __restrict__ bias,
     const int* __restrict__ labels, float* __restrict__ logits_out, float* __restrict__ dh,
-    float* __restrict__ dw, float* __restrict__ db, float* __restrict__ metrics, int B, int K, int C,
-    float grad_scale, int relu_mask, int rows_per_cta) {
+    float* __restrict__ dw, float* __restrict__ db, float* __restrict__ dh_colsum,
+    float* __restrict__ metrics, int B, int K, int C, float grad_scale, int relu_mask,
+    int rows_per_cta) {
   extern __shared__ float sm[];
-  float* ws = sm;            // [K][C]
-  float* dws = ws + K * C;   // [K][C]
-  float* dbs = dws + K * C;  // [C]
-  float* mts = dbs + kHeadMaxC;  // [2]
-  for (int i = threadIdx.x; i < K * C; i += blockDim.x) ws[i] = w[i], dws[i] = 0.f;
-  if (threadIdx.x < kHeadMaxC) dbs[threadIdx.x] = 0.f;
-  if (threadIdx.x < 2) mts[threadIdx.x] = 0.f;
-  __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
+  float* ws = sm;                        // [K][C]
+  float* hs = ws + K * C;                // [8][K]   h rows of this pass
+  float* dhs = hs + kHeadRows * K;       // [8][K]   dh rows of this pass
+  float* dzs = dhs + kHeadRows * K;      // [8][32]
+  float* rowm = dzs + kHeadRows * kHeadMaxC;  // [8][2] loss, correct
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int KC = K * C;
+  for (int i = tid; i < KC; i += 256) ws[i] = w[i];
+  float acc_w[kHeadMaxOut];
+#pragma unroll
+  for (int j = 0; j < kHeadMaxOut; ++j) acc_w[j] = 0.f;
+  float acc_k[kHeadMaxKPerThread];
+#pragma unroll
+  for (int j = 0; j < kHeadMaxKPerThread; ++j) acc_k[j] = 0.f;
+  float acc_b = 0.f, loss_sum = 0.f, correct_sum = 0.f;
   const int row0 = blockIdx.x * rows_per_cta;
   const int row1 = min(B, row0 + rows_per_cta);
-  for (int r = row0 + warp; r < row1; r += nwarp) {
-    const float* hr = h + (size_t)r * K;
+  __syncthreads();
+  for (int base = row0; base < row1; base += kHeadRows) {
+    const int r = base + warp;
+    const bool r_ok = r < row1;
+    // ---- phase 1: this warp's row ----
     float z[kHeadMaxC];
 #pragma unroll
     for (int c = 0; c < kHeadMaxC; ++c) z[c] = 0.f;
-    for (int k = lane; k < K; k += 32) {
-      const float hv = hr[k];
+    if (r_ok) {
+      const float* hr = h + (size_t)r * K;
+      for (int k = lane; k < K; k += 32) {
+        const float hv = hr[k];
+        hs[warp * K + k] = hv;
 #pragma unroll
-      for (int c = 0; c < kHeadMaxC; ++c)
-        if (c < C) z[c] = fmaf(hv, ws[k * C + c], z[c]);
-    }
-    float mx = -INFINITY;
-    int arg = 0;
-#pragma unroll
-    for (int c = 0; c < kHeadMaxC; ++c)
-      if (c < C) {
-        z[c] = warp_sum(z[c]) + bias[c];
-        if (z[c] > mx) mx = z[c], arg = c;
+        for (int c = 0; c < kHeadMaxC; ++c)
+          if (c < C) z[c] = fmaf(hv, ws[k * C + c], z[c]);
       }
-    const int yl = labels[r];
-    float se = 0.f, zy = 0.f;
-#pragma unroll
-    for (int c = 0; c < kHeadMaxC; ++c)
-      if (c < C) {
-        se += __expf(z[c] - mx);
-        if (c == yl) zy = z[c];
-      }
-    const float lse = mx + __logf(se);
-    const float inv = 1.f / se;
-#pragma unroll
-    for (int c = 0; c < kHeadMaxC; ++c)
-      if (c < C) {
-        if (logits_out != nullptr && lane == 0) logits_out[(size_t)r * C + c] = z[c];
-        z[c] = (__expf(z[c] - mx) * inv - (c == yl ? 1.f : 0.f)) * grad_scale;  // dz
-      }
-    if (lane == 0) {
-      atomicAdd(&mts[0], lse - zy);
-      atomicAdd(&mts[1], arg == yl ? 1.f : 0.f);
-    }
-    if (lane < C) {
-      float dzl = 0.f;
-#pragma unroll
-      for (int c = 0; c < kHeadMaxC; ++c)
-        if (c == lane) dzl = z[c];
-      atomicAdd(&dbs[lane], dzl);
-    }
-    for (int k = lane; k < K; k += 32) {
-      const float hv = hr[k];
-      float g = 0.f;
+      float mx = -INFINITY;
+      int arg = 0;
 #pragma unroll
       for (int c = 0; c < kHeadMaxC; ++c)
         if (c < C) {
-          g = fmaf(z[c], ws[k * C + c], g);
-          atomicAdd(&dws[k * C + c], hv * z[c]);
+          z[c] = warp_sum(z[c]) + bias[c];
+          if (z[c] > mx) mx = z[c], arg = c;
         }
-      if (dh != nullptr) dh[(size_t)r * K + k] = (relu_mask && !(hv > 0.f)) ? 0.f : g;
+      const int yl = labels[r];
+      float se = 0.f, zy = 0.f;
+#pragma unroll
+      for (int c = 0; c < kHeadMaxC; ++c)
+        if (c < C) {
+          se += __expf(z[c] - mx);
+          if (c == yl) zy = z[c];
+        }
+      const float lse = mx + __logf(se);
+      const float inv = 1.f / se;
+#pragma unroll
+      for (int c = 0; c < kHeadMaxC; ++c)
+        if (c < C) {
+          if (logits_out != nullptr && lane == 0) logits_out[(size_t)r * C + c] = z[c];
+          z[c] = (__expf(z[c] - mx) * inv - (c == yl ? 1.f : 0.f)) * grad_scale;  // dz
+          if (lane == 0) dzs[warp * kHeadMaxC + c] = z[c];
+        }
+      if (lane == 0) rowm[warp * 2] = lse - zy, rowm[warp * 2 + 1] = arg == yl ? 1.f : 0.f;
+      for (int k = lane; k < K; k += 32) {
+        float g = 0.f;
+#pragma unroll
+        for (int c = 0; c < kHeadMaxC; ++c)
+          if (c < C) g = fmaf(z[c], ws[k * C + c], g);
+        if (relu_mask && !(hs[warp * K + k] > 0.f)) g = 0.f;
+        dhs[warp * K + k] = g;
+        if (dh != nullptr) dh[(size_t)r * K + k] = g;
+      }
+    } else {
+      for (int k = lane; k < K; k += 32) hs[warp * K + k] = 0.f, dhs[warp * K + k] = 0.f;
+      if (lane < kHeadMaxC) dzs[warp * kHeadMaxC + lane] = 0.f;
+      if (lane == 0) rowm[warp * 2] = 0.f, rowm[warp * 2 + 1] = 0.f;
+    }
+    __syncthreads();
+    // ---- phase 2: CTA-wide partial sums over the 8 rows of this pass ----
+#pragma unroll
+    for (int j = 0; j < kHeadMaxOut; ++j) {
+      const int o = tid + j * 256;
+      if (o < KC) {
+        const int k = o / C, c = o - k * C;
+        float s = 0.f;
+#pragma unroll
+        for (int rr = 0; rr < kHeadRows; ++rr) s = fmaf(hs[rr * K + k], dzs[rr * kHeadMaxC + c], s);
+        acc_w[j] += s;
+      }
+    }
+    if (dh_colsum != nullptr) {
+#pragma unroll
+      for (int j = 0; j < kHeadMaxKPerThread; ++j) {
+        const int k = tid + j * 256;
+        if (k < K) {
+          float s = 0.f;
+#pragma unroll
+          for (int rr = 0; rr < kHeadRows; ++rr) s += dhs[rr * K + k];
+          acc_k[j] += s;
+        }
+      }
+    }
+    if (tid < C) {
+#pragma unroll
+      for (int rr = 0; rr < kHeadRows; ++rr) acc_b += dzs[rr * kHeadMaxC + tid];
+    }
+    if (tid == 0) {
+#pragma unroll
+      for (int rr = 0; rr < kHeadRows; ++rr) loss_sum += rowm[rr * 2], correct_sum += rowm[rr * 2 + 1];
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int j = 0; j < kHeadMaxOut; ++j) {
+    const int o = tid + j * 256;
+    if (o < KC) atomicAdd(&dw[o], acc_w[j]);
+  }
+  if (dh_colsum != nullptr) {
+#pragma unroll
+    for (int j = 0; j < kHeadMaxKPerThread; ++j) {
+      const int k = tid + j * 256;
+      if (k < K) atomicAdd(&dh_colsum[k], acc_k[j]);
     }
   }
-  __syncthreads();
-  for (int i = threadIdx.x; i < K * C; i += blockDim.x) atomicAdd(&dw[i], dws[i]);
-  if (threadIdx.x < C) atomicAdd(&db[threadIdx.x], dbs[threadIdx.x]);
-  if (threadIdx.x == 0 && metrics != nullptr) {
-    atomicAdd(&metrics[0], mts[0]);
-    atomicAdd(&metrics[1], mts[1]);
+  if (tid < C) atomicAdd(&db[tid], acc_b);
+  if (tid == 0 && metrics != nullptr) {
+    atomicAdd(&metrics[0], loss_sum);
+    atomicAdd(&metrics[1], correct_sum);
     atomicAdd(&metrics[2], (float)(row1 - row0));
   }
 }
@@ -566,7 +623,8 @@ extern "C" int b2d_conv_c1_pool_bwd(const float* x, const float* dy, const uint8
                                     float* db, int N, int H, int W, int Co, int KS, void* stream) {
   B2D_REQUIRE(KS == 3 || KS == 5, "conv_c1_pool: kernel size must be 3 or 5 (got %d)", KS);
   const int OH = H - KS + 1, OW = W - KS + 1, PH = OH / 2, PW = OW / 2;
-  const int bands = N >= 296 ? 1 : (N >= 148 ? 2 : 4);
+  // Backward pays a cross-warp reduction + ~10*Co global atomics per CTA: fewer, fatter CTAs.
+  const int bands = N >= 120 ? 1 : 2;
   const int band = ceil_div(PH, bands);
   const dim3 grid(N, ceil_div(PH, band));
   const size_t smem = ((size_t)(2 * band + KS) * W + 8 * (KS * KS + 1) * 32) * sizeof(float);
@@ -582,10 +640,12 @@ extern "C" int b2d_conv_c1_pool_bwd(const float* x, const float* dy, const uint8
 
 extern "C" int b2d_dense_xent_head(const float* h, const float* w, const float* bias,
                                    const int* labels, float* logits_out, float* dh, float* dw,
-                                   float* db, float* metrics, int B, int K, int C, float grad_scale,
-                                   int relu_mask, void* stream) {
+                                   float* db, float* dh_colsum, float* metrics, int B, int K, int C,
+                                   float grad_scale, int relu_mask, void* stream) {
   B2D_REQUIRE(C >= 1 && C <= kHeadMaxC, "dense_xent_head: C must be in [1, %d]", kHeadMaxC);
-  const size_t smem = ((size_t)2 * K * C + kHeadMaxC + 2) * sizeof(float);
+  B2D_REQUIRE(K * C <= kHeadMaxOut * 256 && K <= kHeadMaxKPerThread * 256,
+              "dense_xent_head: K*C=%d too large for the fused head", K * C);
+  const size_t smem = ((size_t)K * C + 2 * kHeadRows * K + kHeadRows * kHeadMaxC + 2 * kHeadRows) * sizeof(float);
   B2D_REQUIRE(smem <= 200 * 1024, "dense_xent_head: K*C too large for the fused head (K=%d C=%d)", K, C);
   static bool attr_set = false;
   if (!attr_set) {
@@ -593,10 +653,11 @@ extern "C" int b2d_dense_xent_head(const float* h, const float* w, const float* 
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     attr_set = true;
   }
-  // 8 rows (one per warp) per CTA at small batch; more rows per CTA once the grid is full.
-  const int rows = B <= 8 * 148 ? 8 : ceil_div(B, 148 * 2);
+  // One pass of 8 rows per CTA at small batch; several passes per CTA once the grid is full.
+  int rows = kHeadRows;
+  if (B > kHeadRows * 148 * 2) rows = ceil_div(ceil_div(B, 148 * 2), kHeadRows) * kHeadRows;
   dense_xent_head_kernel<<<ceil_div(B, rows), 256, smem, static_cast<cudaStream_t>(stream)>>>(
-      h, w, bias, labels, logits_out, dh, dw, db, metrics, B, K, C, grad_scale, relu_mask, rows);
+      h, w, bias, labels, logits_out, dh, dw, db, dh_colsum, metrics, B, K, C, grad_scale, relu_mask, rows);
   count_launch();
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;

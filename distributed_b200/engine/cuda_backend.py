@@ -6,6 +6,8 @@ Every callable launches on the *current* torch stream, so the executor can captu
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from ..ops import nn
@@ -27,10 +29,14 @@ class CudaBackend:
         return torch.zeros(shape, dtype=dtype, device=self.device)
 
     def supports_fused_head(self, k_in, units):
-        return units <= _HEAD_MAX_C and (2 * k_in * units + _HEAD_MAX_C + 2) * 4 <= _HEAD_SMEM
+        smem = (k_in * units + 16 * k_in + 8 * _HEAD_MAX_C + 16) * 4
+        return units <= _HEAD_MAX_C and k_in * units <= 48 * 256 and k_in <= 2048 and smem <= _HEAD_SMEM
 
     @staticmethod
     def _tc_ok(*dims):
+        # B200DIST_DENSE=simt forces the exact-fp32 CUDA-core GEMM (debugging / bit-level checks)
+        if os.environ.get("B200DIST_DENSE", "") == "simt":
+            return False
         return all(d % 4 == 0 for d in dims)
 
     def describe_conv(self, layer):
@@ -108,8 +114,9 @@ class CudaBackend:
                 nn.relu_bwd(dx, mask, dx)
         return run
 
-    def dense_xent_head(self, h, w, b, labels, dh, dw, db, metrics, scale, relu_mask, logits):
-        return lambda: nn.dense_xent_head(h, w, b, labels, dh, dw, db, metrics, scale, relu_mask, logits)
+    def dense_xent_head(self, h, w, b, labels, dh, dw, db, metrics, scale, relu_mask, logits, dh_colsum=None):
+        return lambda: nn.dense_xent_head(h, w, b, labels, dh, dw, db, metrics, scale, relu_mask, logits,
+                                          dh_colsum)
 
     def softmax_xent(self, logits, labels, dlogits, metrics, scale):
         return lambda: nn.softmax_xent(logits, labels, dlogits, metrics, scale)

@@ -56,6 +56,11 @@ def lower(layers, batch: int, be, layout: ArenaLayout, params, grads, x_in, labe
         b = layout.view(flat, sl[1]) if len(sl) > 1 else None
         return k, b
 
+    def _fuses_head(layer, is_last, k_in, units):
+        return (training and is_last and layer.activation is None and layer.use_bias
+                and getattr(be, "supports_conv_c1_pool", False) and be.supports_fused_head(k_in, units))
+
+    pending_bias_grad = None
     # ---- forward walk --------------------------------------------------------------
     cur, d_cur = x_in, None             # activation and its gradient buffer (None: no grad needed)
     cur_post_relu = False               # True: gradient w.r.t. `cur` must be masked by cur > 0
@@ -132,13 +137,13 @@ def lower(layers, batch: int, be, layout: ArenaLayout, params, grads, x_in, labe
             w, b = pview(params, i)
             dw, db = pview(grads, i)
             k_in, units = w.shape
-            fuse_head = (training and is_last and layer.activation is None and b is not None
-                         and be.supports_fused_head(k_in, units))
+            fuse_head = _fuses_head(layer, is_last, k_in, units)
             if fuse_head:
                 logits = be.alloc((batch, units))
                 prog.logits = logits
                 stage = be.dense_xent_head(cur, w, b, labels, d_cur, dw, db, metrics, grad_scale,
-                                           cur_post_relu, logits)
+                                           cur_post_relu, logits, dh_colsum=pending_bias_grad)
+                pending_bias_grad = None
                 # forward and backward of the head are one kernel; it runs at the fwd/bwd seam
                 prog.forward.append(stage)
                 bwd_stages.append([])
@@ -151,7 +156,13 @@ def lower(layers, batch: int, be, layout: ArenaLayout, params, grads, x_in, labe
             relu = layer.activation == "relu"
             prog.forward.append(be.dense_fwd(cur, w, b, y, relu))
             if training:
-                stage = [be.dense_wgrad(cur, dy, dw, db)]
+                # If the fused head consumes this layer's output it also produces this layer's
+                # bias gradient (column sums of dy), so no separate reduction kernel is needed.
+                head_takes_bias = (db is not None and isinstance(nxt, L.Dense) and i + 1 == n - 1
+                                   and _fuses_head(nxt, True, units, nxt.units))
+                if head_takes_bias:
+                    pending_bias_grad = db
+                stage = [be.dense_wgrad(cur, dy, dw, None if head_takes_bias else db)]
                 if d_cur is not None:
                     stage.append(be.dense_dgrad(dy, w, d_cur, mask=cur if cur_post_relu else None))
                 bwd_stages.append(stage)

@@ -22,7 +22,7 @@ def _lib():
         vp, i, f, sz, i64 = C.c_void_p, C.c_int, C.c_float, C.c_size_t, C.c_int64
         lib.b2d_conv_c1_pool_fwd.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, i, vp]
         lib.b2d_conv_c1_pool_bwd.argtypes = [vp, vp, vp, vp, vp, i, i, i, i, i, vp]
-        lib.b2d_dense_xent_head.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, f, i, vp]
+        lib.b2d_dense_xent_head.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, f, i, vp]
         lib.b2d_softmax_xent.argtypes = [vp, vp, vp, vp, i, i, f, vp]
         lib.b2d_maxpool2_fwd.argtypes = [vp, vp, vp, i, i, i, i, vp]
         lib.b2d_maxpool2_bwd.argtypes = [vp, vp, vp, vp, i, i, i, i, i, vp]
@@ -63,12 +63,16 @@ def conv_c1_pool_bwd(x, dy, code, dw, db):
              "conv_c1_pool_bwd")
 
 
-def dense_xent_head(h, w, b, labels, dh, dw, db, metrics, grad_scale, relu_mask, logits=None):
-    """Dense(C<=32) + softmax cross-entropy + every gradient of both, one kernel."""
+def dense_xent_head(h, w, b, labels, dh, dw, db, metrics, grad_scale, relu_mask, logits=None,
+                    dh_colsum=None):
+    """Dense(C<=32) + softmax cross-entropy + every gradient of both, one kernel.
+
+    ``dh_colsum`` (optional, [K]) additionally accumulates the column sums of ``dh`` — the bias
+    gradient of the layer that produced ``h``."""
     B, K = h.shape
     Cc = w.shape[1]
     nl.check(_lib().b2d_dense_xent_head(_p(h), _p(w), _p(b), _p(labels), _p(logits), _p(dh), _p(dw),
-                                        _p(db), _p(metrics), B, K, Cc, float(grad_scale),
+                                        _p(db), _p(dh_colsum), _p(metrics), B, K, Cc, float(grad_scale),
                                         int(relu_mask), _s()), "dense_xent_head")
 
 

@@ -1,0 +1,199 @@
+"""SymmComm: the GPU communicator — fused all-reduce + average + SGD over NVLink peer memory.
+
+Each replica owns one block of *symmetric memory* (csrc/runtime/symm.cpp): weight arena,
+gradient arena and signal pads at the same offsets on every GPU, with every peer's block
+mapped into every process.  The per-step update is one kernel (csrc/cuda/allreduce.cu) that
+reads the peers' gradients and writes the peers' weights directly through NVSwitch — one-shot,
+two-shot or NVLS multicast, chosen by message size — and that is captured into the step's CUDA
+graph.  No NCCL call exists on this path; torch.distributed (gloo) is used only as the control
+plane (barriers around set-up, replica-consistency checks).
+
+This replaces the reference's "Collective batch_all_reduce: 6 all-reduces" + 4 metric
+all-reduces + optimizer step per iteration (README.md:403-407, 302).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+
+from .._native import cuda_lib as nl
+
+MAX_RANKS = 8
+ALGOS = {"oneshot": 0, "one_shot": 0, "twoshot": 1, "two_shot": 1, "nvls": 2, "auto": -1}
+ALGO_NAMES = {0: "one-shot", 1: "two-shot", 2: "NVLS multicast"}
+
+_VP8 = C.c_void_p * MAX_RANKS
+
+
+class AllreduceDesc(C.Structure):
+    _fields_ = [("w", _VP8), ("g", _VP8), ("sig", _VP8), ("epoch", _VP8), ("out", _VP8),
+                ("w_mc", C.c_void_p), ("g_mc", C.c_void_p),
+                ("n_params", C.c_int64), ("n_total", C.c_int64), ("lr", C.c_float),
+                ("rank", C.c_int), ("world", C.c_int), ("algo", C.c_int), ("emulate", C.c_int),
+                ("plain", C.c_int), ("blocks", C.c_int)]
+
+
+def _declare(lib):
+    if getattr(lib, "_symm_declared", False):
+        return
+    vp, i, sz = C.c_void_p, C.c_int, C.c_size_t
+    lib.b2d_symm_create.argtypes = [C.POINTER(vp), C.c_char_p, i, i, i, sz, C.c_double]
+    lib.b2d_symm_multicast_phase1.argtypes = [vp]
+    lib.b2d_symm_multicast_phase2.argtypes = [vp]
+    lib.b2d_symm_ptr.argtypes = [vp, i]
+    lib.b2d_symm_ptr.restype = vp
+    lib.b2d_symm_multicast_ptr.argtypes = [vp]
+    lib.b2d_symm_multicast_ptr.restype = vp
+    lib.b2d_symm_bytes.argtypes = [vp]
+    lib.b2d_symm_bytes.restype = sz
+    lib.b2d_symm_multicast_supported.argtypes = [vp]
+    lib.b2d_symm_destroy.argtypes = [vp]
+    lib.b2d_allreduce_signal_bytes.restype = sz
+    lib.b2d_allreduce_epoch_bytes.restype = sz
+    lib.b2d_allreduce_pick_algo.argtypes = [C.c_int64, i, i]
+    lib.b2d_allreduce_sgd.argtypes = [C.POINTER(AllreduceDesc), vp]
+    lib._symm_declared = True
+
+
+class _Raw:
+    """Zero-copy view of raw device memory for torch.as_tensor."""
+
+    def __init__(self, ptr: int, n: int, typestr: str = "<f4"):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False),
+                                         "version": 3, "strides": None}
+
+
+def _align(n: int, a: int = 256) -> int:
+    return (n + a - 1) // a * a
+
+
+class SymmComm:
+    name = "symm"
+    capturable = True
+
+    def __init__(self, strategy, tag: str, capacity_floats: int, device, timeout_s: float = 120.0):
+        import torch.distributed as dist
+        lib = nl.lib()
+        _declare(lib)
+        self._lib, self._dist = lib, dist
+        self.rank, self.world = strategy.rank, strategy.num_workers
+        if self.world > MAX_RANKS:
+            raise RuntimeError(f"SymmComm supports up to {MAX_RANKS} replicas (one NVSwitch box)")
+        self.device = torch.device(device)
+        self.n = _align(capacity_floats, 64)
+        arena_bytes = self.n * 4
+        self.sig_bytes = int(lib.b2d_allreduce_signal_bytes())
+        self.epoch_bytes = int(lib.b2d_allreduce_epoch_bytes())
+        # layout of the symmetric block (same offsets on every replica)
+        self.off_w = 0
+        self.off_g = _align(arena_bytes, 4096)
+        self.off_sig = self.off_g + _align(arena_bytes, 4096)
+        self.off_epoch = self.off_sig + _align(self.sig_bytes, 4096)
+        total = self.off_epoch + _align(self.epoch_bytes, 4096)
+        h = C.c_void_p()
+        torch.cuda.set_device(self.device)
+        dist.barrier()
+        nl.check(lib.b2d_symm_create(C.byref(h), tag.encode(), self.rank, self.world, self.device.index,
+                                     total, timeout_s), "b2d_symm_create")
+        self._h = h
+        self.base = [int(lib.b2d_symm_ptr(h, p)) for p in range(self.world)]
+        dist.barrier()
+        # NVLS multicast where the fabric exposes it (optional; agreed on by all replicas)
+        self.mc_base = 0
+        self.mc_reason = "disabled by B200DIST_NVLS=0"
+        want = os.environ.get("B200DIST_NVLS", "1") != "0"
+        if want:
+            self.mc_reason = "CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED is 0"
+        ok = torch.tensor([1 if (want and lib.b2d_symm_multicast_supported(h)) else 0])
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok[0]):
+            rc = lib.b2d_symm_multicast_phase1(h)
+            if rc != 0:
+                self.mc_reason = "create/add-device failed: " + lib.b2d_last_error().decode(errors="replace")
+            ok = torch.tensor([1 if rc == 0 else 0])
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if int(ok[0]):
+                rc = lib.b2d_symm_multicast_phase2(h)
+                if rc != 0:
+                    self.mc_reason = "bind/map failed: " + lib.b2d_last_error().decode(errors="replace")
+                ok = torch.tensor([1 if rc == 0 else 0])
+                dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+                if int(ok[0]):
+                    self.mc_base = int(lib.b2d_symm_multicast_ptr(h))
+                    self.mc_reason = "bound"
+            elif rc == 0:
+                self.mc_reason = "a peer failed to set up multicast"
+        self._next = 0
+        mode = os.environ.get("B200DIST_ALLREDUCE", "").lower() or {
+            "ONE_SHOT": "oneshot", "TWO_SHOT": "twoshot", "NVLS": "nvls"}.get(strategy.communication.name, "auto")
+        if mode not in ALGOS:
+            raise ValueError(f"B200DIST_ALLREDUCE must be one of {sorted(ALGOS)}")
+        self.algo = ALGOS[mode]
+        if self.algo == 2 and not self.mc_base:
+            raise RuntimeError(f"NVLS all-reduce requested but multicast is not available on this box ({self.mc_reason})")
+        resolved = self.algo if self.algo >= 0 else int(
+            lib.b2d_allreduce_pick_algo(self.n, self.world, 1 if self.mc_base else 0))
+        self.algo_resolved = resolved
+        self.description = (f"fused peer-memory all-reduce+SGD over NVLink ({ALGO_NAMES[resolved]}, "
+                            f"{self.world} GPUs, multicast {'bound' if self.mc_base else 'unavailable: ' + self.mc_reason})")
+
+    # -- symmetric tensors -------------------------------------------------------------
+    def _tensor(self, off_bytes: int, n: int, typestr="<f4"):
+        t = torch.as_tensor(_Raw(self.base[self.rank] + off_bytes, n, typestr), device=self.device)
+        t._b2d_owner = self       # the mapping lives as long as the communicator
+        return t
+
+    def alloc(self, n, be):
+        """First call: weight arena; second call: gradient arena (both symmetric)."""
+        assert n <= self.n, "arena larger than the communicator's capacity"
+        off = (self.off_w, self.off_g)[self._next]
+        self._next += 1
+        return self._tensor(off, n)
+
+    def make_update(self, be, params, grads, n_params, lr):
+        d = AllreduceDesc()
+        for p in range(self.world):
+            d.w[p] = self.base[p] + self.off_w
+            d.g[p] = self.base[p] + self.off_g
+            d.sig[p] = self.base[p] + self.off_sig
+            d.epoch[p] = self.base[p] + self.off_epoch
+        if self.mc_base:
+            d.w_mc = self.mc_base + self.off_w
+            d.g_mc = self.mc_base + self.off_g
+        n_total = params.numel()
+        assert params.data_ptr() == d.w[self.rank] and grads.data_ptr() == d.g[self.rank]
+        assert n_total % 4 == 0 and n_params % 4 == 0
+        d.n_params, d.n_total, d.lr = n_params, n_total, float(lr)
+        d.rank, d.world, d.algo, d.emulate, d.plain, d.blocks = self.rank, self.world, self.algo, 0, 0, 0
+        self._descs = getattr(self, "_descs", []) + [d]
+        lib = self._lib
+
+        def run():
+            nl.check(lib.b2d_allreduce_sgd(C.byref(d), torch.cuda.current_stream().cuda_stream),
+                     "b2d_allreduce_sgd")
+        return run
+
+    # -- control plane ------------------------------------------------------------------
+    def barrier(self):
+        torch.cuda.synchronize(self.device)
+        self._dist.barrier()
+
+    def all_equal(self, tensor) -> bool:
+        torch.cuda.synchronize(self.device)
+        flat = tensor.detach().reshape(-1).float().cpu().contiguous()
+        mx, mn = flat.clone(), flat.clone()
+        self._dist.all_reduce(mx, op=self._dist.ReduceOp.MAX)
+        self._dist.all_reduce(mn, op=self._dist.ReduceOp.MIN)
+        return bool(torch.equal(mx, mn))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            try:
+                torch.cuda.synchronize(self.device)
+                self._dist.barrier()
+            except Exception:
+                pass
+            self._lib.b2d_symm_destroy(self._h)
+            self._h = None

@@ -16,24 +16,42 @@ def _fit(backend, x, y, epochs=2, steps=5, lr=0.05, model="mnist"):
     return m, h
 
 
-def test_cuda_fit_matches_cpu_backend():
+def test_cuda_fit_matches_cpu_backend_exact_fp32(monkeypatch):
+    """With the dense layers forced onto the fp32 CUDA-core GEMM, every other kernel of the step
+    (fused conv/pool both ways, fused head, SGD, graph replay) must track the CPU oracle tightly."""
+    monkeypatch.setenv("B200DIST_DENSE", "simt")
+    rng = np.random.default_rng(0)
+    x = rng.random((640, 28, 28, 1)).astype(np.float32)
+    y = rng.integers(0, 10, 640)
+    mc, hc = _fit("cpu", x, y)
+    mg, hg = _fit("cuda", x, y)
+    assert mg._trainer.use_graph
+    assert hc.history["loss"] == pytest.approx(hg.history["loss"], abs=1e-5)
+    assert hc.history["accuracy"] == pytest.approx(hg.history["accuracy"], abs=1e-6)
+    for wc, wg, name in zip(mc.get_weights(), mg.get_weights(), mc.weight_names()):
+        assert np.allclose(wc, wg, atol=2e-6), (name, np.abs(wc - wg).max())
+
+
+def test_cuda_fit_tcgen05_tracks_cpu_backend():
+    """Default path (tf32 tensor-core dense layers).  tf32 rounding flips a few near-zero ReLU
+    pre-activations, which moves whole gradient terms, so weights are compared in aggregate;
+    exactness of each kernel is covered by the per-kernel tests and the fp32 variant above."""
     rng = np.random.default_rng(0)
     x = rng.random((640, 28, 28, 1)).astype(np.float32)
     y = rng.integers(0, 10, 640)
     mc, hc = _fit("cpu", x, y)
     mg, hg = _fit("cuda", x, y)
     assert mg._trainer.use_graph and mg._trainer.kernels_per_step <= 8
+    assert "tcgen05" in " ".join(mg._trainer.describe())
     for a, b in zip(hc.history["loss"], hg.history["loss"]):
         assert abs(a - b) < 2e-3, (hc.history, hg.history)
-    # near-tied random-init logits flip under tf32 rounding: allow a few of the 320 samples
     assert hc.history["accuracy"] == pytest.approx(hg.history["accuracy"], abs=8 / 320)
     import distributed_b200 as tf
     w_init = tf.models.mnist_cnn().get_weights()
     for wi, wc, wg, name in zip(w_init, mc.get_weights(), mg.get_weights(), mc.weight_names()):
-        step = np.abs(wc - wi).max()            # how far training moved this tensor
-        # tf32 rounding flips a few near-zero ReLU pre-activations, which moves whole gradient
-        # terms; exactness is covered by the per-kernel tests, this is an end-to-end sanity bound
-        assert np.abs(wc - wg).max() <= 0.25 * step + 1e-6, (name, np.abs(wc - wg).max(), step)
+        upd_c, upd_g = wc - wi, wg - wi
+        rel = np.linalg.norm(upd_g - upd_c) / max(np.linalg.norm(upd_c), 1e-12)
+        assert rel < 0.3, (name, rel)
 
 
 def test_cuda_generic_path_scaled_cnn_matches_cpu():

@@ -44,7 +44,7 @@ def test_conv_c1_pool_forward_and_backward(N, H, W, Co, KS):
     assert torch.allclose(db, b.grad, atol=2e-3 * b.grad.abs().max().item(), rtol=1e-3)
 
 
-@pytest.mark.parametrize("B,K,C,relu_mask", [(64, 64, 10, True), (1024, 1024, 10, True), (37, 50, 7, False)])
+@pytest.mark.parametrize("B,K,C,relu_mask", [(64, 64, 10, True), (1024, 1024, 10, True), (37, 50, 7, False), (5000, 256, 32, True)])
 def test_dense_xent_head_matches_autograd(B, K, C, relu_mask):
     from distributed_b200.ops import nn
     g = _gen(B + K)
@@ -60,8 +60,10 @@ def test_dense_xent_head_matches_autograd(B, K, C, relu_mask):
     dw, db = torch.zeros_like(w), torch.zeros_like(b)
     metrics = torch.zeros(4, device="cuda")
     logits = torch.empty((B, C), device="cuda")
+    dprev = torch.ones(K, device="cuda")
     nn.dense_xent_head(h.detach().contiguous(), w.detach(), b.detach(), labels, dh, dw, db, metrics,
-                       1.0 / B, relu_mask, logits)
+                       1.0 / B, relu_mask, logits, dh_colsum=dprev)
+    assert torch.allclose(dprev, pre.grad.sum(0) + 1, atol=1e-5, rtol=1e-3)
     assert torch.allclose(logits, logits_ref, atol=1e-3, rtol=1e-3)
     assert abs(metrics[0].item() - loss.item()) < 1e-3 * abs(loss.item())
     assert metrics[1].item() == (logits_ref.argmax(1) == labels).sum().item()
