@@ -27,7 +27,7 @@ namespace b2d {
 
 constexpr int kMaxRanks = 8;
 constexpr int kArThreads = 512;
-constexpr int kMaxArBlocks = 64;  // signal pad: kMaxArBlocks * kMaxRanks words per rank
+constexpr int kMaxArBlocks = 144;  // signal pad: kMaxArBlocks * kMaxRanks words per rank
 
 struct ArArgs {
   float* w[kMaxRanks];        // weight arenas (peer-mapped); w[rank] is local
@@ -91,38 +91,76 @@ __global__ void __launch_bounds__(kArThreads) allreduce_sgd_kernel(const ArArgs 
   const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
 
+  pdl_wait();     // this replica's backward has finished writing its gradients
+  pdl_trigger();
   rank_barrier(a, rank, &s_epoch);  // A: every replica's gradients are complete
 
+  // Peer loads have ~2 us latency: keep kUnroll independent 16-byte loads per peer in flight per
+  // thread (all loads of a batch are issued before the first use).
+  constexpr int kUnroll = 4;
   if (ALGO == kOneShot) {
     float4* wl = reinterpret_cast<float4*>(a.plain ? a.out[rank] : a.w[rank]);
-    for (long long i = t0; i < a.n_total4; i += stride) {
-      float4 acc = zero;
+    for (long long i0 = t0; i0 < a.n_total4; i0 += stride * kUnroll) {
+      float4 acc[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) acc[u] = zero;
 #pragma unroll 1
-      for (int p = 0; p < world; ++p)  // fixed rank order: identical bits on every replica
-        acc = f4_add(acc, ld_nc_na_f4(reinterpret_cast<const float4*>(a.g[p]) + i));
-      wl[i] = a.plain ? acc : apply_update(wl[i], acc, i < a.n_params4, a.scale);
+      for (int p = 0; p < world; ++p) {  // fixed rank order: identical bits on every replica
+        float4 v[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+          const long long i = i0 + u * stride;
+          v[u] = i < a.n_total4 ? ld_nc_na_f4(reinterpret_cast<const float4*>(a.g[p]) + i) : zero;
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) acc[u] = f4_add(acc[u], v[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long i = i0 + u * stride;
+        if (i < a.n_total4) wl[i] = a.plain ? acc[u] : apply_update(wl[i], acc[u], i < a.n_params4, a.scale);
+      }
     }
   } else {
     const long long per = (a.n_total4 + world - 1) / world;
     const long long s0 = min(a.n_total4, per * rank), s1 = min(a.n_total4, s0 + per);
-    for (long long i = s0 + t0; i < s1; i += stride) {
-      float4 acc;
+    for (long long i0 = s0 + t0; i0 < s1; i0 += stride * kUnroll) {
+      float4 acc[kUnroll];
       if (ALGO == kNvls) {
-        acc = multimem_ld_reduce_add_f4(reinterpret_cast<const float4*>(a.g_mc) + i);
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+          const long long i = i0 + u * stride;
+          acc[u] = i < s1 ? multimem_ld_reduce_add_f4(reinterpret_cast<const float4*>(a.g_mc) + i) : zero;
+        }
       } else {
-        acc = zero;
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) acc[u] = zero;
 #pragma unroll 1
-        for (int p = 0; p < world; ++p)
-          acc = f4_add(acc, ld_nc_na_f4(reinterpret_cast<const float4*>(a.g[p]) + i));
+        for (int p = 0; p < world; ++p) {
+          float4 v[kUnroll];
+#pragma unroll
+          for (int u = 0; u < kUnroll; ++u) {
+            const long long i = i0 + u * stride;
+            v[u] = i < s1 ? ld_nc_na_f4(reinterpret_cast<const float4*>(a.g[p]) + i) : zero;
+          }
+#pragma unroll
+          for (int u = 0; u < kUnroll; ++u) acc[u] = f4_add(acc[u], v[u]);
+        }
       }
-      float4 v = acc;
-      if (!a.plain) v = apply_update(reinterpret_cast<const float4*>(a.w[rank])[i], acc, i < a.n_params4, a.scale);
-      if (ALGO == kNvls) {
-        multimem_st_f4(reinterpret_cast<float4*>(a.plain ? a.g_mc : a.w_mc) + i, v);
-      } else {
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long i = i0 + u * stride;
+        if (i >= s1) continue;
+        float4 v = acc[u];
+        if (!a.plain)
+          v = apply_update(reinterpret_cast<const float4*>(a.w[rank])[i], acc[u], i < a.n_params4, a.scale);
+        if (ALGO == kNvls) {
+          multimem_st_f4(reinterpret_cast<float4*>(a.plain ? a.g_mc : a.w_mc) + i, v);
+        } else {
 #pragma unroll 1
-        for (int p = 0; p < world; ++p)
-          st_na_f4(reinterpret_cast<float4*>(a.plain ? a.g[p] : a.w[p]) + i, v);
+          for (int p = 0; p < world; ++p)
+            st_na_f4(reinterpret_cast<float4*>(a.plain ? a.g[p] : a.w[p]) + i, v);
+        }
       }
     }
   }
@@ -205,7 +243,7 @@ extern "C" int b2d_allreduce_sgd(const b2d_allreduce_desc* d, void* stream) {
   const long long work4 = algo == kOneShot ? a.n_total4 : (a.n_total4 + d->world - 1) / d->world;
   int blocks = d->blocks > 0 ? d->blocks
                              : static_cast<int>(std::min<long long>(
-                                   kMaxArBlocks, std::max<long long>(1, (work4 + kArThreads * 4 - 1) / (kArThreads * 4))));
+                                   kMaxArBlocks, std::max<long long>(1, (work4 + kArThreads * 4 - 1) / (kArThreads * 4))));  // ~4 float4 per thread
   blocks = std::min(blocks, kMaxArBlocks);
   void (*kern)(const ArArgs) = algo == kOneShot  ? allreduce_sgd_kernel<kOneShot>
                                : algo == kTwoShot ? allreduce_sgd_kernel<kTwoShot>
@@ -216,10 +254,9 @@ extern "C" int b2d_allreduce_sgd(const b2d_allreduce_desc* d, void* stream) {
     void* params[] = {&a};
     B2D_CUDA_CHECK(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(kern), dim3(blocks, d->world),
                                                dim3(kArThreads), params, 0, st));
+    count_launch();
   } else {
-    kern<<<blocks, kArThreads, 0, st>>>(a);
-    B2D_CUDA_CHECK(cudaGetLastError());
+    B2D_CUDA_CHECK(launch_pdl(kern, dim3(blocks), dim3(kArThreads), 0, st, a));
   }
-  count_launch();
   return B2D_OK;
 }

@@ -32,9 +32,27 @@ enum GemmFlags : int {
   kFlagOutBf16 = 8,
 };
 
+// Implicit-GEMM convolution view of the A operand (stride-1 NHWC convolutions): the M tile is a
+// box (n_t images x ho_t rows x wo_t columns) of output pixels, and k-block kb = (tap, channel
+// chunk) loads the input box shifted by that filter tap with ONE 4-D TMA copy — out-of-range
+// pixels (zero padding) are filled by the TMA unit.  No im2col buffer exists anywhere.
+struct ConvGeom {
+  int enabled;
+  int kw, c_chunks;        // filter width; 128-byte channel chunks per tap
+  int wo_t, ho_t, n_t;     // output-pixel box of one M tile (wo_t * ho_t * n_t <= 128 rows)
+  int rows_used;           // wo_t * ho_t * n_t
+  int OH, OW, N_img;       // output geometry
+  int tiles_h;             // M tiles per image (when n_t == 1)
+  int w_base, h_base;      // input coordinate of tap (0,0) for output pixel (0,0)
+  int tap_sign;            // +1 forward (in = out + tap - pad), -1 dgrad (in = out + pad - tap)
+  int b_rows_per_tap;      // K-major B (dgrad): rows of the weight matrix per tap (= C_in)
+};
+
 struct GemmArgs {
   CUtensorMap tmA;
   CUtensorMap tmB;
+  ConvGeom cv;
+  int stages;
   void* D;
   const float* bias;
   const float* mask;
@@ -111,7 +129,8 @@ struct GemmCfg {
 template <MmaKind KIND, bool A_MN, bool B_MN, int BLOCK_N>
 __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const __grid_constant__ GemmArgs args) {
   using Cfg = GemmCfg<KIND, A_MN, B_MN, BLOCK_N>;
-  constexpr int STAGES = Cfg::STAGES;
+  const int STAGES = args.stages;  // ring depth chosen on the host (<= Cfg::STAGES): short K loops
+                                   // ask for little shared memory
   constexpr int STAGE_BYTES = Cfg::STAGE_BYTES;
   constexpr int BLOCK_K = Cfg::BLOCK_K;
 
@@ -131,6 +150,17 @@ __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const __grid_constant__
   const int kb_begin = blockIdx.z * args.kb_per_split;
   const int kb_end = min(args.kb_total, kb_begin + args.kb_per_split);
   const int num_kb = kb_end - kb_begin;  // >= 1 by construction on the host
+  // convolution view: first image / first output row of this M tile
+  const ConvGeom& cv = args.cv;
+  int cv_n0 = 0, cv_oh0 = 0;
+  if (cv.enabled) {
+    if (cv.n_t == 1) {
+      cv_n0 = blockIdx.x / cv.tiles_h;
+      cv_oh0 = (blockIdx.x % cv.tiles_h) * cv.ho_t;
+    } else {
+      cv_n0 = blockIdx.x * cv.n_t;
+    }
+  }
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&args.tmA);
@@ -149,6 +179,10 @@ __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const __grid_constant__
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // Everything above (barrier init, TMEM allocation, descriptor prefetch) overlapped with the
+  // tail of the previous kernel; from here on its results are needed.
+  pdl_wait();
+  pdl_trigger();
 
   if (warp == 0) {
     // ===== TMA producer =====
@@ -157,12 +191,21 @@ __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const __grid_constant__
         const int stage = i % STAGES;
         const uint32_t phase = (i / STAGES) & 1;
         mbar_wait(&empty_bar[stage], phase ^ 1);
-        mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
         uint8_t* sa = smem + stage * STAGE_BYTES;
         uint8_t* sb = sa + kABytes;
-        const int k0 = (kb_begin + i) * BLOCK_K;
+        const int kb = kb_begin + i;
+        const int k0 = kb * BLOCK_K;
+        int tap = 0, cc = 0;
+        if (cv.enabled) tap = kb / cv.c_chunks, cc = kb - tap * cv.c_chunks;
+        mbar_expect_tx(&full_bar[stage], cv.enabled ? cv.rows_used * 128 + Cfg::B_BYTES : STAGE_BYTES);
         if constexpr (!A_MN) {
-          tma_load_2d(sa, &args.tmA, &full_bar[stage], k0, m0);
+          if (cv.enabled) {
+            const int r = tap / cv.kw, sx = tap - r * cv.kw;
+            tma_load_4d(sa, &args.tmA, &full_bar[stage], cc * BLOCK_K, cv.w_base + cv.tap_sign * sx,
+                        cv_oh0 + cv.h_base + cv.tap_sign * r, cv_n0);
+          } else {
+            tma_load_2d(sa, &args.tmA, &full_bar[stage], k0, m0);
+          }
         } else {
 #pragma unroll
           for (int a = 0; a < kBlockM / Cfg::ATOM_E; ++a)
@@ -170,7 +213,10 @@ __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const __grid_constant__
                         k0);
         }
         if constexpr (!B_MN) {
-          tma_load_2d(sb, &args.tmB, &full_bar[stage], k0, n0);
+          if (cv.enabled)  // dgrad: weights [taps * C_in rows][C_out], K = C_out chunk of this tap
+            tma_load_2d(sb, &args.tmB, &full_bar[stage], cc * BLOCK_K, tap * cv.b_rows_per_tap + n0);
+          else
+            tma_load_2d(sb, &args.tmB, &full_bar[stage], k0, n0);
         } else {
 #pragma unroll
           for (int a = 0; a < (BLOCK_N + Cfg::ATOM_E - 1) / Cfg::ATOM_E; ++a)
@@ -209,8 +255,16 @@ __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const __grid_constant__
   } else if (warp >= 4) {
     // ===== epilogue: 4 warps, warp q owns TMEM lanes [32q, 32q+32) =====
     const int q = warp - 4;
-    const int row = m0 + q * 32 + lane;
-    const bool row_ok = row < args.M;
+    int row = m0 + q * 32 + lane;
+    bool row_ok = row < args.M;
+    if (cv.enabled) {  // tile-local pixel index -> (image, out row, out column) -> output matrix row
+      const int m = q * 32 + lane;
+      const int w_i = m % cv.wo_t, t = m / cv.wo_t;
+      const int h_i = t % cv.ho_t, n_i = t / cv.ho_t;
+      const int oh = cv_oh0 + h_i, n = cv_n0 + n_i;
+      row_ok = m < cv.rows_used && oh < cv.OH && n < cv.N_img;
+      row = (n * cv.OH + oh) * cv.OW + w_i;
+    }
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
     const bool finalize = (args.flags & kFlagFinalize) != 0;
@@ -346,7 +400,10 @@ static int resolve(const b2d_gemm_desc& d, b2d_gemm_geometry* g) {
   const int per = ceil_div(g->k_blocks, splits);
   g->splits = ceil_div(g->k_blocks, per);
   const int stage_bytes = kABytes + g->block_n * 128;
-  g->stages = min(kMaxStages, kSmemBudget / stage_bytes);
+  // Ring depth: never deeper than the K loop of one CTA (short loops keep the kernel's
+  // shared-memory footprint small), never deeper than fits.
+  const int per_cta = ceil_div(g->k_blocks, g->splits);
+  g->stages = max(2, min(min(kMaxStages, kSmemBudget / stage_bytes), per_cta));
   g->smem_bytes = g->stages * stage_bytes + 1024 + 256;
   return B2D_OK;
 }
@@ -359,7 +416,8 @@ struct b2d_gemm_plan {
   GemmArgs args;
   b2d_gemm_geometry geo;
   void (*kernel)(const GemmArgs);
-  int smem_bytes;
+  int smem_bytes;     // maximum the kernel instantiation may ask for (function attribute)
+  int launch_smem;    // what this plan actually launches with (ring depth of this problem)
 };
 
 template <MmaKind KIND, bool A_MN, bool B_MN>
@@ -452,6 +510,8 @@ extern "C" int b2d_gemm_plan_create(const b2d_gemm_desc* desc, b2d_gemm_plan** o
   a.kb_total = g.k_blocks, a.kb_per_split = ceil_div(g.k_blocks, g.splits), a.splits = g.splits;
   a.flags = (d.relu ? kFlagRelu : 0) | (d.accumulate ? kFlagAccumulate : 0) |
             (finalize ? kFlagFinalize : 0) | (d.out_dtype == B2D_BF16 ? kFlagOutBf16 : 0);
+  a.stages = g.stages;
+  p->launch_smem = g.smem_bytes;
   p->geo = g;
   if (d.dtype == B2D_F32)
     select_major<MmaKind::TF32>(d.a_mn_major, d.b_mn_major, g.block_n, &p->kernel, &p->smem_bytes);
@@ -471,13 +531,393 @@ extern "C" int b2d_gemm_plan_create(const b2d_gemm_desc* desc, b2d_gemm_plan** o
 extern "C" int b2d_gemm_plan_run(const b2d_gemm_plan* p, void* stream) {
   B2D_REQUIRE(p != nullptr, "gemm_plan_run: null plan");
   const dim3 grid(p->geo.m_tiles, p->geo.n_tiles, p->geo.splits);
-  p->kernel<<<grid, 256, p->smem_bytes, static_cast<cudaStream_t>(stream)>>>(p->args);
-  count_launch();
-  B2D_CUDA_CHECK(cudaGetLastError());
+  B2D_CUDA_CHECK(launch_pdl(p->kernel, grid, dim3(256), p->launch_smem, static_cast<cudaStream_t>(stream), p->args));
   return B2D_OK;
 }
 
 extern "C" void b2d_gemm_plan_destroy(b2d_gemm_plan* p) { delete p; }
+
+// ---------------------------------------------------------------------------------------
+// Implicit-GEMM convolution plans (stride 1, NHWC x HWIO) on the same kernel.       [W1, W3]
+//   forward : y[n,oh,ow,:]  = act( sum_{r,s} x[n,oh+r-ph,ow+s-pw,:] . W[r,s,:,:] + b )
+//             A = x through a 4-D TMA box per filter tap, B = W viewed [KH*KW*Ci][Co] (MN-major)
+//   dgrad   : dx[n,ih,iw,:] = sum_{r,s} dy[n,ih+ph-r,iw+pw-s,:] . W[r,s,:,:]^T  (x mask)
+//             A = dy through the mirrored taps, B = the same weight matrix read K-major
+// Reference: Conv2D layers (README.md:293); the reference ships no kernels.
+// ---------------------------------------------------------------------------------------
+typedef struct b2d_conv_desc {
+  int dtype;      // b2d_dtype of activations and weights
+  int out_dtype;  // b2d_dtype of the output
+  int N, H, W, Ci, Co, KH, KW, pad_h, pad_w;
+  const void* x;      // forward: input [N,H,W,Ci]      dgrad: OUTPUT dx [N,H,W,Ci]
+  const void* w;      // weights [KH,KW,Ci,Co]
+  void* y;            // forward: output [N,OH,OW,Co]    dgrad: INPUT dy [N,OH,OW,Co]
+  const float* bias;  // forward only, optional
+  const float* mask;  // optional fp32 tensor shaped like the output: zero where mask <= 0
+  int relu;
+} b2d_conv_desc;
+
+static int encode_tmap_4d(CUtensorMap* tm, int dtype, const void* base, uint64_t C, uint64_t W,
+                          uint64_t H, uint64_t N, uint32_t box_c, uint32_t box_w, uint32_t box_h,
+                          uint32_t box_n, bool mn_major = false) {
+  static EncodeTiledFn fn = reinterpret_cast<EncodeTiledFn>(driver_fn("cuTensorMapEncodeTiled"));
+  if (fn == nullptr) return B2D_ERR_UNSUPPORTED;
+  const uint64_t es = dtype == B2D_F32 ? 4 : 2;
+  const cuuint64_t dims[4] = {C, W, H, N};
+  const cuuint64_t strides[3] = {C * es, W * C * es, H * W * C * es};
+  const cuuint32_t box[4] = {box_c, box_w, box_h, box_n};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  const CUtensorMapDataType dt =
+      dtype == B2D_F32 ? CU_TENSOR_MAP_DATA_TYPE_TFLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  // channels-as-MN (wgrad) fp32 tiles need the 32-byte-chunk swizzle, like the 2-D MN-major maps
+  const CUtensorMapSwizzle sw = (mn_major && dtype == B2D_F32) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
+                                                               : CU_TENSOR_MAP_SWIZZLE_128B;
+  CUresult r = fn(tm, dt, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled(4d) failed: CUresult %d (C=%llu W=%llu H=%llu N=%llu box=%u,%u,%u,%u)",
+              (int)r, (unsigned long long)C, (unsigned long long)W, (unsigned long long)H,
+              (unsigned long long)N, box_c, box_w, box_h, box_n);
+    return B2D_ERR_CUDA;
+  }
+  return B2D_OK;
+}
+
+// 1 if the tensor-core path can take this convolution (otherwise use the direct kernels).
+extern "C" int b2d_conv_tc_supported(const b2d_conv_desc* d, int dgrad) {
+  if (d == nullptr) return 0;
+  const int es = d->dtype == B2D_F32 ? 4 : 2;
+  const int OH = d->H + 2 * d->pad_h - d->KH + 1, OW = d->W + 2 * d->pad_w - d->KW + 1;
+  const int k_ch = dgrad ? d->Co : d->Ci;       // reduction channels
+  const int n_ch = dgrad ? d->Ci : d->Co;       // output channels
+  const int out_w = dgrad ? d->W : OW;
+  if (OH <= 0 || OW <= 0) return 0;
+  if ((k_ch * es) % 128 != 0) return 0;          // whole 128-byte channel chunks per tap
+  if (n_ch % 4 != 0 || (n_ch * es) % 16 != 0) return 0;
+  if (out_w > 128 || out_w < 1) return 0;        // one output row must fit the 128-row M tile
+  return 1;
+}
+
+static int conv_plan_create(const b2d_conv_desc& d, bool dgrad, b2d_gemm_plan** out) {
+  B2D_REQUIRE(b2d_conv_tc_supported(&d, dgrad), "conv: shape not supported by the tensor-core path");
+  B2D_REQUIRE(d.x && d.w && d.y, "conv: null tensor pointer");
+  const int es = d.dtype == B2D_F32 ? 4 : 2;
+  const int block_k = 128 / es;
+  const int OH = d.H + 2 * d.pad_h - d.KH + 1, OW = d.W + 2 * d.pad_w - d.KW + 1;
+  // geometry of the *output* of this GEMM and of the tensor the taps slide over
+  const int out_h = dgrad ? d.H : OH, out_w = dgrad ? d.W : OW;
+  const int in_h = dgrad ? OH : d.H, in_w = dgrad ? OW : d.W;
+  const int k_ch = dgrad ? d.Co : d.Ci, n_ch = dgrad ? d.Ci : d.Co;
+  const void* in_ptr = dgrad ? d.y : d.x;
+  void* out_ptr = dgrad ? const_cast<void*>(d.x) : d.y;
+
+  b2d_gemm_desc gd{};
+  gd.dtype = d.dtype, gd.out_dtype = d.out_dtype;
+  gd.M = d.N * out_h * out_w, gd.N = n_ch, gd.K = d.KH * d.KW * k_ch;
+  gd.lda = k_ch, gd.ldb = dgrad ? d.Co : d.Co, gd.ldd = n_ch, gd.ldmask = n_ch;
+  gd.b_mn_major = dgrad ? 0 : 1;
+  gd.splits = 1;
+  b2d_gemm_geometry g;
+  int rc = resolve(gd, &g);
+  if (rc != B2D_OK) return rc;
+
+  b2d_gemm_plan* p = new (std::nothrow) b2d_gemm_plan();
+  B2D_REQUIRE(p != nullptr, "conv: out of host memory");
+  ConvGeom& cv = p->args.cv;
+  cv.enabled = 1, cv.kw = d.KW, cv.c_chunks = k_ch / block_k;
+  cv.wo_t = out_w;
+  cv.ho_t = min(out_h, kBlockM / out_w);
+  cv.n_t = 1;
+  if (cv.ho_t >= out_h) {
+    cv.ho_t = out_h;
+    cv.n_t = max(1, min(d.N, kBlockM / (out_w * out_h)));
+  }
+  cv.rows_used = cv.wo_t * cv.ho_t * cv.n_t;
+  cv.OH = out_h, cv.OW = out_w, cv.N_img = d.N;
+  cv.tiles_h = ceil_div(out_h, cv.ho_t);
+  cv.tap_sign = dgrad ? -1 : 1;
+  cv.w_base = dgrad ? d.pad_w : -d.pad_w;
+  cv.h_base = dgrad ? d.pad_h : -d.pad_h;
+  cv.b_rows_per_tap = d.Ci;
+  g.m_tiles = cv.n_t == 1 ? d.N * cv.tiles_h : ceil_div(d.N, cv.n_t);
+
+  rc = encode_tmap_4d(&p->args.tmA, d.dtype, in_ptr, k_ch, in_w, in_h, d.N, block_k, cv.wo_t, cv.ho_t, cv.n_t);
+  if (rc == B2D_OK) {
+    const uint64_t w_rows = (uint64_t)d.KH * d.KW * d.Ci;
+    if (!dgrad)   // MN-major B: dims {Co, rows}, box {one 128-byte atom of Co, BLOCK_K rows}
+      rc = encode_tmap_2d(&p->args.tmB, d.dtype, d.w, d.Co, w_rows, (uint64_t)d.Co * es, block_k, block_k, true);
+    else          // K-major B: dims {Co (K), rows (N = ci)}, box {BLOCK_K, BLOCK_N rows}
+      rc = encode_tmap_2d(&p->args.tmB, d.dtype, d.w, d.Co, w_rows, (uint64_t)d.Co * es, block_k, g.block_n, false);
+  }
+  if (rc != B2D_OK) {
+    delete p;
+    return rc;
+  }
+  GemmArgs& a = p->args;
+  a.D = out_ptr, a.bias = dgrad ? nullptr : d.bias, a.mask = d.mask, a.ws = nullptr, a.counters = nullptr;
+  a.ldd = n_ch, a.ldmask = n_ch, a.ldws = 0;
+  a.M = gd.M, a.N = gd.N, a.K = gd.K;
+  a.kb_total = g.k_blocks, a.kb_per_split = g.k_blocks, a.splits = 1;
+  a.flags = (d.relu ? kFlagRelu : 0) | (d.out_dtype == B2D_BF16 ? kFlagOutBf16 : 0);
+  a.stages = g.stages;
+  p->launch_smem = g.smem_bytes;
+  p->geo = g;
+  if (d.dtype == B2D_F32)
+    select_major<MmaKind::TF32>(false, !dgrad, g.block_n, &p->kernel, &p->smem_bytes);
+  else
+    select_major<MmaKind::F16>(false, !dgrad, g.block_n, &p->kernel, &p->smem_bytes);
+  cudaError_t e = cudaFuncSetAttribute(reinterpret_cast<const void*>(p->kernel),
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem_bytes);
+  if (e != cudaSuccess) {
+    set_error("conv: cudaFuncSetAttribute(smem=%d) failed: %s", p->smem_bytes, cudaGetErrorString(e));
+    delete p;
+    return B2D_ERR_CUDA;
+  }
+  *out = p;
+  return B2D_OK;
+}
+
+extern "C" int b2d_conv_fwd_plan_create(const b2d_conv_desc* d, b2d_gemm_plan** out) {
+  B2D_REQUIRE(d != nullptr && out != nullptr, "conv_fwd_plan_create: null argument");
+  return conv_plan_create(*d, false, out);
+}
+extern "C" int b2d_conv_dgrad_plan_create(const b2d_conv_desc* d, b2d_gemm_plan** out) {
+  B2D_REQUIRE(d != nullptr && out != nullptr, "conv_dgrad_plan_create: null argument");
+  return conv_plan_create(*d, true, out);
+}
+
+// ---------------------------------------------------------------------------------------
+// Convolution filter gradient on tcgen05.                                             [W2]
+//   dW[r,s,ci,co] += sum_{n,oh,ow} x[n,oh+r-ph,ow+s-pw,ci] * dy[n,oh,ow,co]
+// Per filter tap this is a GEMM with the *pixels* as the reduction dimension:
+//   D[co, ci] = sum_pix dy[pix, co] * x_tap[pix, ci]
+// Both operands are MN-major (channels contiguous, pixels along K) and both come straight from
+// the NHWC tensors through 4-D TMA boxes of (ho_t x OW) pixels — the x box shifted by the tap.
+// One CTA = one (tap, co tile, ci tile) x a chunk of pixel boxes; the fp32 accumulator stays
+// in TMEM across the whole chunk and is added to dW with coalesced reductions (the TMEM row is
+// co, which is the contiguous dimension of HWIO).
+// ---------------------------------------------------------------------------------------
+namespace b2d {
+
+struct WgradArgs {
+  CUtensorMap tmDy;  // dims {Co, OW, OH, N}
+  CUtensorMap tmX;   // dims {Ci, W,  H,  N}
+  float* dw;
+  int Ci, Co, KW, pad_h, pad_w;
+  int rows;          // pixels per k-block = OW * ho_t
+  int ho_t, tiles_h; // box height, boxes per image
+  int tiles_total;   // N * tiles_h
+  int tiles_per_cta;
+  int m_tiles, n_tiles;
+  int stages;
+};
+
+template <MmaKind KIND, int BLOCK_N>
+__global__ void __launch_bounds__(256, 1) conv_wgrad_tc_kernel(const __grid_constant__ WgradArgs args) {
+  constexpr int ES = (KIND == MmaKind::TF32) ? 4 : 2;
+  constexpr int ATOM = 128 / ES;          // channels per 128-byte atom
+  constexpr int UMMA_K = 32 / ES;         // pixels per MMA
+  constexpr int A_ATOMS = kBlockM / ATOM;
+  constexpr int B_ATOMS = BLOCK_N / ATOM;
+  constexpr uint32_t MN_LAYOUT = (KIND == MmaKind::TF32) ? kUmmaSw128Base32 : kUmmaSw128;
+  constexpr uint32_t MN_SBO = (KIND == MmaKind::TF32) ? 512 : 1024;
+  constexpr uint32_t IDESC = umma_idesc(KIND == MmaKind::TF32 ? 2u : 1u, 1u, 1u, kBlockM, BLOCK_N);
+  constexpr uint32_t TMEM_COLS = BLOCK_N < 32 ? 32 : BLOCK_N;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  const int R = args.rows;
+  const int atom_bytes = R * 128;
+  const int stage_bytes = (A_ATOMS + B_ATOMS) * atom_bytes;
+  const int STAGES = args.stages;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * stage_bytes);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int id = blockIdx.x;
+  const int n_tile = id % args.n_tiles;
+  id /= args.n_tiles;
+  const int m_tile = id % args.m_tiles;
+  const int tap = id / args.m_tiles;
+  const int r = tap / args.KW, sx = tap - r * args.KW;
+  const int co0 = m_tile * kBlockM, ci0 = n_tile * BLOCK_N;
+  const int t_begin = blockIdx.y * args.tiles_per_cta;
+  const int t_end = min(args.tiles_total, t_begin + args.tiles_per_cta);
+  const int num_kb = t_end - t_begin;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&args.tmDy);
+    tma_prefetch_desc(&args.tmX);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<TMEM_COLS>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
+  pdl_trigger();
+  if (num_kb <= 0) {  // nothing to reduce for this CTA (uneven split): contribute nothing
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc<TMEM_COLS>(tmem_base);
+    return;
+  }
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int i = 0; i < num_kb; ++i) {
+        const int stage = i % STAGES;
+        const uint32_t phase = (i / STAGES) & 1;
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        mbar_expect_tx(&full_bar[stage], stage_bytes);
+        const int t = t_begin + i;
+        const int n = t / args.tiles_h, oh0 = (t - n * args.tiles_h) * args.ho_t;
+        uint8_t* sa = smem + stage * stage_bytes;
+        uint8_t* sb = sa + A_ATOMS * atom_bytes;
+#pragma unroll
+        for (int a = 0; a < A_ATOMS; ++a)
+          tma_load_4d(sa + a * atom_bytes, &args.tmDy, &full_bar[stage], co0 + a * ATOM, 0, oh0, n);
+#pragma unroll
+        for (int a = 0; a < B_ATOMS; ++a)
+          tma_load_4d(sb + a * atom_bytes, &args.tmX, &full_bar[stage], ci0 + a * ATOM, sx - args.pad_w,
+                      oh0 + r - args.pad_h, n);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const int mmas = R / UMMA_K;
+      for (int i = 0; i < num_kb; ++i) {
+        const int stage = i % STAGES;
+        const uint32_t phase = (i / STAGES) & 1;
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t a_base = smem_u32(smem + stage * stage_bytes);
+        const uint32_t b_base = a_base + A_ATOMS * atom_bytes;
+        for (int j = 0; j < mmas; ++j) {
+          const uint64_t da = umma_smem_desc_sw128(a_base + j * UMMA_K * 128, atom_bytes, MN_SBO, MN_LAYOUT);
+          const uint64_t db = umma_smem_desc_sw128(b_base + j * UMMA_K * 128, atom_bytes, MN_SBO, MN_LAYOUT);
+          tc_mma<KIND>(tmem_base, da, db, IDESC, (i | j) != 0 ? 1u : 0u);
+        }
+        tc_commit(&empty_bar[stage]);
+      }
+      tc_commit(tmem_full_bar);
+    }
+  } else if (warp >= 4) {
+    const int q = warp - 4;
+    const int co = co0 + q * 32 + lane;
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    float* base = args.dw + (size_t)tap * args.Ci * args.Co;
+#pragma unroll 1
+    for (int c = 0; c < BLOCK_N / 32; ++c) {
+      uint32_t v[32];
+      tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c * 32, v);
+      tmem_ld_wait();
+      if (co < args.Co) {
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+          const int ci = ci0 + c * 32 + k;
+          if (ci < args.Ci) atomicAdd(base + (size_t)ci * args.Co + co, __uint_as_float(v[k]));
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<TMEM_COLS>(tmem_base);
+}
+
+}  // namespace b2d
+
+struct b2d_conv_wgrad_plan {
+  WgradArgs args;
+  void (*kernel)(const WgradArgs);
+  dim3 grid;
+  int smem_bytes;
+};
+
+static int gcd_int(int a, int b) { return b == 0 ? a : gcd_int(b, a % b); }
+
+extern "C" int b2d_conv_wgrad_plan_create(const b2d_conv_desc* dp, b2d_conv_wgrad_plan** out) {
+  B2D_REQUIRE(dp != nullptr && out != nullptr, "conv_wgrad_plan_create: null argument");
+  const b2d_conv_desc& d = *dp;
+  const int es = d.dtype == B2D_F32 ? 4 : 2;
+  const int atom = 128 / es, umma_k = 32 / es;
+  const int OH = d.H + 2 * d.pad_h - d.KH + 1, OW = d.W + 2 * d.pad_w - d.KW + 1;
+  B2D_REQUIRE(OH > 0 && OW > 0 && OW <= 256, "conv_wgrad: unsupported output size %dx%d", OH, OW);
+  B2D_REQUIRE((d.Ci * es) % 16 == 0 && (d.Co * es) % 16 == 0,
+              "conv_wgrad: channel counts must make pixels 16-byte aligned (Ci=%d Co=%d)", d.Ci, d.Co);
+  B2D_REQUIRE(d.x && d.w && d.y, "conv_wgrad: null tensor pointer");
+  b2d_conv_wgrad_plan* p = new (std::nothrow) b2d_conv_wgrad_plan();
+  B2D_REQUIRE(p != nullptr, "conv_wgrad: out of host memory");
+  WgradArgs& a = p->args;
+  // Box height: smallest h making OW*h a multiple of the MMA K, scaled up towards ~96 pixels.
+  const int h_unit = umma_k / gcd_int(OW, umma_k);
+  int ho_t = h_unit;
+  while (OW * (ho_t + h_unit) <= 96 && ho_t + h_unit <= 256 && ho_t < OH) ho_t += h_unit;
+  a.ho_t = ho_t, a.rows = OW * ho_t;
+  a.tiles_h = ceil_div(OH, ho_t);
+  a.tiles_total = d.N * a.tiles_h;
+  a.Ci = d.Ci, a.Co = d.Co, a.KW = d.KW, a.pad_h = d.pad_h, a.pad_w = d.pad_w;
+  a.dw = static_cast<float*>(const_cast<void*>(d.w));
+  const int block_n = d.Ci <= 32 && atom <= 32 ? 32 : (d.Ci <= 64 ? 64 : 128);
+  a.m_tiles = ceil_div(d.Co, kBlockM), a.n_tiles = ceil_div(d.Ci, block_n);
+  const int a_atoms = kBlockM / atom, b_atoms = block_n / atom;
+  const int stage_bytes = (a_atoms + b_atoms) * a.rows * 128;
+  a.stages = max(1, min(4, kSmemBudget / stage_bytes));
+  if (stage_bytes > kSmemBudget) {
+    set_error("conv_wgrad: pixel box of %d rows does not fit shared memory", a.rows);
+    delete p;
+    return B2D_ERR_UNSUPPORTED;
+  }
+  p->smem_bytes = a.stages * stage_bytes + 1024 + 256;
+  const int fixed = d.KH * d.KW * a.m_tiles * a.n_tiles;
+  int chunks = max(1, min(a.tiles_total, (148 * 2 + fixed - 1) / fixed));
+  a.tiles_per_cta = ceil_div(a.tiles_total, chunks);
+  chunks = ceil_div(a.tiles_total, a.tiles_per_cta);
+  p->grid = dim3(fixed, chunks);
+  int rc = encode_tmap_4d(&a.tmDy, d.dtype, d.y, d.Co, OW, OH, d.N, atom, OW, ho_t, 1, true);
+  if (rc == B2D_OK) rc = encode_tmap_4d(&a.tmX, d.dtype, d.x, d.Ci, d.W, d.H, d.N, atom, OW, ho_t, 1, true);
+  if (rc != B2D_OK) {
+    delete p;
+    return rc;
+  }
+  if (d.dtype == B2D_F32)
+    p->kernel = block_n == 32 ? conv_wgrad_tc_kernel<MmaKind::TF32, 32>
+                : block_n == 64 ? conv_wgrad_tc_kernel<MmaKind::TF32, 64>
+                                : conv_wgrad_tc_kernel<MmaKind::TF32, 128>;
+  else
+    p->kernel = block_n == 64 ? conv_wgrad_tc_kernel<MmaKind::F16, 64> : conv_wgrad_tc_kernel<MmaKind::F16, 128>;
+  cudaError_t e = cudaFuncSetAttribute(reinterpret_cast<const void*>(p->kernel),
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  if (e != cudaSuccess) {
+    set_error("conv_wgrad: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
+    delete p;
+    return B2D_ERR_CUDA;
+  }
+  *out = p;
+  return B2D_OK;
+}
+
+extern "C" int b2d_conv_wgrad_plan_run(const b2d_conv_wgrad_plan* p, void* stream) {
+  B2D_REQUIRE(p != nullptr, "conv_wgrad_plan_run: null plan");
+  B2D_CUDA_CHECK(launch_pdl(p->kernel, p->grid, dim3(256), p->smem_bytes, static_cast<cudaStream_t>(stream), p->args));
+  return B2D_OK;
+}
+
+extern "C" void b2d_conv_wgrad_plan_destroy(b2d_conv_wgrad_plan* p) { delete p; }
 
 // ---------------------------------------------------------------------------------------
 // b2d_gemm_noalloc — the same GEMM for callers that must not allocate device memory.
@@ -568,7 +1008,7 @@ extern "C" int b2d_gemm_noalloc(const b2d_gemm_desc* desc, void* stream) {
   uint32_t* counters = reinterpret_cast<uint32_t*>(scratch);
   float* workspace = scratch + kStaticCounterWords;
 
-  b2d_gemm_plan plan;  // on the stack: no host allocation either
+  b2d_gemm_plan plan{};  // on the stack: no host allocation either
   const int es = d.dtype == B2D_F32 ? 4 : 2;
   const uint32_t block_k = 128 / es, atom = 128 / es;
   if (!d.a_mn_major)
@@ -588,6 +1028,7 @@ extern "C" int b2d_gemm_noalloc(const b2d_gemm_desc* desc, void* stream) {
   a.kb_total = g.k_blocks, a.kb_per_split = ceil_div(g.k_blocks, g.splits), a.splits = g.splits;
   a.flags = (d.relu ? kFlagRelu : 0) | (d.accumulate ? kFlagAccumulate : 0) |
             (finalize ? kFlagFinalize : 0) | (d.out_dtype == B2D_BF16 ? kFlagOutBf16 : 0);
+  a.stages = g.stages;
   if (d.dtype == B2D_F32)
     select_major<MmaKind::TF32>(d.a_mn_major, d.b_mn_major, g.block_n, &plan.kernel, &plan.smem_bytes);
   else
@@ -602,8 +1043,6 @@ extern "C" int b2d_gemm_noalloc(const b2d_gemm_desc* desc, void* stream) {
     B2D_CUDA_CHECK(cudaMemsetAsync(workspace, 0, ws_floats * sizeof(float), st));
   }
   const dim3 grid(g.m_tiles, g.n_tiles, g.splits);
-  plan.kernel<<<grid, 256, plan.smem_bytes, st>>>(plan.args);
-  count_launch();
-  B2D_CUDA_CHECK(cudaGetLastError());
+  B2D_CUDA_CHECK(launch_pdl(plan.kernel, grid, dim3(256), g.smem_bytes, st, plan.args));
   return B2D_OK;
 }

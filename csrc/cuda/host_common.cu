@@ -1,5 +1,6 @@
 #include "host_common.h"
 
+#include <cstdlib>
 #include <cstring>
 
 namespace b2d {
@@ -14,10 +15,42 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("B2D_PDL");
+    return e == nullptr || e[0] != '0';
+  }();
+  return on;
+}
+
+void set_uniform_carveout(const void* kernel) {
+  static const bool on = [] {
+    const char* e = getenv("B2D_CARVEOUT");
+    return e == nullptr || e[0] != '0';
+  }();
+  if (!on) return;
+  // small fixed table: the library has a few dozen kernels; lookups are lock-free reads
+  static std::atomic<const void*> seen[256];
+  for (auto& slot : seen) {
+    const void* cur = slot.load(std::memory_order_acquire);
+    if (cur == kernel) return;
+    if (cur == nullptr) {
+      const void* expected = nullptr;
+      if (slot.compare_exchange_strong(expected, kernel)) {
+        cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                             cudaSharedmemCarveoutMaxShared);
+        (void)cudaGetLastError();
+        return;
+      }
+      if (expected == kernel) return;
+    }
+  }
+}
+
 void* driver_fn(const char* name) {
   void* fn = nullptr;
   cudaDriverEntryPointQueryResult q;
-  cudaError_t e = cudaGetDriverEntryPointByVersion(name, &fn, 12000, cudaEnableDefault, &q);
+  cudaError_t e = cudaGetDriverEntryPointByVersion(name, &fn, 12080, cudaEnableDefault, &q);
   if (e != cudaSuccess || q != cudaDriverEntryPointSuccess || fn == nullptr) {
     set_error("driver entry point %s unavailable (%s)", name, cudaGetErrorString(e));
     (void)cudaGetLastError();

@@ -51,4 +51,31 @@ void* driver_fn(const char* name);
 
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
+// Programmatic dependent launch: every kernel of this library is launched with the
+// programmatic-stream-serialization attribute and begins with griddepcontrol.wait /
+// griddepcontrol.launch_dependents (pdl_wait / pdl_trigger in ptx.cuh), so kernel N+1 is
+// scheduled and runs its prologue while kernel N is still executing; its wait returns once
+// kernel N has completed and flushed.  B2D_PDL=0 turns the attribute off (the device-side
+// instructions are then no-ops).  Captured into CUDA graphs the edges stay programmatic.
+bool pdl_enabled();
+// Every kernel asks for the same (maximal) shared-memory carve-out, so the SMs never have to
+// re-partition L1/shared memory between consecutive kernels of a step (that switch drains the
+// SM).  B2D_CARVEOUT=0 leaves the driver's per-kernel default.
+void set_uniform_carveout(const void* kernel);
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                              cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid, cfg.blockDim = block, cfg.dynamicSmemBytes = smem, cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  set_uniform_carveout(reinterpret_cast<const void*>(kernel));
+  count_launch();
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 }  // namespace b2d

@@ -11,6 +11,7 @@
 // Layouts follow Keras: activations NHWC, conv kernels HWIO, Dense kernels (in, out).
 // Reference behaviour: README.md:292-302 (the layer list, loss, optimizer and metric).
 #include "host_common.h"
+#include "ptx.cuh"
 
 namespace b2d {
 
@@ -36,6 +37,8 @@ __global__ void __launch_bounds__(256) conv_c1_pool_fwd_kernel(
     const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
     float* __restrict__ y, uint8_t* __restrict__ code, int H, int W, int Co, int PH, int PW,
     int band) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ float xs[];  // [(2*band + KS) rows][W]
   const int n = blockIdx.x;
   const int ph0 = blockIdx.y * band;
@@ -90,6 +93,8 @@ template <int KS>
 __global__ void __launch_bounds__(256) conv_c1_pool_bwd_kernel(
     const float* __restrict__ x, const float* __restrict__ dy, const uint8_t* __restrict__ code,
     float* __restrict__ dw, float* __restrict__ db, int H, int W, int Co, int PH, int PW, int band) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ float sm[];
   float* xs = sm;  // image band
   const int n = blockIdx.x;
@@ -146,18 +151,19 @@ __global__ void __launch_bounds__(256) conv_c1_pool_bwd_kernel(
 
 // =======================================================================================
 // Classifier head: logits = h.W + b ; softmax cross-entropy ; all gradients.   [K4+K5+K6]
-//   Phase 1 — one warp per batch row (8 rows per pass): logits by warp-reduced dot products
-//   against W in shared memory, softmax, dz, and dh = dz.W^T (ReLU-masked) written straight out.
-//   Phase 2 — the whole CTA turns the pass's 8 (h, dz) rows into dW / db partial sums held in
-//   registers (each thread owns fixed (k, c) outputs), so no shared-memory atomics exist; one
-//   global atomic per output per CTA at the end.  Optionally also accumulates the bias gradient
-//   of the layer that produced h (column sums of dh), saving that layer a kernel.
+//   Phase 1 — one warp per batch row (8 rows per pass): class c's logit is a warp-reduced dot
+//   product against W in shared memory; the softmax runs with lane = class; dh = dz.W^T
+//   (ReLU-masked) is written straight out.
+//   Phase 2 — the whole CTA turns the pass's 8 (h, dz) rows into dW / db partial sums; each
+//   thread owns fixed (k, c) outputs, so there are no shared-memory atomics; one global atomic
+//   per output per CTA.  Optionally also accumulates the bias gradient of the layer that
+//   produced h (column sums of dh), saving that layer a kernel.
+//   The kernel runs once per step on a handful of CTAs, i.e. it is instruction-fetch bound:
+//   every loop is deliberately NOT unrolled to keep the code a few hundred instructions.
 //   metrics[0] += sum of per-row losses, metrics[1] += #correct, metrics[2] += #rows.
 // =======================================================================================
 constexpr int kHeadMaxC = 32;
-constexpr int kHeadRows = 8;          // rows per pass = warps per CTA
-constexpr int kHeadMaxOut = 48;       // dW outputs per thread: K*C <= 48*256
-constexpr int kHeadMaxKPerThread = 8; // dh column sums per thread: K <= 8*256
+constexpr int kHeadRows = 8;  // rows per pass = warps per CTA
 
 __global__ void __launch_bounds__(256) dense_xent_head_kernel(
     const float* __restrict__ h, const float* __restrict__ w, const float* __restrict__ bias,
@@ -165,104 +171,104 @@ __global__ void __launch_bounds__(256) dense_xent_head_kernel(
     float* __restrict__ dw, float* __restrict__ db, float* __restrict__ dh_colsum,
     float* __restrict__ metrics, int B, int K, int C, float grad_scale, int relu_mask,
     int rows_per_cta) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ float sm[];
-  float* ws = sm;                        // [K][C]
-  float* hs = ws + K * C;                // [8][K]   h rows of this pass
-  float* dhs = hs + kHeadRows * K;       // [8][K]   dh rows of this pass
-  float* dzs = dhs + kHeadRows * K;      // [8][32]
-  float* rowm = dzs + kHeadRows * kHeadMaxC;  // [8][2] loss, correct
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int KC = K * C;
-  for (int i = tid; i < KC; i += 256) ws[i] = w[i];
-  float acc_w[kHeadMaxOut];
-#pragma unroll
-  for (int j = 0; j < kHeadMaxOut; ++j) acc_w[j] = 0.f;
-  float acc_k[kHeadMaxKPerThread];
-#pragma unroll
-  for (int j = 0; j < kHeadMaxKPerThread; ++j) acc_k[j] = 0.f;
-  float acc_b = 0.f, loss_sum = 0.f, correct_sum = 0.f;
+  float* ws = sm;                             // [K][C]
+  float* hs = ws + KC;                        // [8][K]   h rows of this pass
+  float* dhs = hs + kHeadRows * K;            // [8][K]   dh rows of this pass
+  float* dzs = dhs + kHeadRows * K;           // [8][32]  dz rows of this pass
+  float* rowm = dzs + kHeadRows * kHeadMaxC;  // [8][2]   loss, correct
+  float* accw = rowm + 2 * kHeadRows;         // [K*C]    multi-pass dW partial sums
+  float* acck = accw + KC;                    // [K]      multi-pass dh column sums
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int row0 = blockIdx.x * rows_per_cta;
   const int row1 = min(B, row0 + rows_per_cta);
+  const bool multi_pass = row1 - row0 > kHeadRows;
+#pragma unroll 1
+  for (int i = tid; i < KC; i += 256) ws[i] = w[i], accw[i] = 0.f;
+#pragma unroll 1
+  for (int i = tid; i < K; i += 256) acck[i] = 0.f;
+  float acc_b = 0.f, loss_sum = 0.f, correct_sum = 0.f;
   __syncthreads();
+#pragma unroll 1
   for (int base = row0; base < row1; base += kHeadRows) {
     const int r = base + warp;
-    const bool r_ok = r < row1;
-    // ---- phase 1: this warp's row ----
-    float z[kHeadMaxC];
-#pragma unroll
-    for (int c = 0; c < kHeadMaxC; ++c) z[c] = 0.f;
-    if (r_ok) {
+    float* hrow = hs + warp * K;
+    float* dhrow = dhs + warp * K;
+    float* dzrow = dzs + warp * kHeadMaxC;
+    if (r < row1) {
       const float* hr = h + (size_t)r * K;
-      for (int k = lane; k < K; k += 32) {
-        const float hv = hr[k];
-        hs[warp * K + k] = hv;
-#pragma unroll
-        for (int c = 0; c < kHeadMaxC; ++c)
-          if (c < C) z[c] = fmaf(hv, ws[k * C + c], z[c]);
+#pragma unroll 1
+      for (int k = lane; k < K; k += 32) hrow[k] = hr[k];
+      __syncwarp();
+      // logits: lane c ends up holding z[c]
+      float zc = -INFINITY;
+#pragma unroll 1
+      for (int c = 0; c < C; ++c) {
+        float p = 0.f;
+#pragma unroll 1
+        for (int k = lane; k < K; k += 32) p = fmaf(hrow[k], ws[k * C + c], p);
+        p = warp_sum(p);
+        if (lane == c) zc = p + bias[c];
       }
-      float mx = -INFINITY;
-      int arg = 0;
+      if (logits_out != nullptr && lane < C) logits_out[(size_t)r * C + lane] = zc;
+      // softmax over lanes, arg-max with lowest-index tie-break
+      float mx = zc;
+      int arg = lane < C ? lane : 0x7fffffff;
 #pragma unroll
-      for (int c = 0; c < kHeadMaxC; ++c)
-        if (c < C) {
-          z[c] = warp_sum(z[c]) + bias[c];
-          if (z[c] > mx) mx = z[c], arg = c;
-        }
+      for (int o = 16; o > 0; o >>= 1) {
+        const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+        const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+        if (om > mx || (om == mx && oa < arg)) mx = om, arg = oa;
+      }
+      const float e = lane < C ? __expf(zc - mx) : 0.f;
+      const float se = warp_sum(e);
       const int yl = labels[r];
-      float se = 0.f, zy = 0.f;
-#pragma unroll
-      for (int c = 0; c < kHeadMaxC; ++c)
-        if (c < C) {
-          se += __expf(z[c] - mx);
-          if (c == yl) zy = z[c];
-        }
-      const float lse = mx + __logf(se);
-      const float inv = 1.f / se;
-#pragma unroll
-      for (int c = 0; c < kHeadMaxC; ++c)
-        if (c < C) {
-          if (logits_out != nullptr && lane == 0) logits_out[(size_t)r * C + c] = z[c];
-          z[c] = (__expf(z[c] - mx) * inv - (c == yl ? 1.f : 0.f)) * grad_scale;  // dz
-          if (lane == 0) dzs[warp * kHeadMaxC + c] = z[c];
-        }
-      if (lane == 0) rowm[warp * 2] = lse - zy, rowm[warp * 2 + 1] = arg == yl ? 1.f : 0.f;
+      const float zy = __shfl_sync(0xffffffffu, zc, yl);
+      const float dz = lane < C ? (e / se - (lane == yl ? 1.f : 0.f)) * grad_scale : 0.f;
+      dzrow[lane] = dz;
+      if (lane == 0) rowm[warp * 2] = mx + __logf(se) - zy, rowm[warp * 2 + 1] = arg == yl ? 1.f : 0.f;
+      __syncwarp();
+#pragma unroll 1
       for (int k = lane; k < K; k += 32) {
         float g = 0.f;
-#pragma unroll
-        for (int c = 0; c < kHeadMaxC; ++c)
-          if (c < C) g = fmaf(z[c], ws[k * C + c], g);
-        if (relu_mask && !(hs[warp * K + k] > 0.f)) g = 0.f;
-        dhs[warp * K + k] = g;
+#pragma unroll 1
+        for (int c = 0; c < C; ++c) g = fmaf(dzrow[c], ws[k * C + c], g);
+        if (relu_mask && !(hrow[k] > 0.f)) g = 0.f;
+        dhrow[k] = g;
         if (dh != nullptr) dh[(size_t)r * K + k] = g;
       }
     } else {
-      for (int k = lane; k < K; k += 32) hs[warp * K + k] = 0.f, dhs[warp * K + k] = 0.f;
-      if (lane < kHeadMaxC) dzs[warp * kHeadMaxC + lane] = 0.f;
+#pragma unroll 1
+      for (int k = lane; k < K; k += 32) hrow[k] = 0.f, dhrow[k] = 0.f;
+      dzrow[lane] = 0.f;
       if (lane == 0) rowm[warp * 2] = 0.f, rowm[warp * 2 + 1] = 0.f;
     }
     __syncthreads();
     // ---- phase 2: CTA-wide partial sums over the 8 rows of this pass ----
+#pragma unroll 1
+    for (int o = tid; o < KC; o += 256) {
+      const int k = o / C, c = o - k * C;
+      float s = 0.f;
 #pragma unroll
-    for (int j = 0; j < kHeadMaxOut; ++j) {
-      const int o = tid + j * 256;
-      if (o < KC) {
-        const int k = o / C, c = o - k * C;
-        float s = 0.f;
-#pragma unroll
-        for (int rr = 0; rr < kHeadRows; ++rr) s = fmaf(hs[rr * K + k], dzs[rr * kHeadMaxC + c], s);
-        acc_w[j] += s;
-      }
+      for (int rr = 0; rr < kHeadRows; ++rr) s = fmaf(hs[rr * K + k], dzs[rr * kHeadMaxC + c], s);
+      if (multi_pass)
+        accw[o] += s;
+      else
+        atomicAdd(&dw[o], s);
     }
     if (dh_colsum != nullptr) {
+#pragma unroll 1
+      for (int k = tid; k < K; k += 256) {
+        float s = 0.f;
 #pragma unroll
-      for (int j = 0; j < kHeadMaxKPerThread; ++j) {
-        const int k = tid + j * 256;
-        if (k < K) {
-          float s = 0.f;
-#pragma unroll
-          for (int rr = 0; rr < kHeadRows; ++rr) s += dhs[rr * K + k];
-          acc_k[j] += s;
-        }
+        for (int rr = 0; rr < kHeadRows; ++rr) s += dhs[rr * K + k];
+        if (multi_pass)
+          acck[k] += s;
+        else
+          atomicAdd(&dh_colsum[k], s);
       }
     }
     if (tid < C) {
@@ -275,16 +281,12 @@ __global__ void __launch_bounds__(256) dense_xent_head_kernel(
     }
     __syncthreads();
   }
-#pragma unroll
-  for (int j = 0; j < kHeadMaxOut; ++j) {
-    const int o = tid + j * 256;
-    if (o < KC) atomicAdd(&dw[o], acc_w[j]);
-  }
-  if (dh_colsum != nullptr) {
-#pragma unroll
-    for (int j = 0; j < kHeadMaxKPerThread; ++j) {
-      const int k = tid + j * 256;
-      if (k < K) atomicAdd(&dh_colsum[k], acc_k[j]);
+  if (multi_pass) {
+#pragma unroll 1
+    for (int o = tid; o < KC; o += 256) atomicAdd(&dw[o], accw[o]);
+    if (dh_colsum != nullptr) {
+#pragma unroll 1
+      for (int k = tid; k < K; k += 256) atomicAdd(&dh_colsum[k], acck[k]);
     }
   }
   if (tid < C) atomicAdd(&db[tid], acc_b);
@@ -301,6 +303,8 @@ __global__ void __launch_bounds__(256) softmax_xent_kernel(const float* __restri
                                                             float* __restrict__ dz,
                                                             float* __restrict__ metrics, int B, int C,
                                                             float grad_scale) {
+  pdl_wait();
+  pdl_trigger();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= B) return;
   const float* zr = z + (size_t)warp * C;
@@ -338,6 +342,8 @@ __global__ void __launch_bounds__(256) softmax_xent_kernel(const float* __restri
 __global__ void maxpool2_fwd_kernel(const float* __restrict__ x, float* __restrict__ y,
                                     uint8_t* __restrict__ code, int N, int H, int W, int C, int PH,
                                     int PW) {
+  pdl_wait();
+  pdl_trigger();
   const size_t total = (size_t)N * PH * PW * C;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total;
        i += (size_t)gridDim.x * blockDim.x) {
@@ -364,6 +370,8 @@ __global__ void maxpool2_fwd_kernel(const float* __restrict__ x, float* __restri
 __global__ void maxpool2_bwd_kernel(const float* __restrict__ dy, const uint8_t* __restrict__ code,
                                     const float* __restrict__ y_pooled, float* __restrict__ dx, int N,
                                     int H, int W, int C, int PH, int PW, int act_relu) {
+  pdl_wait();
+  pdl_trigger();
   const size_t total = (size_t)N * H * W * C;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total;
        i += (size_t)gridDim.x * blockDim.x) {
@@ -387,6 +395,8 @@ __global__ void maxpool2_bwd_kernel(const float* __restrict__ dy, const uint8_t*
 __global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ dy,
                                                       float* __restrict__ db, int M, int N,
                                                       int rows_per_cta) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ float part[8][33];
   const int col = blockIdx.x * 32 + (threadIdx.x & 31);
   const int wy = threadIdx.x >> 5;
@@ -407,6 +417,8 @@ __global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ d
 // dx = dy where y > 0 else 0 (in place allowed).
 __global__ void relu_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y,
                                 float* __restrict__ dx, size_t n) {
+  pdl_wait();
+  pdl_trigger();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n;
        i += (size_t)gridDim.x * blockDim.x)
     dx[i] = y[i] > 0.f ? dy[i] : 0.f;
@@ -423,6 +435,8 @@ struct ConvShape {
 __global__ void conv2d_fwd_direct_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                          const float* __restrict__ bias, float* __restrict__ y,
                                          ConvShape s, int relu) {
+  pdl_wait();
+  pdl_trigger();
   const size_t total = (size_t)s.N * s.OH * s.OW * s.Co;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total;
        i += (size_t)gridDim.x * blockDim.x) {
@@ -451,6 +465,8 @@ __global__ void conv2d_fwd_direct_kernel(const float* __restrict__ x, const floa
 // dx[n,ih,iw,ci] = sum_{kh,kw,co} dy[n,oh,ow,co] * w[kh,kw,ci,co]
 __global__ void conv2d_dgrad_direct_kernel(const float* __restrict__ dy, const float* __restrict__ w,
                                            float* __restrict__ dx, ConvShape s) {
+  pdl_wait();
+  pdl_trigger();
   const size_t total = (size_t)s.N * s.H * s.W * s.Ci;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total;
        i += (size_t)gridDim.x * blockDim.x) {
@@ -486,6 +502,8 @@ __global__ void __launch_bounds__(256) conv2d_wgrad_direct_kernel(const float* _
                                                                    const float* __restrict__ dy,
                                                                    float* __restrict__ dw,
                                                                    ConvShape s) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ float part[8][33];
   const int tap = blockIdx.x;  // (kh*KW + kw)*Ci + ci
   const int ci = tap % s.Ci;
@@ -524,6 +542,8 @@ __global__ void __launch_bounds__(256) sgemm_simt_kernel(const float* __restrict
                                                           float* __restrict__ D, long long ldd,
                                                           const float* __restrict__ bias, int M, int N,
                                                           int K, int relu, int accumulate) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ float as[32][33], bs[32][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
   const int m0 = blockIdx.y * 32, n0 = blockIdx.x * 32;
@@ -568,6 +588,8 @@ __global__ void __launch_bounds__(256) sgemm_simt_kernel(const float* __restrict
 // =======================================================================================
 __global__ void sgd_apply_kernel(float* __restrict__ w, float* __restrict__ g, size_t n_params,
                                  size_t n_total, float lr) {
+  pdl_wait();
+  pdl_trigger();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n_total;
        i += (size_t)gridDim.x * blockDim.x) {
     const float gv = g[i];
@@ -578,6 +600,8 @@ __global__ void sgd_apply_kernel(float* __restrict__ w, float* __restrict__ g, s
 
 __global__ void cast_f32_bf16_kernel(const float* __restrict__ src, uint16_t* __restrict__ dst,
                                      size_t n) {
+  pdl_wait();
+  pdl_trigger();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n;
        i += (size_t)gridDim.x * blockDim.x) {
     uint32_t r;
@@ -611,10 +635,9 @@ extern "C" int b2d_conv_c1_pool_fwd(const float* x, const float* w, const float*
   const size_t smem = (size_t)(2 * band + KS) * W * sizeof(float);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (KS == 3)
-    conv_c1_pool_fwd_kernel<3><<<grid, 256, smem, st>>>(x, w, bias, y, code, H, W, Co, PH, PW, band);
+    B2D_CUDA_CHECK(launch_pdl(conv_c1_pool_fwd_kernel<3>, dim3(grid), dim3(256), smem, st, x, w, bias, y, code, H, W, Co, PH, PW, band));
   else
-    conv_c1_pool_fwd_kernel<5><<<grid, 256, smem, st>>>(x, w, bias, y, code, H, W, Co, PH, PW, band);
-  count_launch();
+    B2D_CUDA_CHECK(launch_pdl(conv_c1_pool_fwd_kernel<5>, dim3(grid), dim3(256), smem, st, x, w, bias, y, code, H, W, Co, PH, PW, band));
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;
 }
@@ -630,10 +653,9 @@ extern "C" int b2d_conv_c1_pool_bwd(const float* x, const float* dy, const uint8
   const size_t smem = ((size_t)(2 * band + KS) * W + 8 * (KS * KS + 1) * 32) * sizeof(float);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (KS == 3)
-    conv_c1_pool_bwd_kernel<3><<<grid, 256, smem, st>>>(x, dy, code, dw, db, H, W, Co, PH, PW, band);
+    B2D_CUDA_CHECK(launch_pdl(conv_c1_pool_bwd_kernel<3>, dim3(grid), dim3(256), smem, st, x, dy, code, dw, db, H, W, Co, PH, PW, band));
   else
-    conv_c1_pool_bwd_kernel<5><<<grid, 256, smem, st>>>(x, dy, code, dw, db, H, W, Co, PH, PW, band);
-  count_launch();
+    B2D_CUDA_CHECK(launch_pdl(conv_c1_pool_bwd_kernel<5>, dim3(grid), dim3(256), smem, st, x, dy, code, dw, db, H, W, Co, PH, PW, band));
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;
 }
@@ -643,9 +665,8 @@ extern "C" int b2d_dense_xent_head(const float* h, const float* w, const float* 
                                    float* db, float* dh_colsum, float* metrics, int B, int K, int C,
                                    float grad_scale, int relu_mask, void* stream) {
   B2D_REQUIRE(C >= 1 && C <= kHeadMaxC, "dense_xent_head: C must be in [1, %d]", kHeadMaxC);
-  B2D_REQUIRE(K * C <= kHeadMaxOut * 256 && K <= kHeadMaxKPerThread * 256,
-              "dense_xent_head: K*C=%d too large for the fused head", K * C);
-  const size_t smem = ((size_t)K * C + 2 * kHeadRows * K + kHeadRows * kHeadMaxC + 2 * kHeadRows) * sizeof(float);
+  const size_t smem =
+      ((size_t)2 * K * C + (2 * kHeadRows + 1) * K + kHeadRows * kHeadMaxC + 2 * kHeadRows) * sizeof(float);
   B2D_REQUIRE(smem <= 200 * 1024, "dense_xent_head: K*C too large for the fused head (K=%d C=%d)", K, C);
   static bool attr_set = false;
   if (!attr_set) {
@@ -656,18 +677,14 @@ extern "C" int b2d_dense_xent_head(const float* h, const float* w, const float* 
   // One pass of 8 rows per CTA at small batch; several passes per CTA once the grid is full.
   int rows = kHeadRows;
   if (B > kHeadRows * 148 * 2) rows = ceil_div(ceil_div(B, 148 * 2), kHeadRows) * kHeadRows;
-  dense_xent_head_kernel<<<ceil_div(B, rows), 256, smem, static_cast<cudaStream_t>(stream)>>>(
-      h, w, bias, labels, logits_out, dh, dw, db, dh_colsum, metrics, B, K, C, grad_scale, relu_mask, rows);
-  count_launch();
+  B2D_CUDA_CHECK(launch_pdl(dense_xent_head_kernel, dim3(ceil_div(B, rows)), dim3(256), smem, static_cast<cudaStream_t>(stream), h, w, bias, labels, logits_out, dh, dw, db, dh_colsum, metrics, B, K, C, grad_scale, relu_mask, rows));
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;
 }
 
 extern "C" int b2d_softmax_xent(const float* logits, const int* labels, float* dlogits,
                                 float* metrics, int B, int C, float grad_scale, void* stream) {
-  softmax_xent_kernel<<<ceil_div(B * 32, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      logits, labels, dlogits, metrics, B, C, grad_scale);
-  count_launch();
+  B2D_CUDA_CHECK(launch_pdl(softmax_xent_kernel, dim3(ceil_div(B * 32, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), logits, labels, dlogits, metrics, B, C, grad_scale));
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;
 }
@@ -675,9 +692,7 @@ extern "C" int b2d_softmax_xent(const float* logits, const int* labels, float* d
 extern "C" int b2d_maxpool2_fwd(const float* x, float* y, uint8_t* code, int N, int H, int W, int C,
                                 void* stream) {
   const int PH = H / 2, PW = W / 2;
-  maxpool2_fwd_kernel<<<grid_for((size_t)N * PH * PW * C), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      x, y, code, N, H, W, C, PH, PW);
-  count_launch();
+  B2D_CUDA_CHECK(launch_pdl(maxpool2_fwd_kernel, dim3(grid_for((size_t)N * PH * PW * C)), dim3(256), 0, static_cast<cudaStream_t>(stream), x, y, code, N, H, W, C, PH, PW));
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;
 }
@@ -685,9 +700,7 @@ extern "C" int b2d_maxpool2_fwd(const float* x, float* y, uint8_t* code, int N, 
 extern "C" int b2d_maxpool2_bwd(const float* dy, const uint8_t* code, const float* y_pooled, float* dx,
                                 int N, int H, int W, int C, int act_relu, void* stream) {
   const int PH = H / 2, PW = W / 2;
-  maxpool2_bwd_kernel<<<grid_for((size_t)N * H * W * C), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      dy, code, y_pooled, dx, N, H, W, C, PH, PW, act_relu);
-  count_launch();
+  B2D_CUDA_CHECK(launch_pdl(maxpool2_bwd_kernel, dim3(grid_for((size_t)N * H * W * C)), dim3(256), 0, static_cast<cudaStream_t>(stream), dy, code, y_pooled, dx, N, H, W, C, PH, PW, act_relu));
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;
 }
@@ -695,15 +708,13 @@ extern "C" int b2d_maxpool2_bwd(const float* dy, const uint8_t* code, const floa
 extern "C" int b2d_colsum(const float* dy, float* db, int M, int N, void* stream) {
   const int rows = max(8, ceil_div(M, 64));
   const dim3 grid(ceil_div(N, 32), ceil_div(M, rows));
-  colsum_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(dy, db, M, N, rows);
-  count_launch();
+  B2D_CUDA_CHECK(launch_pdl(colsum_kernel, dim3(grid), dim3(256), 0, static_cast<cudaStream_t>(stream), dy, db, M, N, rows));
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;
 }
 
 extern "C" int b2d_relu_bwd(const float* dy, const float* y, float* dx, size_t n, void* stream) {
-  relu_bwd_kernel<<<grid_for(n), 256, 0, static_cast<cudaStream_t>(stream)>>>(dy, y, dx, n);
-  count_launch();
+  B2D_CUDA_CHECK(launch_pdl(relu_bwd_kernel, dim3(grid_for(n)), dim3(256), 0, static_cast<cudaStream_t>(stream), dy, y, dx, n));
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;
 }
@@ -719,9 +730,7 @@ extern "C" int b2d_conv2d_fwd_direct(const float* x, const float* w, const float
                                      int N, int H, int W, int Ci, int Co, int KH, int KW, int sh,
                                      int sw, int ph, int pw, int relu, void* stream) {
   const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw);
-  conv2d_fwd_direct_kernel<<<grid_for((size_t)N * s.OH * s.OW * Co), 256, 0,
-                             static_cast<cudaStream_t>(stream)>>>(x, w, bias, y, s, relu);
-  count_launch();
+  B2D_CUDA_CHECK(launch_pdl(conv2d_fwd_direct_kernel, dim3(grid_for((size_t)N * s.OH * s.OW * Co)), dim3(256), 0, static_cast<cudaStream_t>(stream), x, w, bias, y, s, relu));
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;
 }
@@ -730,9 +739,7 @@ extern "C" int b2d_conv2d_dgrad_direct(const float* dy, const float* w, float* d
                                        int Ci, int Co, int KH, int KW, int sh, int sw, int ph, int pw,
                                        void* stream) {
   const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw);
-  conv2d_dgrad_direct_kernel<<<grid_for((size_t)N * H * W * Ci), 256, 0,
-                               static_cast<cudaStream_t>(stream)>>>(dy, w, dx, s);
-  count_launch();
+  B2D_CUDA_CHECK(launch_pdl(conv2d_dgrad_direct_kernel, dim3(grid_for((size_t)N * H * W * Ci)), dim3(256), 0, static_cast<cudaStream_t>(stream), dy, w, dx, s));
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;
 }
@@ -742,8 +749,7 @@ extern "C" int b2d_conv2d_wgrad_direct(const float* x, const float* dy, float* d
                                        void* stream) {
   const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw);
   const dim3 grid(KH * KW * Ci, ceil_div(Co, 32));
-  conv2d_wgrad_direct_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, dy, dw, s);
-  count_launch();
+  B2D_CUDA_CHECK(launch_pdl(conv2d_wgrad_direct_kernel, dim3(grid), dim3(256), 0, static_cast<cudaStream_t>(stream), x, dy, dw, s));
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;
 }
@@ -752,26 +758,20 @@ extern "C" int b2d_sgemm_simt(const float* A, int64_t sam, int64_t sak, const fl
                               int64_t sbn, float* D, int64_t ldd, const float* bias, int M, int N,
                               int K, int relu, int accumulate, void* stream) {
   const dim3 grid(ceil_div(N, 32), ceil_div(M, 32));
-  sgemm_simt_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(A, sam, sak, B, sbk, sbn, D, ldd,
-                                                                        bias, M, N, K, relu, accumulate);
-  count_launch();
+  B2D_CUDA_CHECK(launch_pdl(sgemm_simt_kernel, dim3(grid), dim3(256), 0, static_cast<cudaStream_t>(stream), A, sam, sak, B, sbk, sbn, D, ldd, bias, M, N, K, relu, accumulate));
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;
 }
 
 extern "C" int b2d_sgd_apply(float* w, float* g, size_t n_params, size_t n_total, float lr,
                              void* stream) {
-  sgd_apply_kernel<<<grid_for(n_total), 256, 0, static_cast<cudaStream_t>(stream)>>>(w, g, n_params,
-                                                                                  n_total, lr);
-  count_launch();
+  B2D_CUDA_CHECK(launch_pdl(sgd_apply_kernel, dim3(grid_for(n_total)), dim3(256), 0, static_cast<cudaStream_t>(stream), w, g, n_params, n_total, lr));
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;
 }
 
 extern "C" int b2d_cast_f32_bf16(const float* src, void* dst, size_t n, void* stream) {
-  cast_f32_bf16_kernel<<<grid_for(n), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      src, static_cast<uint16_t*>(dst), n);
-  count_launch();
+  B2D_CUDA_CHECK(launch_pdl(cast_f32_bf16_kernel, dim3(grid_for(n)), dim3(256), 0, static_cast<cudaStream_t>(stream), src, static_cast<uint16_t*>(dst), n));
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;
 }

@@ -34,6 +34,14 @@ __device__ __forceinline__ bool elect_one() {
 }
 
 // ----------------------------------------------------------------------------------------
+// Programmatic dependent launch (see launch_pdl in host_common.h).
+// ----------------------------------------------------------------------------------------
+// Blocks until every grid this one depends on has completed and its memory is visible.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// Lets the runtime schedule the dependent grid (it will block in its own pdl_wait).
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// ----------------------------------------------------------------------------------------
 // mbarrier
 // ----------------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {

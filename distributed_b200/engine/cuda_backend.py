@@ -29,8 +29,8 @@ class CudaBackend:
         return torch.zeros(shape, dtype=dtype, device=self.device)
 
     def supports_fused_head(self, k_in, units):
-        smem = (k_in * units + 16 * k_in + 8 * _HEAD_MAX_C + 16) * 4
-        return units <= _HEAD_MAX_C and k_in * units <= 48 * 256 and k_in <= 2048 and smem <= _HEAD_SMEM
+        smem = (2 * k_in * units + 17 * k_in + 8 * _HEAD_MAX_C + 16) * 4
+        return units <= _HEAD_MAX_C and smem <= _HEAD_SMEM
 
     @staticmethod
     def _tc_ok(*dims):
@@ -40,7 +40,20 @@ class CudaBackend:
         return all(d % 4 == 0 for d in dims)
 
     def describe_conv(self, layer):
+        from ..ops import conv as tc
+        ci = layer.input_shape[2]
+        x_shape = (1, *layer.input_shape)
+        w_shape = (*layer.kernel_size, ci, layer.filters)
+        if self._conv_tc_ok(x_shape, w_shape, layer.strides, layer.pad_amounts()):
+            return "tcgen05 tf32 implicit GEMM (4-D TMA taps)"
         return "direct conv (CUDA cores)"
+
+    @staticmethod
+    def _conv_tc_ok(x_shape, w_shape, strides, pad, dgrad=False):
+        from ..ops import conv as tc
+        if os.environ.get("B200DIST_CONV", "") == "direct":
+            return False
+        return tc.tc_supported(tuple(x_shape), tuple(w_shape), pad, torch.float32, dgrad=dgrad, strides=strides)
 
     def describe_dense(self, b, k, n):
         return "tcgen05 tf32 GEMM" if self._tc_ok(k, n) else "CUDA-core GEMM"
@@ -59,18 +72,37 @@ class CudaBackend:
 
     # ---- general conv (direct fallback; implicit-GEMM path plugs in here) --------------
     def conv2d_fwd(self, x, w, b, y, strides, pad, relu):
+        from ..ops import conv as tc
+        if self._conv_tc_ok(x.shape, w.shape, strides, pad):
+            plan = tc.ConvFwdPlan(x, w, y, pad, bias=b, relu=relu)
+            self.plans.append(plan)
+            return plan.run
         return lambda: nn.conv2d_fwd_direct(x, w, b, y, strides, pad, relu)
 
     def conv2d_wgrad(self, x, dy, dw, db, strides, pad):
+        from ..ops import conv as tc
         dy2 = dy.view(-1, dy.shape[-1])
+        if self._conv_tc_ok(x.shape, dw.shape, strides, pad) and x.shape[3] % 4 == 0 and dw.shape[3] % 4 == 0:
+            plan = tc.ConvWgradPlan(x, dy, dw, pad)
+            self.plans.append(plan)
+            wgrad = plan.run
+        else:
+            def wgrad():
+                nn.conv2d_wgrad_direct(x, dy, dw, strides, pad)
 
         def run():
-            nn.conv2d_wgrad_direct(x, dy, dw, strides, pad)
+            wgrad()
             if db is not None:
                 nn.colsum(dy2, db)
         return run
 
     def conv2d_dgrad(self, dy, w, dx, strides, pad, mask=None):
+        from ..ops import conv as tc
+        if self._conv_tc_ok(dx.shape, w.shape, strides, pad, dgrad=True):
+            plan = tc.ConvDgradPlan(dy, w, dx, pad, mask=mask)     # ReLU mask fused in the epilogue
+            self.plans.append(plan)
+            return plan.run
+
         def run():
             nn.conv2d_dgrad_direct(dy, w, dx, strides, pad)
             if mask is not None:

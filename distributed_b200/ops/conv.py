@@ -1,0 +1,123 @@
+"""Implicit-GEMM convolution plans on the tcgen05 core (csrc/cuda/gemm_tcgen05.cu).
+
+Stride-1 NHWC x HWIO convolutions: the A operand is the activation tensor itself, read through
+4-D TMA boxes shifted per filter tap (zero padding = TMA out-of-bounds fill), so there is no
+im2col buffer.  Forward, data gradient and (ConvWgradPlan) filter gradient all run on the
+tensor cores.  Conv2D of the README / scaled models (README.md:293, BASELINE.json config 3).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from .._native import cuda_lib as nl
+from .gemm import _DT, _stream_ptr
+
+
+class ConvDesc(C.Structure):
+    _fields_ = [("dtype", C.c_int), ("out_dtype", C.c_int),
+                ("N", C.c_int), ("H", C.c_int), ("W", C.c_int), ("Ci", C.c_int), ("Co", C.c_int),
+                ("KH", C.c_int), ("KW", C.c_int), ("pad_h", C.c_int), ("pad_w", C.c_int),
+                ("x", C.c_void_p), ("w", C.c_void_p), ("y", C.c_void_p),
+                ("bias", C.c_void_p), ("mask", C.c_void_p), ("relu", C.c_int)]
+
+
+_declared = False
+
+
+def _lib():
+    global _declared
+    lib = nl.lib()
+    if not _declared:
+        lib.b2d_conv_tc_supported.argtypes = [C.POINTER(ConvDesc), C.c_int]
+        lib.b2d_conv_fwd_plan_create.argtypes = [C.POINTER(ConvDesc), C.POINTER(C.c_void_p)]
+        lib.b2d_conv_dgrad_plan_create.argtypes = [C.POINTER(ConvDesc), C.POINTER(C.c_void_p)]
+        lib.b2d_conv_wgrad_plan_create.argtypes = [C.POINTER(ConvDesc), C.POINTER(C.c_void_p)]
+        lib.b2d_conv_wgrad_plan_run.argtypes = [C.c_void_p, C.c_void_p]
+        lib.b2d_conv_wgrad_plan_destroy.argtypes = [C.c_void_p]
+        lib.b2d_conv_wgrad_plan_destroy.restype = None
+        _declared = True
+    return lib
+
+
+def _desc(x, w, y, padding, bias=None, mask=None, relu=False):
+    N, H, W, Ci = x.shape
+    KH, KW, Ci2, Co = w.shape
+    assert Ci == Ci2 and x.dtype == w.dtype
+    d = ConvDesc()
+    d.dtype, d.out_dtype = _DT[x.dtype], _DT[x.dtype]
+    d.N, d.H, d.W, d.Ci, d.Co, d.KH, d.KW = N, H, W, Ci, Co, KH, KW
+    d.pad_h, d.pad_w = padding
+    d.x, d.w, d.y = x.data_ptr(), w.data_ptr(), y.data_ptr()
+    d.bias = bias.data_ptr() if bias is not None else None
+    d.mask = mask.data_ptr() if mask is not None else None
+    d.relu = int(relu)
+    return d
+
+
+def tc_supported(x_shape, w_shape, padding, dtype, dgrad=False, strides=(1, 1)) -> bool:
+    if tuple(strides) != (1, 1) or dtype not in _DT:
+        return False
+    d = ConvDesc()
+    d.dtype = d.out_dtype = _DT[dtype]
+    d.N, d.H, d.W, d.Ci = x_shape
+    d.KH, d.KW, _, d.Co = w_shape
+    d.pad_h, d.pad_w = padding
+    return bool(_lib().b2d_conv_tc_supported(C.byref(d), int(dgrad)))
+
+
+class _Plan:
+    def __init__(self, create, desc, keep):
+        self._lib = _lib()
+        h = C.c_void_p()
+        nl.check(create(C.byref(desc), C.byref(h)), "conv plan create")
+        self._h, self._keep = h, keep
+
+    def run(self, stream=None):
+        nl.check(self._lib.b2d_gemm_plan_run(self._h, _stream_ptr(stream)), "conv plan run")
+
+    __call__ = run
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            self._lib.b2d_gemm_plan_destroy(h)
+
+
+class ConvFwdPlan(_Plan):
+    """y = act(conv2d(x, w) + bias), x [N,H,W,Ci], w [KH,KW,Ci,Co], y [N,OH,OW,Co]."""
+
+    def __init__(self, x, w, y, padding=(0, 0), bias=None, relu=False):
+        super().__init__(_lib().b2d_conv_fwd_plan_create, _desc(x, w, y, padding, bias, None, relu),
+                         [x, w, y, bias])
+
+
+class ConvDgradPlan(_Plan):
+    """dx = conv2d_transpose(dy, w) (zeroed where mask <= 0), dx [N,H,W,Ci], dy [N,OH,OW,Co]."""
+
+    def __init__(self, dy, w, dx, padding=(0, 0), mask=None):
+        super().__init__(_lib().b2d_conv_dgrad_plan_create, _desc(dx, w, dy, padding, None, mask, False),
+                         [dy, w, dx, mask])
+
+
+class ConvWgradPlan:
+    """dw += x (*) dy over all pixels (fp32 accumulation into dw [KH,KW,Ci,Co])."""
+
+    def __init__(self, x, dy, dw, padding=(0, 0)):
+        self._lib = _lib()
+        d = _desc(x, dw, dy, padding)
+        d.dtype = _DT[x.dtype]
+        h = C.c_void_p()
+        nl.check(self._lib.b2d_conv_wgrad_plan_create(C.byref(d), C.byref(h)), "conv wgrad plan create")
+        self._h, self._keep = h, [x, dy, dw]
+
+    def run(self, stream=None):
+        nl.check(self._lib.b2d_conv_wgrad_plan_run(self._h, _stream_ptr(stream)), "conv wgrad run")
+
+    __call__ = run
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            self._lib.b2d_conv_wgrad_plan_destroy(h)

@@ -102,6 +102,167 @@ int b2d_gemm_noalloc(const b2d_gemm_desc* desc, void* stream);
 size_t b2d_gemm_noalloc_max_workspace_floats(void);
 size_t b2d_gemm_noalloc_max_tiles(void);
 
+/* ---------------------------------------------------------------------------------------
+ * Implicit-GEMM convolution on the same tensor-core kernel (Conv2D, README.md:293; stride 1).
+ * forward: x [N,H,W,Ci], w [KH,KW,Ci,Co] -> y [N,OH,OW,Co] (+bias, ReLU)
+ * dgrad  : x is the OUTPUT dx, y is the INPUT dy; optional ReLU mask shaped like dx
+ * wgrad  : w is the OUTPUT dW (fp32, accumulated), y is dy
+ * b2d_conv_tc_supported() tells whether a shape qualifies (whole 128-byte channel chunks,
+ * output width <= 128); otherwise use the direct kernels below.  fwd/dgrad plans are
+ * b2d_gemm_plan objects (run/destroy with the GEMM functions).
+ * ------------------------------------------------------------------------------------- */
+typedef struct b2d_conv_desc {
+  int dtype, out_dtype;
+  int N, H, W, Ci, Co, KH, KW, pad_h, pad_w;
+  const void* x;
+  const void* w;
+  void* y;
+  const float* bias;
+  const float* mask;
+  int relu;
+} b2d_conv_desc;
+typedef struct b2d_conv_wgrad_plan b2d_conv_wgrad_plan;
+int b2d_conv_tc_supported(const b2d_conv_desc* desc, int dgrad);
+int b2d_conv_fwd_plan_create(const b2d_conv_desc* desc, b2d_gemm_plan** out);
+int b2d_conv_dgrad_plan_create(const b2d_conv_desc* desc, b2d_gemm_plan** out);
+int b2d_conv_wgrad_plan_create(const b2d_conv_desc* desc, b2d_conv_wgrad_plan** out);
+int b2d_conv_wgrad_plan_run(const b2d_conv_wgrad_plan* plan, void* stream);
+void b2d_conv_wgrad_plan_destroy(b2d_conv_wgrad_plan* plan);
+
+/* ---------------------------------------------------------------------------------------
+ * Non-GEMM kernels (csrc/cuda/nn_kernels.cu).  fp32, NHWC / HWIO / (in,out).  One launch each.
+ * ------------------------------------------------------------------------------------- */
+/* Conv2D(C_in=1, KSxKS valid) + bias + ReLU + MaxPool2x2 in one kernel (README.md:293-294);
+ * code = argmax position 0..3, or 4 where ReLU clamped.  KS in {3,5}. */
+int b2d_conv_c1_pool_fwd(const float* x, const float* w, const float* bias, float* y, uint8_t* code,
+                         int N, int H, int W, int Co, int KS, void* stream);
+/* Pool-backward + ReLU-backward + filter/bias gradient of the layer above (accumulates). */
+int b2d_conv_c1_pool_bwd(const float* x, const float* dy, const uint8_t* code, float* dw, float* db,
+                         int N, int H, int W, int Co, int KS, void* stream);
+/* Dense(C<=32) + SparseCategoricalCrossentropy(from_logits) + accuracy count + dW/db/dh
+ * (README.md:297, 301-302).  metrics += {loss sum, correct, rows}.  dh_colsum (optional, [K])
+ * accumulates the bias gradient of the layer that produced h. */
+int b2d_dense_xent_head(const float* h, const float* w, const float* bias, const int* labels,
+                        float* logits_out, float* dh, float* dw, float* db, float* dh_colsum,
+                        float* metrics, int B, int K, int C, float grad_scale, int relu_mask,
+                        void* stream);
+int b2d_softmax_xent(const float* logits, const int* labels, float* dlogits, float* metrics, int B,
+                     int C, float grad_scale, void* stream);
+int b2d_maxpool2_fwd(const float* x, float* y, uint8_t* code, int N, int H, int W, int C, void* stream);
+int b2d_maxpool2_bwd(const float* dy, const uint8_t* code, const float* y_pooled, float* dx, int N,
+                     int H, int W, int C, int act_relu, void* stream);
+int b2d_colsum(const float* dy, float* db, int M, int N, void* stream);          /* db += column sums */
+int b2d_relu_bwd(const float* dy, const float* y, float* dx, size_t n, void* stream);
+/* Direct (CUDA-core) convolutions: any stride / zero padding. */
+int b2d_conv2d_fwd_direct(const float* x, const float* w, const float* bias, float* y, int N, int H,
+                          int W, int Ci, int Co, int KH, int KW, int sh, int sw, int ph, int pw,
+                          int relu, void* stream);
+int b2d_conv2d_dgrad_direct(const float* dy, const float* w, float* dx, int N, int H, int W, int Ci,
+                            int Co, int KH, int KW, int sh, int sw, int ph, int pw, void* stream);
+int b2d_conv2d_wgrad_direct(const float* x, const float* dy, float* dw, int N, int H, int W, int Ci,
+                            int Co, int KH, int KW, int sh, int sw, int ph, int pw, void* stream);
+/* CUDA-core GEMM with arbitrary strides (tiny / unaligned problems). */
+int b2d_sgemm_simt(const float* A, int64_t sam, int64_t sak, const float* B, int64_t sbk, int64_t sbn,
+                   float* D, int64_t ldd, const float* bias, int M, int N, int K, int relu,
+                   int accumulate, void* stream);
+/* Single-replica optimizer step: w[:n_params] -= lr*g, w[n_params:] += g, g = 0 (README.md:302). */
+int b2d_sgd_apply(float* w, float* g, size_t n_params, size_t n_total, float lr, void* stream);
+int b2d_cast_f32_bf16(const float* src, void* dst, size_t n, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * Symmetric memory over NVLink (csrc/runtime/symm.cpp): one block per GPU, POSIX-fd exchange
+ * over Unix sockets, every peer mapped into every process; optional NVLS multicast binding.
+ * create / multicast_phase1 / multicast_phase2 are collective over the ranks of `tag`
+ * (the caller provides a cross-rank barrier between the multicast phases).
+ * ------------------------------------------------------------------------------------- */
+typedef struct b2d_symm b2d_symm;
+int b2d_symm_create(b2d_symm** out, const char* tag, int rank, int world, int device, size_t bytes,
+                    double timeout_s);
+int b2d_symm_multicast_phase1(b2d_symm* s);
+int b2d_symm_multicast_phase2(b2d_symm* s);
+void* b2d_symm_ptr(const b2d_symm* s, int rank);       /* this process' mapping of `rank`'s block */
+void* b2d_symm_multicast_ptr(const b2d_symm* s);       /* NULL unless multicast is bound          */
+size_t b2d_symm_bytes(const b2d_symm* s);
+int b2d_symm_multicast_supported(const b2d_symm* s);
+int b2d_symm_destroy(b2d_symm* s);
+
+/* ---------------------------------------------------------------------------------------
+ * Fused gradient all-reduce + 1/world averaging + SGD + metric sums + gradient zeroing over
+ * peer memory (csrc/cuda/allreduce.cu): replaces "batch_all_reduce: 6 all-reduces", the four
+ * metric all-reduces and the optimizer step of the reference (README.md:403-407, 302).
+ * algo: 0 one-shot, 1 two-shot (weights all-gather), 2 NVLS multicast, -1 by size.
+ * ------------------------------------------------------------------------------------- */
+typedef struct b2d_allreduce_desc {
+  void* w[8];      /* weight arenas of every rank (peer-mapped)          */
+  void* g[8];      /* gradient arenas                                    */
+  void* sig[8];    /* signal pads, b2d_allreduce_signal_bytes() each     */
+  void* epoch[8];  /* barrier epochs, b2d_allreduce_epoch_bytes() each   */
+  void* out[8];    /* plain one-shot all-reduce destinations             */
+  void* w_mc;      /* multicast views (NVLS) or NULL                     */
+  void* g_mc;
+  int64_t n_params; /* floats updated by SGD (multiple of 4)             */
+  int64_t n_total;  /* n_params + metric tail slots (multiple of 4)      */
+  float lr;
+  int rank, world, algo;
+  int emulate;      /* all ranks in one cooperative launch on one GPU (tests) */
+  int plain;        /* sum only: no SGD, no zeroing                     */
+  int blocks;       /* 0 = automatic                                    */
+} b2d_allreduce_desc;
+size_t b2d_allreduce_signal_bytes(void);
+size_t b2d_allreduce_epoch_bytes(void);
+int b2d_allreduce_pick_algo(int64_t n_total_floats, int world, int have_multicast);
+int b2d_allreduce_sgd(const b2d_allreduce_desc* desc, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * Native step executor (csrc/runtime/executor.cpp): captures the step's launches into CUDA
+ * graphs (one per input staging slot) and runs the fit() hot loop — input prefetch on a copy
+ * stream, graph launch, per-step device->host read of the metric sums (README.md:304, 392).
+ * ------------------------------------------------------------------------------------- */
+typedef struct b2d_executor b2d_executor;
+int b2d_exec_create(b2d_executor** out);
+void b2d_exec_destroy(b2d_executor* e);
+void* b2d_exec_stream(b2d_executor* e);
+int b2d_exec_set_io(b2d_executor* e, int slot, void* x_dev, size_t x_bytes, void* y_dev, size_t y_bytes);
+int b2d_exec_set_metrics(b2d_executor* e, const void* metrics_dev, size_t bytes, void* pinned_ring,
+                         int ring_len);
+int b2d_exec_begin_capture(b2d_executor* e);
+int b2d_exec_end_capture(b2d_executor* e, int slot);
+uint64_t b2d_exec_graph_nodes(const b2d_executor* e, int slot);
+int b2d_exec_run(b2d_executor* e, const void* x_src, size_t x_stride, const void* y_src, size_t y_stride,
+                 int64_t first_step, int64_t steps_in_src, int64_t n_steps, int sync, float* elapsed_ms);
+int b2d_exec_sync(b2d_executor* e);
+uint64_t b2d_exec_steps_done(const b2d_executor* e);
+int b2d_host_alloc(void** out, size_t bytes);   /* pinned host memory */
+int b2d_host_free(void* p);
+
+/* ---------------------------------------------------------------------------------------
+ * CPU backend (libb200dist_cpu.so): C++ reference ops + shared-memory fused all-reduce/SGD.
+ * ------------------------------------------------------------------------------------- */
+void b2c_set_num_threads(int n);
+void b2c_conv2d_fwd(const float* x, const float* w, const float* bias, float* y, int N, int H, int W,
+                    int Ci, int Co, int KH, int KW, int sh, int sw, int ph, int pw, int relu);
+void b2c_conv2d_wgrad(const float* x, const float* dy, float* dw, float* db, int N, int H, int W, int Ci,
+                      int Co, int KH, int KW, int sh, int sw, int ph, int pw);
+void b2c_conv2d_dgrad(const float* dy, const float* w, float* dx, int N, int H, int W, int Ci, int Co,
+                      int KH, int KW, int sh, int sw, int ph, int pw);
+void b2c_maxpool2_fwd(const float* x, float* y, uint8_t* code, int N, int H, int W, int C);
+void b2c_maxpool2_bwd(const float* dy, const uint8_t* code, const float* y_pooled, float* dx, int N,
+                      int H, int W, int C, int act_relu);
+void b2c_gemm(const float* A, int64_t sam, int64_t sak, const float* B, int64_t sbk, int64_t sbn, float* D,
+              int64_t ldd, const float* bias, int M, int N, int K, int relu, int accumulate);
+void b2c_softmax_xent(const float* z, const int32_t* labels, float* dz, float* metrics, int B, int C,
+                      float grad_scale);
+void b2c_relu_bwd(const float* dy, const float* y, float* dx, int64_t n);
+void b2c_colsum(const float* dy, float* db, int M, int N);
+void b2c_sgd_apply(float* w, float* g, int64_t n_params, int64_t n_total, float lr);
+typedef struct b2c_shm_comm b2c_shm_comm;
+const char* b2c_last_error(void);
+b2c_shm_comm* b2c_shm_create(const char* name, int rank, int world, int64_t capacity_floats, double timeout_s);
+void b2c_shm_destroy(b2c_shm_comm* c);
+int b2c_shm_barrier(b2c_shm_comm* c);
+int b2c_shm_allreduce(b2c_shm_comm* c, float* buf, int64_t n);
+int b2c_shm_allreduce_sgd(b2c_shm_comm* c, float* w, float* g, int64_t n_params, int64_t n_total, float lr);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,48 @@
+"""Implicit-GEMM convolution on tcgen05 (forward, dgrad, wgrad) vs PyTorch fp32 references."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [
+    # N, H, W, Ci, Co, K, pad
+    (4, 13, 13, 64, 128, 3, 0),      # scaled-CNN conv2 (BASELINE.json config 3)
+    (130, 13, 13, 64, 128, 3, 0),
+    (3, 14, 14, 32, 64, 3, 1),       # 'same' padding: zero fill by TMA
+    (5, 7, 7, 64, 64, 1, 0),         # 1x1, several images per M tile
+    (2, 56, 56, 64, 64, 3, 1),       # ResNet-style 56x56
+    (2, 9, 20, 96, 36, 5, 2),
+]
+
+
+def _ref(x, w, b, pad):
+    return F.conv2d(x.permute(0, 3, 1, 2), w.permute(3, 2, 0, 1), b, padding=pad).permute(0, 2, 3, 1).contiguous()
+
+
+@pytest.mark.parametrize("N,H,W,Ci,Co,K,pad", SHAPES)
+def test_conv_forward_dgrad_wgrad(N, H, W, Ci, Co, K, pad):
+    from distributed_b200.ops.conv import ConvDgradPlan, ConvFwdPlan, ConvWgradPlan, tc_supported
+    g = torch.Generator(device="cuda").manual_seed(N * H + Ci)
+    x = (torch.randn((N, H, W, Ci), device="cuda", generator=g) * 0.5).requires_grad_()
+    w = (torch.randn((K, K, Ci, Co), device="cuda", generator=g) * 0.1).requires_grad_()
+    b = torch.randn((Co,), device="cuda", generator=g).requires_grad_()
+    assert tc_supported(x.shape, w.shape, (pad, pad), torch.float32)
+    ref = torch.relu(_ref(x, w, b, pad))
+    y = torch.full(ref.shape, float("nan"), device="cuda")
+    ConvFwdPlan(x.detach(), w.detach(), y, (pad, pad), bias=b.detach(), relu=True).run()
+    tol = 3e-3 * ref.abs().max().item()
+    assert (y - ref).abs().max().item() < tol
+    dy = torch.randn(ref.shape, device="cuda", generator=g)
+    ref.backward(dy)
+    dpre = (dy * (ref > 0)).contiguous()
+    if tc_supported(x.shape, w.shape, (pad, pad), torch.float32, dgrad=True):
+        dx = torch.full(x.shape, float("nan"), device="cuda")
+        ConvDgradPlan(dpre, w.detach(), dx, (pad, pad)).run()
+        assert (dx - x.grad).abs().max().item() < 3e-3 * x.grad.abs().max().item()
+        mask = torch.randn(x.shape, device="cuda", generator=g)
+        ConvDgradPlan(dpre, w.detach(), dx, (pad, pad), mask=mask).run()
+        assert (dx - x.grad * (mask > 0)).abs().max().item() < 3e-3 * x.grad.abs().max().item()
+    dw = torch.ones_like(w)
+    ConvWgradPlan(x.detach(), dpre, dw, (pad, pad)).run()
+    assert (dw - 1 - w.grad).abs().max().item() < 3e-3 * w.grad.abs().max().item()
