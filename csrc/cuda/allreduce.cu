@@ -186,23 +186,7 @@ __global__ void __launch_bounds__(kArThreads) allreduce_sgd_kernel(const ArArgs 
 
 using namespace b2d;
 
-struct b2d_allreduce_desc {
-  void* w[kMaxRanks];
-  void* g[kMaxRanks];
-  void* sig[kMaxRanks];
-  void* epoch[kMaxRanks];
-  void* out[kMaxRanks];
-  void* w_mc;
-  void* g_mc;
-  int64_t n_params;  // floats, multiple of 4
-  int64_t n_total;   // floats, multiple of 4
-  float lr;
-  int rank, world;
-  int algo;     // 0 one-shot, 1 two-shot, 2 NVLS, -1 automatic
-  int emulate;  // all ranks in one cooperative launch on this GPU (tests)
-  int plain;    // plain sum all-reduce: one-shot writes out[], two-shot/NVLS are in place on g
-  int blocks;   // 0 = automatic
-};
+// b2d_allreduce_desc is declared in include/b200dist.h
 
 extern "C" size_t b2d_allreduce_signal_bytes(void) {
   return sizeof(uint32_t) * kMaxArBlocks * kMaxRanks;
