@@ -34,7 +34,7 @@ def run(args, ClockSampler, dist_env, max_over_ranks, barrier) -> dict:
     torch.backends.cuda.matmul.allow_tf32 = True
     torch.backends.cudnn.benchmark = True
     if world > 1 and not dist.is_initialized():
-        dist.init_process_group("nccl", device_id=dev)
+        dist.init_process_group("cpu:gloo,cuda:nccl", device_id=dev)    # gloo only for the timing reductions
     torch.manual_seed(0)
     model = build_model(args.model).to(dev)
     if world > 1:

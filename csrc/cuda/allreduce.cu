@@ -11,6 +11,9 @@
 //   two-shot   rank r owns shard r: reads shard r of every G, averages, applies SGD, and writes
 //              the *updated weights* into every peer's W — the all-gather carries weights, so
 //              no optimizer pass exists at all.            traffic/GPU: (N-1)/N S in + out
+//   pull       latency-optimised two-shot: rank r reduces shard r and updates its OWN weights only;
+//              after a cheap flag (local fence, relaxed store) every rank *pulls* the other
+//              shards of the updated weights.  No remote writes -> no system-scope release.
 //   NVLS       like two-shot, but the switch does the sum (multimem.ld_reduce) and the
 //              broadcast (multimem.st).                     traffic/GPU: S/N in + S/N out
 //
@@ -43,10 +46,30 @@ struct ArArgs {
   int rank, world;
   int emulate;                // 1: blockIdx.y is the rank (single-GPU cooperative test mode)
   int plain;                  // 1: out = sum(g), no SGD, no zeroing
+  long long seg_begin4[2];    // up to two [begin, end) float4 ranges of the arenas handled by this
+  long long seg_end4[2];      // launch (bucketing); default one range = the whole arena
+  int nseg;
+  long long* dbg;             // optional timeline (globaltimer ns), 8 slots per block
+  float* gz;                  // double-buffered gradients: the OTHER local buffer, zeroed during
+                              // the reduction (null: single buffer, zeroed after a second barrier)
 };
 
+__device__ __forceinline__ long long ar_time_ns() {
+  long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
 // Block-level barrier across ranks.  All threads of the block call it.
-__device__ __forceinline__ void rank_barrier(const ArArgs& a, int rank, uint32_t* s_epoch) {
+// `publish` = true when this block has written REMOTE memory since the last barrier (two-shot /
+// NVLS weight scatter): the flag store must then be a system-scope release, which costs ~3 us.
+// At the entry barrier nothing has been written by this kernel — the gradients the flag
+// announces were produced by earlier kernels and are already complete in this GPU's L2, which is
+// where peers read them — so a relaxed flag store and relaxed polling suffice (measured: 4.0 us
+// -> see profiles/).
+template <bool kPublish>
+__device__ __forceinline__ void rank_barrier(const ArArgs& a, int rank, uint32_t* s_epoch,
+                                             long long* dbg = nullptr) {
   __syncthreads();  // every thread's earlier accesses are ordered before the release below
   const int b = blockIdx.x;
   if (threadIdx.x == 0) {
@@ -58,10 +81,14 @@ __device__ __forceinline__ void rank_barrier(const ArArgs& a, int rank, uint32_t
   const uint32_t e = *s_epoch;
   if (threadIdx.x < a.world) {
     const int p = threadIdx.x;
-    st_release_sys(a.sig[p] + b * kMaxRanks + rank, e);
+    if (kPublish)
+      st_release_sys(a.sig[p] + b * kMaxRanks + rank, e);
+    else
+      st_relaxed_sys(a.sig[p] + b * kMaxRanks + rank, e);
+    if (dbg != nullptr && threadIdx.x == 0) dbg[0] = ar_time_ns();   // signals sent (dbg = &local[2])
     const uint32_t* mine = a.sig[rank] + b * kMaxRanks + p;
     long long spins = 0;
-    while (static_cast<int32_t>(ld_acquire_sys(mine) - e) < 0) {
+    while (static_cast<int32_t>((kPublish ? ld_acquire_sys(mine) : ld_relaxed_sys(mine)) - e) < 0) {
       if (++spins > (1ll << 31)) {  // a peer died: fail loudly instead of hanging the GPU forever
         printf("b200dist: rank %d block %d timed out waiting for rank %d (epoch %u)\n", rank, b, p, e);
         __trap();
@@ -80,7 +107,7 @@ __device__ __forceinline__ float4 apply_update(float4 w, float4 s, bool is_param
   return f4_add(w, s);  // metric tail: running sums
 }
 
-enum ArAlgo : int { kOneShot = 0, kTwoShot = 1, kNvls = 2 };
+enum ArAlgo : int { kOneShot = 0, kTwoShot = 1, kNvls = 2, kPull = 3 };
 
 template <int ALGO>
 __global__ void __launch_bounds__(kArThreads) allreduce_sgd_kernel(const ArArgs a) {
@@ -91,41 +118,119 @@ __global__ void __launch_bounds__(kArThreads) allreduce_sgd_kernel(const ArArgs 
   const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
 
+  // Debug timeline: per block, slot 0 counts launches and slots 1..4 accumulate nanoseconds spent
+  // (1) launched-early-to-upstream-complete, (2) in the release, (3) waiting for peers, (4) moving data.
+  long long* dbg = a.dbg == nullptr ? nullptr : a.dbg + 8 * blockIdx.x;
+  __shared__ long long s_t[4];
+  if (dbg != nullptr && threadIdx.x == 0) s_t[0] = ar_time_ns();
   pdl_wait();     // this replica's backward has finished writing its gradients
   pdl_trigger();
-  rank_barrier(a, rank, &s_epoch);  // A: every replica's gradients are complete
+  if (dbg != nullptr && threadIdx.x == 0) s_t[1] = ar_time_ns();
+  rank_barrier<false>(a, rank, &s_epoch, dbg == nullptr ? nullptr : &s_t[2]);  // A: every replica's gradients are complete
+  if (dbg != nullptr && threadIdx.x == 0) s_t[3] = ar_time_ns();
 
-  // Peer loads have ~2 us latency: keep kUnroll independent 16-byte loads per peer in flight per
-  // thread (all loads of a batch are issued before the first use).
-  constexpr int kUnroll = 4;
-  if (ALGO == kOneShot) {
-    float4* wl = reinterpret_cast<float4*>(a.plain ? a.out[rank] : a.w[rank]);
-    for (long long i0 = t0; i0 < a.n_total4; i0 += stride * kUnroll) {
-      float4 acc[kUnroll];
+  // Peer loads have ~2 us latency.  All loads of a batch — every peer x kUnroll float4 — are issued
+  // before the first use, and only then summed in fixed rank order (identical bits everywhere).
+  constexpr int kUnroll = 2;
+  auto gather_sum = [&](long long i0, long long limit, float4 (&acc)[kUnroll]) {
+    float4 v[kMaxRanks][kUnroll];
 #pragma unroll
-      for (int u = 0; u < kUnroll; ++u) acc[u] = zero;
-#pragma unroll 1
-      for (int p = 0; p < world; ++p) {  // fixed rank order: identical bits on every replica
-        float4 v[kUnroll];
+    for (int p = 0; p < kMaxRanks; ++p)
+      if (p < world) {
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
           const long long i = i0 + u * stride;
-          v[u] = i < a.n_total4 ? ld_nc_na_f4(reinterpret_cast<const float4*>(a.g[p]) + i) : zero;
+          v[p][u] = i < limit ? ld_nc_na_f4(reinterpret_cast<const float4*>(a.g[p]) + i) : zero;
         }
-#pragma unroll
-        for (int u = 0; u < kUnroll; ++u) acc[u] = f4_add(acc[u], v[u]);
       }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) acc[u] = zero;
+#pragma unroll
+    for (int p = 0; p < kMaxRanks; ++p)
+      if (p < world) {
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) acc[u] = f4_add(acc[u], v[p][u]);
+      }
+  };
+#pragma unroll 1
+  for (int sg = 0; sg < a.nseg; ++sg) {
+  const long long seg_b = a.seg_begin4[sg], seg_e = a.seg_end4[sg];
+  if (ALGO == kOneShot) {
+    float4* wl = reinterpret_cast<float4*>(a.plain ? a.out[rank] : a.w[rank]);
+    for (long long i0 = seg_b + t0; i0 < seg_e; i0 += stride * kUnroll) {
+      float4 acc[kUnroll];
+      float4 wv[kUnroll];
 #pragma unroll
       for (int u = 0; u < kUnroll; ++u) {
         const long long i = i0 + u * stride;
-        if (i < a.n_total4) wl[i] = a.plain ? acc[u] : apply_update(wl[i], acc[u], i < a.n_params4, a.scale);
+        wv[u] = (!a.plain && i < seg_e) ? wl[i] : zero;
+      }
+      gather_sum(i0, seg_e, acc);
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long i = i0 + u * stride;
+        if (i < seg_e) {
+          wl[i] = a.plain ? acc[u] : apply_update(wv[u], acc[u], i < a.n_params4, a.scale);
+          if (a.gz != nullptr) reinterpret_cast<float4*>(a.gz)[i] = zero;
+        }
+      }
+    }
+  } else if (ALGO == kPull) {
+    // phase 1: reduce my shard, update my own weights (local stores only)
+    const long long per = (seg_e - seg_b + world - 1) / world;
+    const long long s0 = min(seg_e, seg_b + per * rank), s1 = min(seg_e, s0 + per);
+    float4* wl = reinterpret_cast<float4*>(a.w[rank]);
+    for (long long i0 = s0 + t0; i0 < s1; i0 += stride * kUnroll) {
+      float4 acc[kUnroll];
+      float4 wv[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long i = i0 + u * stride;
+        wv[u] = i < s1 ? wl[i] : zero;
+      }
+      gather_sum(i0, s1, acc);
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long i = i0 + u * stride;
+        if (i < s1) wl[i] = apply_update(wv[u], acc[u], i < a.n_params4, a.scale);
+      }
+    }
+    if (a.gz != nullptr)
+      for (long long i = seg_b + t0; i < seg_e; i += stride) reinterpret_cast<float4*>(a.gz)[i] = zero;
+    // phase 2: my shard is complete in my own L2 (gpu-scope fence), tell the peers, then pull
+    // every other owner's shard of the new weights.
+    __threadfence();
+    rank_barrier<false>(a, rank, &s_epoch);
+#pragma unroll 1
+    for (int q = 1; q < world; ++q) {
+      const int p = (rank + q) % world;   // stagger the owners so the pulls spread over all links
+      const long long p0 = min(seg_e, seg_b + per * p), p1 = min(seg_e, p0 + per);
+      const float4* src = reinterpret_cast<const float4*>(a.w[p]);
+      for (long long i0 = p0 + t0; i0 < p1; i0 += stride * 4) {
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const long long i = i0 + u * stride;
+          if (i < p1) v[u] = ld_nc_na_f4(src + i);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const long long i = i0 + u * stride;
+          if (i < p1) wl[i] = v[u];
+        }
       }
     }
   } else {
-    const long long per = (a.n_total4 + world - 1) / world;
-    const long long s0 = min(a.n_total4, per * rank), s1 = min(a.n_total4, s0 + per);
+    const long long per = (seg_e - seg_b + world - 1) / world;
+    const long long s0 = min(seg_e, seg_b + per * rank), s1 = min(seg_e, s0 + per);
     for (long long i0 = s0 + t0; i0 < s1; i0 += stride * kUnroll) {
       float4 acc[kUnroll];
+      float4 wv[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long i = i0 + u * stride;
+        wv[u] = (!a.plain && i < s1) ? reinterpret_cast<const float4*>(a.w[rank])[i] : zero;
+      }
       if (ALGO == kNvls) {
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
@@ -133,50 +238,62 @@ __global__ void __launch_bounds__(kArThreads) allreduce_sgd_kernel(const ArArgs 
           acc[u] = i < s1 ? multimem_ld_reduce_add_f4(reinterpret_cast<const float4*>(a.g_mc) + i) : zero;
         }
       } else {
-#pragma unroll
-        for (int u = 0; u < kUnroll; ++u) acc[u] = zero;
-#pragma unroll 1
-        for (int p = 0; p < world; ++p) {
-          float4 v[kUnroll];
-#pragma unroll
-          for (int u = 0; u < kUnroll; ++u) {
-            const long long i = i0 + u * stride;
-            v[u] = i < s1 ? ld_nc_na_f4(reinterpret_cast<const float4*>(a.g[p]) + i) : zero;
-          }
-#pragma unroll
-          for (int u = 0; u < kUnroll; ++u) acc[u] = f4_add(acc[u], v[u]);
-        }
+        gather_sum(i0, s1, acc);
       }
 #pragma unroll
       for (int u = 0; u < kUnroll; ++u) {
         const long long i = i0 + u * stride;
         if (i >= s1) continue;
-        float4 v = acc[u];
-        if (!a.plain)
-          v = apply_update(reinterpret_cast<const float4*>(a.w[rank])[i], acc[u], i < a.n_params4, a.scale);
+        const float4 v = a.plain ? acc[u] : apply_update(wv[u], acc[u], i < a.n_params4, a.scale);
         if (ALGO == kNvls) {
           multimem_st_f4(reinterpret_cast<float4*>(a.plain ? a.g_mc : a.w_mc) + i, v);
         } else {
-#pragma unroll 1
-          for (int p = 0; p < world; ++p)
-            st_na_f4(reinterpret_cast<float4*>(a.plain ? a.g[p] : a.w[p]) + i, v);
+#pragma unroll
+          for (int p = 0; p < kMaxRanks; ++p)
+            if (p < world) st_na_f4(reinterpret_cast<float4*>(a.plain ? a.g[p] : a.w[p]) + i, v);
         }
       }
     }
   }
+  }  // segments
 
-  rank_barrier(a, rank, &s_epoch);  // B: all reads of G and all writes of W have completed
+  // With double-buffered gradients the buffer just reduced is not touched again until the step
+  // after next, whose own barrier A proves every peer has finished reading it; the other buffer
+  // (consumed one step ago) is what gets zeroed.  One-shot then needs no second barrier at all:
+  // nobody writes remote memory.  Two-shot / NVLS still need B so that every peer's weight writes
+  // have landed before the next forward pass reads W.
+  if (dbg != nullptr && threadIdx.x == 0) {
+    const long long t_end = ar_time_ns();
+    dbg[0] += 1;
+    dbg[1] += s_t[1] - s_t[0];
+    dbg[2] += s_t[2] - s_t[1];
+    dbg[3] += s_t[3] - s_t[2];
+    dbg[4] += t_end - s_t[3];
+  }
+  if (a.gz != nullptr) {
+    if (ALGO == kOneShot || ALGO == kPull) return;
+    float4* gzl = reinterpret_cast<float4*>(a.gz);
+    for (int sg = 0; sg < a.nseg; ++sg)
+      for (long long i = a.seg_begin4[sg] + t0; i < a.seg_end4[sg]; i += stride) gzl[i] = zero;
+    rank_barrier<true>(a, rank, &s_epoch);  // B: all writes of W have completed
+    return;
+  }
+
+  rank_barrier<true>(a, rank, &s_epoch);  // B: all reads of G and all writes of W have completed
 
   if (!a.plain) {
     // zero the stripes of my G that block b of some rank has just consumed
     float4* gl = reinterpret_cast<float4*>(a.g[rank]);
-    if (ALGO == kOneShot) {
-      for (long long i = t0; i < a.n_total4; i += stride) gl[i] = zero;
-    } else {
-      const long long per = (a.n_total4 + world - 1) / world;
-      for (int q = 0; q < world; ++q) {
-        const long long s0 = min(a.n_total4, per * q), s1 = min(a.n_total4, s0 + per);
-        for (long long i = s0 + t0; i < s1; i += stride) gl[i] = zero;
+    for (int sg = 0; sg < a.nseg; ++sg) {
+      const long long seg_b = a.seg_begin4[sg], seg_e = a.seg_end4[sg];
+      if (ALGO == kOneShot) {
+        for (long long i = seg_b + t0; i < seg_e; i += stride) gl[i] = zero;
+      } else {
+        const long long per = (seg_e - seg_b + world - 1) / world;
+        for (int q = 0; q < world; ++q) {
+          const long long s0 = min(seg_e, seg_b + per * q), s1 = min(seg_e, s0 + per);
+          for (long long i = s0 + t0; i < s1; i += stride) gl[i] = zero;
+        }
       }
     }
   }
@@ -198,7 +315,8 @@ extern "C" size_t b2d_allreduce_epoch_bytes(void) { return sizeof(uint32_t) * kM
 extern "C" int b2d_allreduce_pick_algo(int64_t n_total_floats, int world, int have_multicast) {
   const int64_t bytes = n_total_floats * 4;
   if (world <= 2 || bytes <= (256 << 10) / world * 2) return kOneShot;
-  if (have_multicast && bytes >= (1 << 20)) return kNvls;
+  if (bytes <= (4 << 20)) return kPull;            // latency regime: no system-scope release
+  if (have_multicast) return kNvls;                // bandwidth regime: the switch reduces
   return kTwoShot;
 }
 
@@ -223,15 +341,36 @@ extern "C" int b2d_allreduce_sgd(const b2d_allreduce_desc* d, void* stream) {
   a.n_params4 = d->n_params / 4, a.n_total4 = d->n_total / 4;
   a.scale = d->lr / static_cast<float>(d->world);
   a.rank = d->rank, a.world = d->world, a.emulate = d->emulate, a.plain = d->plain;
+  a.gz = d->emulate ? nullptr : static_cast<float*>(d->g_zero);
+  a.dbg = static_cast<long long*>(d->timeline);
+  long long span4 = 0;
+  if (d->nseg <= 0) {
+    a.nseg = 1, a.seg_begin4[0] = 0, a.seg_end4[0] = a.n_total4;
+    span4 = a.n_total4;
+  } else {
+    B2D_REQUIRE(d->nseg <= 2, "allreduce_sgd: at most 2 segments per launch");
+    a.nseg = d->nseg;
+    for (int k = 0; k < d->nseg; ++k) {
+      B2D_REQUIRE(d->seg_begin[k] % 4 == 0 && d->seg_end[k] % 4 == 0 && d->seg_begin[k] <= d->seg_end[k] &&
+                      d->seg_end[k] <= d->n_total,
+                  "allreduce_sgd: bad segment [%lld, %lld)", (long long)d->seg_begin[k], (long long)d->seg_end[k]);
+      a.seg_begin4[k] = d->seg_begin[k] / 4, a.seg_end4[k] = d->seg_end[k] / 4;
+      span4 = std::max(span4, a.seg_end4[k] - a.seg_begin4[k]);
+    }
+  }
+  if (algo < 0 || d->algo < 0) algo = b2d_allreduce_pick_algo(span4 * 4, d->world, d->g_mc != nullptr);
 
-  const long long work4 = algo == kOneShot ? a.n_total4 : (a.n_total4 + d->world - 1) / d->world;
+  const long long work4 = algo == kOneShot ? span4 : (span4 + d->world - 1) / d->world;
   int blocks = d->blocks > 0 ? d->blocks
                              : static_cast<int>(std::min<long long>(
-                                   kMaxArBlocks, std::max<long long>(1, (work4 + kArThreads * 4 - 1) / (kArThreads * 4))));  // ~4 float4 per thread
+                                   kMaxArBlocks, std::max<long long>(1, (work4 + kArThreads * 2 - 1) / (kArThreads * 2))));  // ~2 float4 per thread
   blocks = std::min(blocks, kMaxArBlocks);
   void (*kern)(const ArArgs) = algo == kOneShot  ? allreduce_sgd_kernel<kOneShot>
                                : algo == kTwoShot ? allreduce_sgd_kernel<kTwoShot>
+                               : algo == kPull    ? allreduce_sgd_kernel<kPull>
                                                   : allreduce_sgd_kernel<kNvls>;
+  if (d->emulate) blocks = std::max(1, std::min(blocks, 128 / d->world));  // cooperative: all co-resident
+  B2D_REQUIRE(!(algo == kPull && d->plain), "allreduce_sgd: the pull algorithm is fused-SGD only");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (d->emulate) {
     // All ranks in one launch: the blocks wait on one another, so they must be co-resident.

@@ -21,7 +21,8 @@
 using namespace b2d;
 
 struct b2d_executor {
-  cudaStream_t main = nullptr, copy = nullptr;
+  cudaStream_t main = nullptr, copy = nullptr, side = nullptr;
+  cudaEvent_t fork_ev = nullptr, join_ev = nullptr;
   cudaGraph_t graph[2] = {nullptr, nullptr};
   cudaGraphExec_t exec[2] = {nullptr, nullptr};
   cudaEvent_t ready[2] = {nullptr, nullptr}, consumed[2] = {nullptr, nullptr};
@@ -44,6 +45,9 @@ extern "C" int b2d_exec_create(b2d_executor** out) {
   B2D_REQUIRE(e != nullptr, "exec_create: out of host memory");
   B2D_CUDA_CHECK(cudaStreamCreateWithFlags(&e->main, cudaStreamNonBlocking));
   B2D_CUDA_CHECK(cudaStreamCreateWithFlags(&e->copy, cudaStreamNonBlocking));
+  B2D_CUDA_CHECK(cudaStreamCreateWithFlags(&e->side, cudaStreamNonBlocking));
+  B2D_CUDA_CHECK(cudaEventCreateWithFlags(&e->fork_ev, cudaEventDisableTiming));
+  B2D_CUDA_CHECK(cudaEventCreateWithFlags(&e->join_ev, cudaEventDisableTiming));
   for (int i = 0; i < 2; ++i) {
     B2D_CUDA_CHECK(cudaEventCreateWithFlags(&e->ready[i], cudaEventDisableTiming));
     B2D_CUDA_CHECK(cudaEventCreateWithFlags(&e->consumed[i], cudaEventDisableTiming));
@@ -66,10 +70,30 @@ extern "C" void b2d_exec_destroy(b2d_executor* e) {
   if (e->t1) cudaEventDestroy(e->t1);
   if (e->main) cudaStreamDestroy(e->main);
   if (e->copy) cudaStreamDestroy(e->copy);
+  if (e->side) cudaStreamDestroy(e->side);
+  if (e->fork_ev) cudaEventDestroy(e->fork_ev);
+  if (e->join_ev) cudaEventDestroy(e->join_ev);
   delete e;
 }
 
 extern "C" void* b2d_exec_stream(b2d_executor* e) { return e ? e->main : nullptr; }
+
+// Side branch inside a step (bucketed communication overlapped with compute): work launched on
+// b2d_exec_side_stream() between fork and join runs concurrently with the main stream; inside a
+// capture the two calls become the fork / join edges of the step graph.
+extern "C" void* b2d_exec_side_stream(b2d_executor* e) { return e ? e->side : nullptr; }
+extern "C" int b2d_exec_fork(b2d_executor* e) {
+  B2D_REQUIRE(e != nullptr, "exec_fork: null executor");
+  B2D_CUDA_CHECK(cudaEventRecord(e->fork_ev, e->main));
+  B2D_CUDA_CHECK(cudaStreamWaitEvent(e->side, e->fork_ev, 0));
+  return B2D_OK;
+}
+extern "C" int b2d_exec_join(b2d_executor* e) {
+  B2D_REQUIRE(e != nullptr, "exec_join: null executor");
+  B2D_CUDA_CHECK(cudaEventRecord(e->join_ev, e->side));
+  B2D_CUDA_CHECK(cudaStreamWaitEvent(e->main, e->join_ev, 0));
+  return B2D_OK;
+}
 
 extern "C" int b2d_exec_set_io(b2d_executor* e, int slot, void* x_dev, size_t x_bytes, void* y_dev,
                                size_t y_bytes) {

@@ -33,6 +33,8 @@ class StepProgram:
     forward: list[Callable[[], None]] = field(default_factory=list)
     backward: list[Callable[[], None]] = field(default_factory=list)
     logits: torch.Tensor | None = None
+    early_forward: int = 0            # forward launches that need only the FIRST parametrised layer
+    first_param_layer: int = -1       # index of that layer (bucket boundary for overlapped all-reduce)
     description: list[str] = field(default_factory=list)
     keep: list = field(default_factory=list)        # buffers / plans kept alive
 
@@ -80,6 +82,11 @@ def lower(layers, batch: int, be, layout: ArenaLayout, params, grads, x_in, labe
             prog.description.append(f"flatten -> {tuple(cur.shape)} (view)")
             i += 1
             continue
+        if isinstance(layer, (L.Conv2D, L.Dense)):
+            if prog.first_param_layer < 0:
+                prog.first_param_layer = i
+            elif prog.early_forward == 0:
+                prog.early_forward = len(prog.forward)     # everything so far needs only layer 0's weights
         if isinstance(layer, L.Conv2D):
             w, b = pview(params, i)
             dw, db = pview(grads, i)

@@ -27,6 +27,10 @@ def _declare_exec(lib):
     lib.b2d_exec_destroy.restype = None
     lib.b2d_exec_stream.argtypes = [vp]
     lib.b2d_exec_stream.restype = vp
+    lib.b2d_exec_side_stream.argtypes = [vp]
+    lib.b2d_exec_side_stream.restype = vp
+    lib.b2d_exec_fork.argtypes = [vp]
+    lib.b2d_exec_join.argtypes = [vp]
     lib.b2d_exec_set_io.argtypes = [vp, i, vp, sz, vp, sz]
     lib.b2d_exec_set_metrics.argtypes = [vp, vp, sz, vp, i]
     lib.b2d_exec_begin_capture.argtypes = [vp]
@@ -59,13 +63,17 @@ class Trainer:
             self.be = CpuBackend()
         self.comm = strategy.make_comm(self.layout.n_total, self.be)
         self.params = self.comm.alloc(self.layout.n_total, self.be)
-        self.grads = self.comm.alloc(self.layout.n_total, self.be)
+        self.use_graph = bool(use_graph and self.backend_name == "cuda" and self.comm.capturable)
+        # Gradient arena(s): communicators that ping-pong gradients get one per graph slot.
+        n_g = self.comm.num_grad_buffers if self.use_graph else 1
+        self.grad_bufs = [self.comm.alloc(self.layout.n_total, self.be) for _ in range(n_g)]
+        self.grads = self.grad_bufs[0]
         init = torch.from_numpy(self.layout.initial_values(self.layers, strategy.seed))
         self.params.copy_(init)
-        self.grads.zero_()
+        for g in self.grad_bufs:
+            g.zero_()
         if self.comm.world > 1 and not self.comm.all_equal(self.params):
             raise RuntimeError("replicas were not initialised identically (mirrored variables differ)")
-        self.use_graph = bool(use_graph and self.backend_name == "cuda" and self.comm.capturable)
         self._exec = None
         self._build()
 
@@ -104,12 +112,32 @@ class Trainer:
         tail = self.params[lay.n_params:lay.n_total]
         nl.check(lib.b2d_exec_set_metrics(h, tail.data_ptr(), TAIL * 4, self.metrics_host.data_ptr(),
                                           self.ring_len), "b2d_exec_set_metrics")
+        self.side_stream = torch.cuda.ExternalStream(lib.b2d_exec_side_stream(h), device=self.be.device)
+        self.pipelined = []          # per slot: {"small", "deferred", "flush"} or empty
         torch.cuda.synchronize(self.be.device)
+        import os
         with torch.cuda.stream(self.stream):
             for slot in range(n_slots):
-                prog = lower(self.layers, self.batch, be, lay, self.params, self.grads,
+                g_slot = self.grad_bufs[slot % len(self.grad_bufs)]
+                prog = lower(self.layers, self.batch, be, lay, self.params, g_slot,
                              self.x_in[slot], self.y_in[slot])
-                upd = self.comm.make_update(be, self.params, self.grads, lay.n_params, self.lr)
+                if len(self.grad_bufs) > 1:
+                    g_other = self.grad_bufs[(slot + 1) % 2]
+                    upd = self.comm.make_update(be, self.params, g_slot, lay.n_params, self.lr,
+                                                grads_other=g_other)
+                    # Optional (B200DIST_PIPELINE=1) bucketed, cross-step-overlapped update: everything
+                    # but the first layer's parameters is reduced on a side branch while the NEXT
+                    # step's first kernels run.  Measured SLOWER for the README model (the overlap
+                    # window — one 5 us kernel — is shorter than the bucket's barrier + transfer), so
+                    # it is off by default; it pays once the first layer's forward is long.
+                    deferred_begin = self._deferred_begin(prog)
+                    if (self.use_graph and deferred_begin is not None
+                            and hasattr(self.comm, "make_pipelined_updates")
+                            and os.environ.get("B200DIST_PIPELINE", "0") == "1"):
+                        self.pipelined.append(self.comm.make_pipelined_updates(
+                            be, self.params, g_slot, g_other, lay.n_params, self.lr, deferred_begin))
+                else:
+                    upd = self.comm.make_update(be, self.params, g_slot, lay.n_params, self.lr)
                 self.progs.append(prog)
                 self.updates.append(upd)
                 nl.check(lib.b2d_exec_set_io(h, slot, self.x_in[slot].data_ptr(), self.x_bytes,
@@ -118,17 +146,52 @@ class Trainer:
                 # warm every kernel once outside capture (module load, smem attributes), on zero
                 # inputs with the update skipped so the weights are untouched
                 self.progs[0].run()
-                self.grads.zero_()
+                self.grad_bufs[0].zero_()
                 self.stream.synchronize()
                 for slot in range(n_slots):
+                    prog = self.progs[slot]
                     nl.check(lib.b2d_exec_begin_capture(h), "b2d_exec_begin_capture")
-                    self.progs[slot].run()
-                    self.updates[slot]()
+                    if len(self.pipelined) == n_slots:
+                        pipe = self.pipelined[slot]
+                        nl.check(lib.b2d_exec_fork(h), "b2d_exec_fork")
+                        with torch.cuda.stream(self.side_stream):
+                            pipe["deferred"]()            # previous step's big bucket
+                        for f in prog.forward[:prog.early_forward]:
+                            f()                            # needs only the first layer's weights
+                        nl.check(lib.b2d_exec_join(h), "b2d_exec_join")
+                        for f in prog.forward[prog.early_forward:]:
+                            f()
+                        for f in prog.backward:
+                            f()
+                        pipe["small"]()                    # the only communication on the critical path
+                    else:
+                        prog.run()
+                        self.updates[slot]()
                     nl.check(lib.b2d_exec_end_capture(h, slot), "b2d_exec_end_capture")
                 self.kernels_per_step = int(lib.b2d_exec_graph_nodes(h, 0))
             else:
                 self.kernels_per_step = None
         self.stream.synchronize()
+
+    def _deferred_begin(self, prog):
+        """Arena offset where the deferred bucket starts (end of the first parametrised layer), or
+        None when the model has nothing to defer."""
+        if prog.first_param_layer < 0 or prog.early_forward <= 0:
+            return None
+        later = [s for s in self.layout.slots if s.layer_index > prog.first_param_layer]
+        if not later:
+            return None
+        begin = min(s.offset for s in later)
+        return begin if 0 < begin < self.layout.n_params else None
+
+    def _flush_pending(self):
+        """Apply the deferred bucket of the last executed step (all replicas call this together)."""
+        if self.pipelined and self._pending_slot is not None:
+            with torch.cuda.stream(self.stream):
+                self.pipelined[self._pending_slot]["flush"]()
+            self._pending_slot = None
+
+    _pending_slot = None
 
     # ------------------------------------------------------------------------------
     def describe(self) -> list[str]:
@@ -142,14 +205,23 @@ class Trainer:
         B, r = self.batch, self.comm.rank
         row = int(np.prod(self.input_shape))
         if self._exec is not None and self.use_graph:
-            el = C.c_float(0.0)
             xs = x_src.data_ptr() + r * B * row * 4
             ys = y_src.data_ptr() + r * B * 4
             from .._native import cuda_lib as nl
+            if timed:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(self.stream)
             nl.check(self._lib.b2d_exec_run(self._exec, xs, global_batch * row * 4, ys, global_batch * 4,
-                                            first_step, steps_in_src, n_steps, 1,
-                                            C.byref(el) if timed else None), "b2d_exec_run")
-            return el.value if timed else None
+                                            first_step, steps_in_src, n_steps, 0, None), "b2d_exec_run")
+            if n_steps > 0 and self.pipelined:
+                self._pending_slot = (self.steps_done() - 1) & 1
+                self._flush_pending()          # inside the timed region: the work is not skipped
+            if timed:
+                e1.record(self.stream)
+                e1.synchronize()
+                return e0.elapsed_time(e1)
+            self.sync()
+            return None
         # eager loops (CPU backend; CUDA with a non-capturable communicator)
         t0 = time.perf_counter()
         cuda = self.backend_name == "cuda"

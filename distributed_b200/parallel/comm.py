@@ -22,6 +22,7 @@ import torch
 class SingleComm:
     name = "single"
     world, rank = 1, 0
+    num_grad_buffers = 1
 
     def alloc(self, n, be):
         return be.alloc((n,))
@@ -46,6 +47,7 @@ class ShmComm:
     """CPU replicas on one host; fused all-reduce + average + SGD through shared memory."""
     name = "shm"
     capturable = False
+    num_grad_buffers = 1
 
     def __init__(self, job_id: str, rank: int, world: int, capacity: int, timeout_s: float = 120.0):
         from .._native import cpu_lib
@@ -110,6 +112,7 @@ class TorchDistComm:
     the product path is SymmComm.
     """
     capturable = False
+    num_grad_buffers = 1
 
     def __init__(self, group=None):
         import torch.distributed as dist

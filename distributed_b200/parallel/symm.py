@@ -21,8 +21,8 @@ import torch
 from .._native import cuda_lib as nl
 
 MAX_RANKS = 8
-ALGOS = {"oneshot": 0, "one_shot": 0, "twoshot": 1, "two_shot": 1, "nvls": 2, "auto": -1}
-ALGO_NAMES = {0: "one-shot", 1: "two-shot", 2: "NVLS multicast"}
+ALGOS = {"oneshot": 0, "one_shot": 0, "twoshot": 1, "two_shot": 1, "nvls": 2, "pull": 3, "auto": -1}
+ALGO_NAMES = {0: "one-shot", 1: "two-shot", 2: "NVLS multicast", 3: "two-shot pull"}
 
 _VP8 = C.c_void_p * MAX_RANKS
 
@@ -32,7 +32,8 @@ class AllreduceDesc(C.Structure):
                 ("w_mc", C.c_void_p), ("g_mc", C.c_void_p),
                 ("n_params", C.c_int64), ("n_total", C.c_int64), ("lr", C.c_float),
                 ("rank", C.c_int), ("world", C.c_int), ("algo", C.c_int), ("emulate", C.c_int),
-                ("plain", C.c_int), ("blocks", C.c_int)]
+                ("plain", C.c_int), ("blocks", C.c_int), ("g_zero", C.c_void_p), ("timeline", C.c_void_p),
+                ("seg_begin", C.c_int64 * 2), ("seg_end", C.c_int64 * 2), ("nseg", C.c_int)]
 
 
 def _declare(lib):
@@ -89,9 +90,10 @@ class SymmComm:
         # layout of the symmetric block (same offsets on every replica)
         self.off_w = 0
         self.off_g = _align(arena_bytes, 4096)
-        self.off_sig = self.off_g + _align(arena_bytes, 4096)
-        self.off_epoch = self.off_sig + _align(self.sig_bytes, 4096)
-        total = self.off_epoch + _align(self.epoch_bytes, 4096)
+        self.off_g2 = self.off_g + _align(arena_bytes, 4096)       # second gradient buffer (ping-pong)
+        self.off_sig = self.off_g2 + _align(arena_bytes, 4096)
+        self.off_epoch = self.off_sig + _align(self.sig_bytes * self.CHANNELS, 4096)
+        total = self.off_epoch + _align(self.epoch_bytes * self.CHANNELS, 4096)
         h = C.c_void_p()
         torch.cuda.set_device(self.device)
         dist.barrier()
@@ -145,28 +147,42 @@ class SymmComm:
         t._b2d_owner = self       # the mapping lives as long as the communicator
         return t
 
+    CHANNELS = 4              # independent signal pads: kernels of different buckets may overlap
+    num_grad_buffers = 2      # gradients ping-pong between two symmetric buffers (one per graph slot)
+
     def alloc(self, n, be):
-        """First call: weight arena; second call: gradient arena (both symmetric)."""
+        """Calls in order: weight arena, gradient arena 0, gradient arena 1 (all symmetric)."""
         assert n <= self.n, "arena larger than the communicator's capacity"
-        off = (self.off_w, self.off_g)[self._next]
+        off = (self.off_w, self.off_g, self.off_g2)[self._next]
         self._next += 1
         return self._tensor(off, n)
 
-    def make_update(self, be, params, grads, n_params, lr):
+    def make_update(self, be, params, grads, n_params, lr, grads_other=None, segments=None, channel=0,
+                    algo=None):
+        """Fused all-reduce+SGD over ``grads``; ``grads_other`` (the other ping-pong buffer of this
+        rank) is zeroed by the same kernel, which lets one-shot run with a single barrier.
+        ``segments``: up to two [begin, end) float ranges (bucketing); ``channel``: signal pad."""
         d = AllreduceDesc()
+        off_g = self.off_g if grads.data_ptr() == self.base[self.rank] + self.off_g else self.off_g2
         for p in range(self.world):
             d.w[p] = self.base[p] + self.off_w
-            d.g[p] = self.base[p] + self.off_g
-            d.sig[p] = self.base[p] + self.off_sig
-            d.epoch[p] = self.base[p] + self.off_epoch
+            d.g[p] = self.base[p] + off_g
+            d.sig[p] = self.base[p] + self.off_sig + channel * self.sig_bytes
+            d.epoch[p] = self.base[p] + self.off_epoch + channel * self.epoch_bytes
         if self.mc_base:
             d.w_mc = self.mc_base + self.off_w
-            d.g_mc = self.mc_base + self.off_g
+            d.g_mc = self.mc_base + off_g
+        d.g_zero = grads_other.data_ptr() if grads_other is not None else None
         n_total = params.numel()
         assert params.data_ptr() == d.w[self.rank] and grads.data_ptr() == d.g[self.rank]
         assert n_total % 4 == 0 and n_params % 4 == 0
         d.n_params, d.n_total, d.lr = n_params, n_total, float(lr)
-        d.rank, d.world, d.algo, d.emulate, d.plain, d.blocks = self.rank, self.world, self.algo, 0, 0, 0
+        d.rank, d.world, d.emulate, d.plain, d.blocks = self.rank, self.world, 0, 0, 0
+        d.algo = self.algo if algo is None else algo
+        if segments:
+            d.nseg = len(segments)
+            for k, (b0, e0) in enumerate(segments):
+                d.seg_begin[k], d.seg_end[k] = b0, e0
         self._descs = getattr(self, "_descs", []) + [d]
         lib = self._lib
 
@@ -174,6 +190,28 @@ class SymmComm:
             nl.check(lib.b2d_allreduce_sgd(C.byref(d), torch.cuda.current_stream().cuda_stream),
                      "b2d_allreduce_sgd")
         return run
+
+    def make_pipelined_updates(self, be, params, g_slot, g_other, n_params, lr, deferred_begin):
+        """Bucketed update that hides the big bucket behind compute (see engine/trainer.py).
+
+        * ``small``    — [0, deferred_begin) + metric tail of THIS step's gradients, at the end of
+                          the step: one-shot, one barrier (the only communication on the critical path).
+        * ``deferred`` — [deferred_begin, n_params) of the PREVIOUS step's gradients (other ping-pong
+                          buffer), launched on the side stream at the start of the step; it must
+                          finish before the first kernel that reads those weights.
+        * ``flush``    — applies the still-pending deferred bucket of this slot (end of a run).
+        """
+        n_total = params.numel()
+        seg_small = [(0, deferred_begin), (n_params, n_total)]
+        seg_def = [(deferred_begin, n_params)]
+        return {
+            "small": self.make_update(be, params, g_slot, n_params, lr, grads_other=g_other,
+                                      segments=seg_small, channel=0, algo=0),
+            "deferred": self.make_update(be, params, g_other, n_params, lr, grads_other=g_slot,
+                                         segments=seg_def, channel=1),
+            "flush": self.make_update(be, params, g_slot, n_params, lr, grads_other=None,
+                                      segments=seg_def, channel=2),
+        }
 
     # -- control plane ------------------------------------------------------------------
     def barrier(self):

@@ -207,6 +207,13 @@ typedef struct b2d_allreduce_desc {
   int emulate;      /* all ranks in one cooperative launch on one GPU (tests) */
   int plain;        /* sum only: no SGD, no zeroing                     */
   int blocks;       /* 0 = automatic                                    */
+  void* g_zero;     /* double-buffered gradients: this rank's OTHER gradient buffer, zeroed by
+                       the kernel (one-shot then runs with a single cross-GPU barrier); NULL =
+                       single buffer, zeroed in place after a second barrier              */
+  void* timeline;   /* optional debug: 8 x int64 globaltimer stamps per block, or NULL       */
+  int64_t seg_begin[2]; /* bucketing: up to two [begin, end) float ranges of the arenas handled  */
+  int64_t seg_end[2];   /* by this launch (multiples of 4); nseg == 0 means the whole arena      */
+  int nseg;
 } b2d_allreduce_desc;
 size_t b2d_allreduce_signal_bytes(void);
 size_t b2d_allreduce_epoch_bytes(void);
@@ -222,6 +229,9 @@ typedef struct b2d_executor b2d_executor;
 int b2d_exec_create(b2d_executor** out);
 void b2d_exec_destroy(b2d_executor* e);
 void* b2d_exec_stream(b2d_executor* e);
+void* b2d_exec_side_stream(b2d_executor* e);   /* concurrent branch of a step (bucketed all-reduce) */
+int b2d_exec_fork(b2d_executor* e);            /* side stream starts after everything on main so far */
+int b2d_exec_join(b2d_executor* e);            /* main continues after everything on side so far     */
 int b2d_exec_set_io(b2d_executor* e, int slot, void* x_dev, size_t x_bytes, void* y_dev, size_t y_bytes);
 int b2d_exec_set_metrics(b2d_executor* e, const void* metrics_dev, size_t bytes, void* pinned_ring,
                          int ring_len);

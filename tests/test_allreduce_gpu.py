@@ -45,7 +45,7 @@ def _emulated(world, n_params, n_tail, algo, lr=0.1, rounds=2, blocks=0):
 
 
 @pytest.mark.parametrize("world", [2, 3, 4, 8])
-@pytest.mark.parametrize("algo", [0, 1])
+@pytest.mark.parametrize("algo", [0, 1, 3])
 @pytest.mark.parametrize("n_params", [64, 347200, 1000 * 4 + 4])
 def test_emulated_fused_allreduce_sgd(world, algo, n_params):
     _emulated(world, n_params, 4, algo)
@@ -62,6 +62,7 @@ def test_algo_dispatch_by_size():
     lib = nl.lib()
     symm._declare(lib)
     assert lib.b2d_allreduce_pick_algo(1024, 8, 0) == 0            # 4 KB: one-shot
-    assert lib.b2d_allreduce_pick_algo(347204, 8, 0) == 1          # README gradient: two-shot
+    assert lib.b2d_allreduce_pick_algo(347204, 8, 0) == 3          # README gradient: latency-optimised pull
     assert lib.b2d_allreduce_pick_algo(1 << 24, 8, 1) == 2         # 64 MB with multicast: NVLS
+    assert lib.b2d_allreduce_pick_algo(1 << 24, 8, 0) == 1         # 64 MB without multicast: two-shot
     assert lib.b2d_allreduce_pick_algo(1 << 24, 2, 0) == 0         # 2 ranks: one-shot == two-shot traffic

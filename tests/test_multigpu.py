@@ -43,7 +43,7 @@ def _ngpu():
     return torch.cuda.device_count()
 
 
-@pytest.mark.parametrize("algo", ["oneshot", "twoshot", "nvls", "auto"])
+@pytest.mark.parametrize("algo", ["oneshot", "twoshot", "nvls", "pull", "auto"])
 def test_replicas_stay_identical(algo):
     from distributed_b200.launch import barrier_apply
     n = min(_ngpu(), 8)
