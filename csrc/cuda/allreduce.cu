@@ -201,23 +201,25 @@ __global__ void __launch_bounds__(kArThreads) allreduce_sgd_kernel(const ArArgs 
     // every other owner's shard of the new weights.
     __threadfence();
     rank_barrier<false>(a, rank, &s_epoch);
-#pragma unroll 1
-    for (int q = 1; q < world; ++q) {
-      const int p = (rank + q) % world;   // stagger the owners so the pulls spread over all links
-      const long long p0 = min(seg_e, seg_b + per * p), p1 = min(seg_e, p0 + per);
-      const float4* src = reinterpret_cast<const float4*>(a.w[p]);
-      for (long long i0 = p0 + t0; i0 < p1; i0 += stride * 4) {
-        float4 v[4];
+    // One flat loop over "every element that is not mine", 4 remote loads in flight per thread;
+    // consecutive strides of the grid hit different owners, so all links are busy at once.
+    const long long others = per * (world - 1);
+    for (long long j0 = t0; j0 < others; j0 += stride * 4) {
+      float4 v[4];
+      long long idx[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const long long i = i0 + u * stride;
-          if (i < p1) v[u] = ld_nc_na_f4(src + i);
-        }
+      for (int u = 0; u < 4; ++u) {
+        const long long j = j0 + u * stride;
+        const int q = 1 + static_cast<int>(j / per);
+        const int p = (rank + q) % world;            // stagger the owners across ranks
+        idx[u] = seg_b + per * p + (j - (long long)(q - 1) * per);
+        if (j < others && idx[u] < seg_e)
+          v[u] = ld_nc_na_f4(reinterpret_cast<const float4*>(a.w[p]) + idx[u]);
+      }
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const long long i = i0 + u * stride;
-          if (i < p1) wl[i] = v[u];
-        }
+      for (int u = 0; u < 4; ++u) {
+        const long long j = j0 + u * stride;
+        if (j < others && idx[u] < seg_e) wl[idx[u]] = v[u];
       }
     }
   } else {
@@ -314,9 +316,12 @@ extern "C" size_t b2d_allreduce_epoch_bytes(void) { return sizeof(uint32_t) * kM
 // it the (N-1)/N traffic of two-shot (or S/N of NVLS) wins on bandwidth.
 extern "C" int b2d_allreduce_pick_algo(int64_t n_total_floats, int world, int have_multicast) {
   const int64_t bytes = n_total_floats * 4;
+  // Measured on 8 x B200 (profiles/r01_allreduce.md): one-shot (single barrier, reads only) wins
+  // at 2 ranks and for tiny messages; with multicast bound the switch reduction wins from
+  // ~256 KB up at >= 4 ranks; without it the pull variant is the latency choice up to a few MB.
   if (world <= 2 || bytes <= (256 << 10) / world * 2) return kOneShot;
-  if (bytes <= (4 << 20)) return kPull;            // latency regime: no system-scope release
-  if (have_multicast) return kNvls;                // bandwidth regime: the switch reduces
+  if (have_multicast && bytes >= (256 << 10)) return kNvls;
+  if (bytes <= (4 << 20)) return kPull;
   return kTwoShot;
 }
 
@@ -360,7 +365,8 @@ extern "C" int b2d_allreduce_sgd(const b2d_allreduce_desc* d, void* stream) {
   }
   if (algo < 0 || d->algo < 0) algo = b2d_allreduce_pick_algo(span4 * 4, d->world, d->g_mc != nullptr);
 
-  const long long work4 = algo == kOneShot ? span4 : (span4 + d->world - 1) / d->world;
+  // grid sized by the largest phase: one-shot and the pull phase touch the whole span per rank
+  const long long work4 = (algo == kOneShot || algo == kPull) ? span4 : (span4 + d->world - 1) / d->world;
   int blocks = d->blocks > 0 ? d->blocks
                              : static_cast<int>(std::min<long long>(
                                    kMaxArBlocks, std::max<long long>(1, (work4 + kArThreads * 2 - 1) / (kArThreads * 2))));  // ~2 float4 per thread
