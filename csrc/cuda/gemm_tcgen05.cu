@@ -406,8 +406,8 @@ static int pick_block_n(const b2d_gemm_desc& d) {
   if (d.N <= 32 && !(d.dtype == B2D_BF16 && d.b_mn_major)) return 32;
   if (d.N <= 64) return 64;
   const int mt = ceil_div(d.M, kBlockM);
-  // Prefer the widest tile that still yields at least one full wave of CTAs.
-  if (mt * ceil_div(d.N, 256) >= 148) return 256;
+  // Prefer the widest tile that still yields at least one full wave of CTAs (never wider than N).
+  if (d.N > 128 && mt * ceil_div(d.N, 256) >= 148) return 256;
   if (mt * ceil_div(d.N, 128) >= 120) return 128;
   // Few tiles: narrower tiles double the CTA count and halve each CTA's epilogue.
   if (mt * ceil_div(d.N, 128) < 74) return 64;

@@ -391,6 +391,41 @@ __global__ void maxpool2_bwd_kernel(const float* __restrict__ dy, const uint8_t*
   }
 }
 
+// Same, four channels per thread (C % 4 == 0): 16-byte loads/stores, one index decode per 4 outputs.
+__global__ void __launch_bounds__(256) maxpool2_bwd_v4_kernel(const float4* __restrict__ dy,
+                                                               const uchar4* __restrict__ code,
+                                                               const float4* __restrict__ y_pooled,
+                                                               float4* __restrict__ dx, int N, int H, int W,
+                                                               int C4, int PH, int PW, int act_relu) {
+  pdl_wait();
+  pdl_trigger();
+  const size_t total = (size_t)N * H * W * C4;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const int c = i % C4;
+    size_t t = i / C4;
+    const int w = t % W;
+    t /= W;
+    const int hh = t % H;
+    const int n = t / H;
+    const int ph = hh >> 1, pw = w >> 1;
+    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (ph < PH && pw < PW) {
+      const size_t o = (((size_t)n * PH + ph) * PW + pw) * C4 + c;
+      const uchar4 cd = code[o];
+      const float4 d = dy[o];
+      const unsigned char me = (unsigned char)((hh & 1) * 2 + (w & 1));
+      float4 yv = make_float4(1.f, 1.f, 1.f, 1.f);
+      if (act_relu) yv = y_pooled[o];
+      g.x = (cd.x == me && yv.x > 0.f) ? d.x : 0.f;
+      g.y = (cd.y == me && yv.y > 0.f) ? d.y : 0.f;
+      g.z = (cd.z == me && yv.z > 0.f) ? d.z : 0.f;
+      g.w = (cd.w == me && yv.w > 0.f) ? d.w : 0.f;
+    }
+    dx[i] = g;
+  }
+}
+
 // Column sums: db[n] += sum_m dy[m][n]   (bias gradient)                         [K6/K7]
 __global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ dy,
                                                       float* __restrict__ db, int M, int N,
@@ -411,6 +446,35 @@ __global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ d
 #pragma unroll
     for (int k = 0; k < 8; ++k) t += part[k][threadIdx.x];
     atomicAdd(&db[col], t);
+  }
+}
+
+// Vectorised column sums for N % 4 == 0: a warp reads one 512-byte row segment (32 x float4)
+// per step, 8 warps walk different rows; partial sums meet in shared memory, one atomic per column.
+__global__ void __launch_bounds__(256) colsum_v4_kernel(const float* __restrict__ dy, float* __restrict__ db,
+                                                         int M, int N, int rows_per_cta) {
+  pdl_wait();
+  pdl_trigger();
+  __shared__ float4 part[8][32];
+  const int lane = threadIdx.x & 31, wy = threadIdx.x >> 5;
+  const int col = blockIdx.x * 128 + lane * 4;
+  const int r0 = blockIdx.y * rows_per_cta, r1 = min(M, r0 + rows_per_cta);
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (col < N)
+    for (int r = r0 + wy; r < r1; r += 8) {
+      const float4 v = *reinterpret_cast<const float4*>(dy + (size_t)r * N + col);
+      s.x += v.x, s.y += v.y, s.z += v.z, s.w += v.w;
+    }
+  part[wy][lane] = s;
+  __syncthreads();
+  if (wy == 0 && col < N) {
+    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t.x += part[k][lane].x, t.y += part[k][lane].y, t.z += part[k][lane].z, t.w += part[k][lane].w;
+    atomicAdd(&db[col], t.x);
+    atomicAdd(&db[col + 1], t.y);
+    atomicAdd(&db[col + 2], t.z);
+    atomicAdd(&db[col + 3], t.w);
   }
 }
 
@@ -675,8 +739,10 @@ extern "C" int b2d_dense_xent_head(const float* h, const float* w, const float* 
     attr_set = true;
   }
   // One pass of 8 rows per CTA at small batch; several passes per CTA once the grid is full.
+  // Every CTA ends with K*C global atomics onto the same addresses: keep the CTA count modest
+  // (<= 64) once the batch is large, trading a little parallelism for 2-4x fewer atomics.
   int rows = kHeadRows;
-  if (B > kHeadRows * 148 * 2) rows = ceil_div(ceil_div(B, 148 * 2), kHeadRows) * kHeadRows;
+  if (B > kHeadRows * 64) rows = ceil_div(ceil_div(B, 64), kHeadRows) * kHeadRows;
   B2D_CUDA_CHECK(launch_pdl(dense_xent_head_kernel, dim3(ceil_div(B, rows)), dim3(256), smem, static_cast<cudaStream_t>(stream), h, w, bias, labels, logits_out, dh, dw, db, dh_colsum, metrics, B, K, C, grad_scale, relu_mask, rows));
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;
@@ -700,12 +766,26 @@ extern "C" int b2d_maxpool2_fwd(const float* x, float* y, uint8_t* code, int N, 
 extern "C" int b2d_maxpool2_bwd(const float* dy, const uint8_t* code, const float* y_pooled, float* dx,
                                 int N, int H, int W, int C, int act_relu, void* stream) {
   const int PH = H / 2, PW = W / 2;
+  if (C % 4 == 0) {
+    const size_t n4 = (size_t)N * H * W * (C / 4);
+    B2D_CUDA_CHECK(launch_pdl(maxpool2_bwd_v4_kernel, dim3(grid_for(n4, 256, 148 * 32)), dim3(256), 0,
+                              static_cast<cudaStream_t>(stream), reinterpret_cast<const float4*>(dy),
+                              reinterpret_cast<const uchar4*>(code), reinterpret_cast<const float4*>(y_pooled),
+                              reinterpret_cast<float4*>(dx), N, H, W, C / 4, PH, PW, act_relu));
+    return B2D_OK;
+  }
   B2D_CUDA_CHECK(launch_pdl(maxpool2_bwd_kernel, dim3(grid_for((size_t)N * H * W * C)), dim3(256), 0, static_cast<cudaStream_t>(stream), dy, code, y_pooled, dx, N, H, W, C, PH, PW, act_relu));
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;
 }
 
 extern "C" int b2d_colsum(const float* dy, float* db, int M, int N, void* stream) {
+  if (N % 4 == 0 && M >= 1024) {
+    const int rows_v4 = max(64, ceil_div(M, 512));
+    B2D_CUDA_CHECK(launch_pdl(colsum_v4_kernel, dim3(ceil_div(N, 128), ceil_div(M, rows_v4)), dim3(256), 0,
+                              static_cast<cudaStream_t>(stream), dy, db, M, N, rows_v4));
+    return B2D_OK;
+  }
   const int rows = max(8, ceil_div(M, 64));
   const dim3 grid(ceil_div(N, 32), ceil_div(M, rows));
   B2D_CUDA_CHECK(launch_pdl(colsum_kernel, dim3(grid), dim3(256), 0, static_cast<cudaStream_t>(stream), dy, db, M, N, rows));
