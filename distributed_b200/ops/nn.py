@@ -35,6 +35,13 @@ def _lib():
         lib.b2d_sgemm_simt.argtypes = [vp, i64, i64, vp, i64, i64, vp, i64, vp, i, i, i, i, i, vp]
         lib.b2d_sgd_apply.argtypes = [vp, vp, sz, sz, f, vp]
         lib.b2d_cast_f32_bf16.argtypes = [vp, vp, sz, vp]
+        lib.b2d_bn_fwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, i, i, f, f, i, vp]
+        lib.b2d_bn_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp]
+        lib.b2d_add_act.argtypes = [vp, vp, vp, sz, i, vp]
+        lib.b2d_maxpool_fwd.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, vp]
+        lib.b2d_maxpool_bwd.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, vp]
+        lib.b2d_gap_fwd.argtypes = [vp, vp, i, i, i, vp]
+        lib.b2d_gap_bwd.argtypes = [vp, vp, i, i, i, vp]
         _declared = True
     return lib
 
@@ -142,3 +149,42 @@ def sgd_apply(w, g, n_params, lr):
 
 def cast_f32_bf16(src, dst):
     nl.check(_lib().b2d_cast_f32_bf16(_p(src), _p(dst), src.numel(), _s()), "cast_f32_bf16")
+
+
+# ---- ResNet-family extras (BASELINE.json config 4) ---------------------------------------
+def bn_fwd(x2d, gamma, beta, stats, saved, moving, y2d, eps, momentum, relu):
+    """Training-mode BatchNorm over rows of x2d [M, C] (+ReLU).  stats [2C] scratch (kept zero),
+    saved [2C] receives mean / rstd, moving [2C] (mean, variance) is updated in place."""
+    M, Cc = x2d.shape
+    nl.check(_lib().b2d_bn_fwd(_p(x2d), _p(gamma), _p(beta), _p(stats), _p(saved), _p(moving), _p(y2d),
+                               M, Cc, float(eps), float(momentum), int(relu), _s()), "bn_fwd")
+
+
+def bn_bwd(x2d, y2d, dy2d, gamma, saved, red, dx2d, dgamma, dbeta, relu):
+    M, Cc = x2d.shape
+    nl.check(_lib().b2d_bn_bwd(_p(x2d), _p(y2d), _p(dy2d), _p(gamma), _p(saved), _p(red), _p(dx2d),
+                               _p(dgamma), _p(dbeta), M, Cc, int(relu), _s()), "bn_bwd")
+
+
+def add_act(a, b, out, relu):
+    nl.check(_lib().b2d_add_act(_p(a), _p(b), _p(out), a.numel(), int(relu), _s()), "add_act")
+
+
+def maxpool_fwd(x, y, code, k, s, p):
+    N, H, W, Cc = x.shape
+    nl.check(_lib().b2d_maxpool_fwd(_p(x), _p(y), _p(code), N, H, W, Cc, k, s, p, _s()), "maxpool_fwd")
+
+
+def maxpool_bwd(dy, code, dx, k, s, p):
+    N, H, W, Cc = dx.shape
+    nl.check(_lib().b2d_maxpool_bwd(_p(dy), _p(code), _p(dx), N, H, W, Cc, k, s, p, _s()), "maxpool_bwd")
+
+
+def gap_fwd(x, y):
+    N, H, W, Cc = x.shape
+    nl.check(_lib().b2d_gap_fwd(_p(x), _p(y), N, H * W, Cc, _s()), "gap_fwd")
+
+
+def gap_bwd(dy, dx):
+    N, H, W, Cc = dx.shape
+    nl.check(_lib().b2d_gap_bwd(_p(dy), _p(dx), N, H * W, Cc, _s()), "gap_bwd")
