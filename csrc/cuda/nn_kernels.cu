@@ -799,17 +799,21 @@ extern "C" int b2d_relu_bwd(const float* dy, const float* y, float* dx, size_t n
   return B2D_OK;
 }
 
+// ph / pw are the padding at the top / left; the bottom / right padding is whatever the given
+// output size implies (TensorFlow's 'same' puts the odd pixel at the end), since reads outside
+// the image are skipped.  OH / OW <= 0 mean "derive from symmetric padding".
 static ConvShape make_shape(int N, int H, int W, int Ci, int Co, int KH, int KW, int sh, int sw,
-                            int ph, int pw) {
-  ConvShape s{N, H, W, Ci, Co, KH, KW, (H + 2 * ph - KH) / sh + 1, (W + 2 * pw - KW) / sw + 1,
-              sh, sw, ph, pw};
+                            int ph, int pw, int OH, int OW) {
+  if (OH <= 0) OH = (H + 2 * ph - KH) / sh + 1;
+  if (OW <= 0) OW = (W + 2 * pw - KW) / sw + 1;
+  ConvShape s{N, H, W, Ci, Co, KH, KW, OH, OW, sh, sw, ph, pw};
   return s;
 }
 
 extern "C" int b2d_conv2d_fwd_direct(const float* x, const float* w, const float* bias, float* y,
                                      int N, int H, int W, int Ci, int Co, int KH, int KW, int sh,
-                                     int sw, int ph, int pw, int relu, void* stream) {
-  const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw);
+                                     int sw, int ph, int pw, int OH, int OW, int relu, void* stream) {
+  const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw, OH, OW);
   B2D_CUDA_CHECK(launch_pdl(conv2d_fwd_direct_kernel, dim3(grid_for((size_t)N * s.OH * s.OW * Co)), dim3(256), 0, static_cast<cudaStream_t>(stream), x, w, bias, y, s, relu));
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;
@@ -817,8 +821,8 @@ extern "C" int b2d_conv2d_fwd_direct(const float* x, const float* w, const float
 
 extern "C" int b2d_conv2d_dgrad_direct(const float* dy, const float* w, float* dx, int N, int H, int W,
                                        int Ci, int Co, int KH, int KW, int sh, int sw, int ph, int pw,
-                                       void* stream) {
-  const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw);
+                                       int OH, int OW, void* stream) {
+  const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw, OH, OW);
   B2D_CUDA_CHECK(launch_pdl(conv2d_dgrad_direct_kernel, dim3(grid_for((size_t)N * H * W * Ci)), dim3(256), 0, static_cast<cudaStream_t>(stream), dy, w, dx, s));
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;
@@ -826,8 +830,8 @@ extern "C" int b2d_conv2d_dgrad_direct(const float* dy, const float* w, float* d
 
 extern "C" int b2d_conv2d_wgrad_direct(const float* x, const float* dy, float* dw, int N, int H, int W,
                                        int Ci, int Co, int KH, int KW, int sh, int sw, int ph, int pw,
-                                       void* stream) {
-  const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw);
+                                       int OH, int OW, void* stream) {
+  const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw, OH, OW);
   const dim3 grid(KH * KW * Ci, ceil_div(Co, 32));
   B2D_CUDA_CHECK(launch_pdl(conv2d_wgrad_direct_kernel, dim3(grid), dim3(256), 0, static_cast<cudaStream_t>(stream), x, dy, dw, s));
   B2D_CUDA_CHECK(cudaGetLastError());
@@ -1162,17 +1166,20 @@ extern "C" int b2d_add_act(const float* a, const float* b, float* out, size_t n,
   return B2D_OK;
 }
 
+// p = padding at the top / left; OH, OW = output size (<= 0: derive from symmetric padding).
 extern "C" int b2d_maxpool_fwd(const float* x, float* y, uint8_t* code, int N, int H, int W, int C, int k, int s,
-                               int p, void* stream) {
-  const int OH = (H + 2 * p - k) / s + 1, OW = (W + 2 * p - k) / s + 1;
+                               int p, int OH, int OW, void* stream) {
+  if (OH <= 0) OH = (H + 2 * p - k) / s + 1;
+  if (OW <= 0) OW = (W + 2 * p - k) / s + 1;
   B2D_CUDA_CHECK(launch_pdl(maxpool_fwd_kernel, dim3(grid_for((size_t)N * OH * OW * C, 256, 148 * 16)), dim3(256), 0,
                             static_cast<cudaStream_t>(stream), x, y, code, N, H, W, C, OH, OW, k, s, p));
   return B2D_OK;
 }
 
 extern "C" int b2d_maxpool_bwd(const float* dy, const uint8_t* code, float* dx, int N, int H, int W, int C, int k,
-                               int s, int p, void* stream) {
-  const int OH = (H + 2 * p - k) / s + 1, OW = (W + 2 * p - k) / s + 1;
+                               int s, int p, int OH, int OW, void* stream) {
+  if (OH <= 0) OH = (H + 2 * p - k) / s + 1;
+  if (OW <= 0) OW = (W + 2 * p - k) / s + 1;
   B2D_CUDA_CHECK(launch_pdl(maxpool_bwd_kernel, dim3(grid_for((size_t)N * H * W * C, 256, 148 * 16)), dim3(256), 0,
                             static_cast<cudaStream_t>(stream), dy, code, dx, N, H, W, C, OH, OW, k, s, p));
   return B2D_OK;

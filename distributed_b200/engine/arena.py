@@ -28,9 +28,12 @@ class Slot:
 
 class ArenaLayout:
     def __init__(self, model_layers):
+        from ..keras.layers import flatten_layers
         self.slots: list[Slot] = []
+        self.leaves = flatten_layers(model_layers)
+        self._index = {id(l): i for i, l in enumerate(self.leaves)}
         off = 0
-        for li, layer in enumerate(model_layers):
+        for li, layer in enumerate(self.leaves):
             for spec in layer.param_specs():
                 self.slots.append(Slot(spec.name, tuple(spec.shape), off, spec.size, li))
                 off += (spec.size + ALIGN - 1) // ALIGN * ALIGN
@@ -48,15 +51,20 @@ class ArenaLayout:
         """View of one tensor inside a flat torch buffer."""
         return flat[slot.offset:slot.offset + slot.size].view(slot.shape)
 
-    def layer_slots(self, layer_index: int) -> list[Slot]:
-        return [s for s in self.slots if s.layer_index == layer_index]
+    def layer_slots(self, layer) -> list[Slot]:
+        """Slots of a leaf layer (by object, or by its index in the flattened layer list)."""
+        li = layer if isinstance(layer, int) else self._index[id(layer)]
+        return [s for s in self.slots if s.layer_index == li]
+
+    def leaf_index(self, layer) -> int:
+        return self._index[id(layer)]
 
     def initial_values(self, model_layers, seed: int) -> np.ndarray:
         """Identical on every replica: one generator seeded per tensor from (seed, position)."""
         from ..keras.layers import initialize
         flat = np.zeros(self.n_total, np.float32)
         k = 0
-        for layer in model_layers:
+        for layer in self.leaves:
             for spec in layer.param_specs():
                 s = self.slots[k]
                 rng = np.random.default_rng([seed, k])

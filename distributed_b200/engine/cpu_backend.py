@@ -63,5 +63,14 @@ class CpuBackend:
     def softmax_xent(self, logits, labels, dlogits, metrics, scale):
         return lambda: cpu.softmax_xent(logits, labels, dlogits, metrics, scale)
 
+    def relu_bwd(self, dy, y, dx):
+        return lambda: cpu.relu_bwd(dy, y, dx)
+
+    def __getattr__(self, name):
+        if name in ("bn_fwd", "bn_bwd", "add_act", "copy", "maxpool_fwd", "maxpool_bwd", "gap_fwd", "gap_bwd"):
+            raise NotImplementedError(f"{name}: BatchNormalization / Residual / general pooling layers run on the "
+                                      "CUDA backend only (the CPU backend covers the reference's layer set)")
+        raise AttributeError(name)
+
     def sgd_apply(self, params, grads, n_params, lr):
         return lambda: cpu.sgd_apply(params, grads, n_params, lr)

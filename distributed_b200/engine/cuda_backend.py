@@ -53,6 +53,9 @@ class CudaBackend:
         from ..ops import conv as tc
         if os.environ.get("B200DIST_CONV", "") == "direct":
             return False
+        kh, kw = w_shape[0], w_shape[1]
+        if tuple(strides) == (1, 1) and tuple(pad) != (0, 0) and ((kh - 1) % 2 or (kw - 1) % 2):
+            return False        # 'same' with an even kernel pads asymmetrically: direct kernels only
         return tc.tc_supported(tuple(x_shape), tuple(w_shape), pad, torch.float32, dgrad=dgrad, strides=strides)
 
     def describe_dense(self, b, k, n):
@@ -149,6 +152,34 @@ class CudaBackend:
     def dense_xent_head(self, h, w, b, labels, dh, dw, db, metrics, scale, relu_mask, logits, dh_colsum=None):
         return lambda: nn.dense_xent_head(h, w, b, labels, dh, dw, db, metrics, scale, relu_mask, logits,
                                           dh_colsum)
+
+    # ---- ResNet-family ops --------------------------------------------------------------
+    def bn_fwd(self, x2d, gamma, beta, stats, saved, moving, y2d, eps, momentum, relu):
+        return lambda: nn.bn_fwd(x2d, gamma, beta, stats, saved, moving, y2d, eps, momentum, relu)
+
+    def bn_bwd(self, x2d, y2d, dy2d, gamma, saved, red, dx2d, dgamma, dbeta, relu):
+        return lambda: nn.bn_bwd(x2d, y2d, dy2d, gamma, saved, red, dx2d, dgamma, dbeta, relu)
+
+    def add_act(self, a, b, out, relu):
+        return lambda: nn.add_act(a, b, out, relu)
+
+    def relu_bwd(self, dy, y, dx):
+        return lambda: nn.relu_bwd(dy, y, dx)
+
+    def copy(self, src, dst):
+        return lambda: dst.copy_(src)          # contiguous D2D: a memcpy node, not a kernel
+
+    def maxpool_fwd(self, x, y, code, k, s, p):
+        return lambda: nn.maxpool_fwd(x, y, code, k, s, p)
+
+    def maxpool_bwd(self, dy, code, dx, k, s, p):
+        return lambda: nn.maxpool_bwd(dy, code, dx, k, s, p)
+
+    def gap_fwd(self, x, y):
+        return lambda: nn.gap_fwd(x, y)
+
+    def gap_bwd(self, dy, dx):
+        return lambda: nn.gap_bwd(dy, dx)
 
     def softmax_xent(self, logits, labels, dlogits, metrics, scale):
         return lambda: nn.softmax_xent(logits, labels, dlogits, metrics, scale)

@@ -146,21 +146,38 @@ class Conv2D(Layer):
 
 
 class MaxPooling2D(Layer):
-    """Max pooling; the default (2, 2) window / stride 2 / 'valid' is what README.md:294 uses."""
+    """Max pooling; the default (2, 2) window / stride 2 / 'valid' is what README.md:294 uses
+    (fused fast path).  Other square windows / strides / 'same' padding use the general kernel."""
     base_name = "max_pooling2d"
 
     def __init__(self, pool_size=(2, 2), strides=None, padding="valid", **kw):
         super().__init__(**kw)
         self.pool_size = _pair(pool_size)
         self.strides = _pair(strides) if strides is not None else self.pool_size
-        if padding.lower() != "valid":
-            raise ValueError("MaxPooling2D supports padding='valid' only")
-        if self.pool_size != (2, 2) or self.strides != (2, 2):
-            raise ValueError("MaxPooling2D supports pool_size=2, strides=2 (the Keras default) only")
+        self.padding = padding.lower()
+        if self.padding not in ("valid", "same"):
+            raise ValueError("padding must be 'valid' or 'same'")
+        if self.pool_size[0] != self.pool_size[1] or self.strides[0] != self.strides[1]:
+            raise ValueError("MaxPooling2D supports square windows and strides")
+
+    @property
+    def is_default_2x2(self) -> bool:
+        return self.pool_size == (2, 2) and self.strides == (2, 2) and self.padding == "valid"
+
+    def pad_amount(self) -> int:
+        if self.padding == "valid":
+            return 0
+        H = self.input_shape[0]
+        k, s = self.pool_size[0], self.strides[0]
+        total = max((math.ceil(H / s) - 1) * s + k - H, 0)
+        return total // 2
 
     def compute_output_shape(self, input_shape):
         H, W, C = input_shape
-        return (H // 2, W // 2, C)
+        k, s = self.pool_size[0], self.strides[0]
+        if self.padding == "valid":
+            return ((H - k) // s + 1, (W - k) // s + 1, C)
+        return (math.ceil(H / s), math.ceil(W / s), C)
 
 
 class Flatten(Layer):
@@ -196,6 +213,75 @@ class Dense(Layer):
         if self.use_bias:
             specs.append(ParamSpec(f"{self.name}/bias:0", (self.units,), self.bias_initializer))
         return specs
+
+
+class BatchNormalization(Layer):
+    """Batch normalisation over the channel axis, training statistics (ResNet-50, BASELINE.json
+    config 4).  Keras weight order: gamma, beta, moving_mean, moving_variance.  A following ReLU
+    is folded into the same kernels."""
+    base_name = "batch_normalization"
+
+    def __init__(self, axis=-1, momentum=0.99, epsilon=1e-3, **kw):
+        super().__init__(**kw)
+        if axis not in (-1, 3):
+            raise ValueError("BatchNormalization supports the channel (last) axis only")
+        self.momentum, self.epsilon = float(momentum), float(epsilon)
+
+    def param_specs(self):
+        c = self.input_shape[-1]
+        return [ParamSpec(f"{self.name}/gamma:0", (c,), "ones"), ParamSpec(f"{self.name}/beta:0", (c,), "zeros")]
+
+
+class GlobalAveragePooling2D(Layer):
+    base_name = "global_average_pooling2d"
+
+    def compute_output_shape(self, input_shape):
+        return (input_shape[-1],)
+
+
+class Residual(Layer):
+    """``relu(main(x) + shortcut(x))`` — the building block of ResNets, as one composite layer so
+    that residual networks fit the Sequential container (``shortcut=None`` is the identity)."""
+    base_name = "residual"
+
+    def __init__(self, main, shortcut=None, activation="relu", **kw):
+        super().__init__(**kw)
+        self.main = list(main)
+        self.shortcut = list(shortcut) if shortcut else []
+        self.activation = _norm_activation(activation)
+
+    def sublayers(self):
+        return self.main + self.shortcut
+
+    def build(self, input_shape):
+        self.input_shape = tuple(int(d) for d in input_shape)
+        shape = self.input_shape
+        for k, l in enumerate(self.main):
+            l.name = l._given_name or f"{self.name}_main{k}_{l.base_name}"
+            shape = l.build(shape)
+        sc = self.input_shape
+        for k, l in enumerate(self.shortcut):
+            l.name = l._given_name or f"{self.name}_sc{k}_{l.base_name}"
+            sc = l.build(sc)
+        if tuple(sc) != tuple(shape):
+            raise ValueError(f"Residual {self.name}: main path {shape} and shortcut {sc} shapes differ")
+        self.output_shape = tuple(shape)
+        self.built = True
+        return self.output_shape
+
+    def param_specs(self):
+        return [s for l in self.sublayers() for s in l.param_specs()]
+
+
+def flatten_layers(layers):
+    """Leaf layers in parameter order (Residual expands to main path then shortcut)."""
+    out = []
+    for l in layers:
+        if isinstance(l, Residual):
+            out.extend(flatten_layers(l.sublayers()))
+        else:
+            out.append(l)
+    return out
 
 
 class Activation(Layer):

@@ -66,7 +66,7 @@ class Sequential(Model):
         if not isinstance(layer, L.Layer):
             raise TypeError("Sequential.add expects a Layer")
         if isinstance(layer, L.Activation) and self.layers and self.layers[-1].activation is None \
-                and isinstance(self.layers[-1], (L.Conv2D, L.Dense)):
+                and isinstance(self.layers[-1], (L.Conv2D, L.Dense, L.BatchNormalization)):
             self.layers[-1].activation = layer.activation     # fold into the producer's epilogue
             self._rebuild_shapes()
             return

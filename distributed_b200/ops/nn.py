@@ -28,7 +28,7 @@ def _lib():
         lib.b2d_maxpool2_bwd.argtypes = [vp, vp, vp, vp, i, i, i, i, i, vp]
         lib.b2d_colsum.argtypes = [vp, vp, i, i, vp]
         lib.b2d_relu_bwd.argtypes = [vp, vp, vp, sz, vp]
-        conv = [i] * 11
+        conv = [i] * 13
         lib.b2d_conv2d_fwd_direct.argtypes = [vp, vp, vp, vp, *conv, i, vp]
         lib.b2d_conv2d_dgrad_direct.argtypes = [vp, vp, vp, *conv, vp]
         lib.b2d_conv2d_wgrad_direct.argtypes = [vp, vp, vp, *conv, vp]
@@ -38,8 +38,8 @@ def _lib():
         lib.b2d_bn_fwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, i, i, f, f, i, vp]
         lib.b2d_bn_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp]
         lib.b2d_add_act.argtypes = [vp, vp, vp, sz, i, vp]
-        lib.b2d_maxpool_fwd.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, vp]
-        lib.b2d_maxpool_bwd.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, vp]
+        lib.b2d_maxpool_fwd.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, i, i, vp]
+        lib.b2d_maxpool_bwd.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, i, i, vp]
         lib.b2d_gap_fwd.argtypes = [vp, vp, i, i, i, vp]
         lib.b2d_gap_bwd.argtypes = [vp, vp, i, i, i, vp]
         _declared = True
@@ -109,27 +109,28 @@ def relu_bwd(dy, y, dx):
     nl.check(_lib().b2d_relu_bwd(_p(dy), _p(y), _p(dx), dy.numel(), _s()), "relu_bwd")
 
 
-def _conv_args(x_shape, w_shape, strides, padding):
+def _conv_args(x_shape, w_shape, strides, padding, out_shape):
+    """padding = (top, left); the output tensor's own height / width fix the bottom / right padding."""
     N, H, W, Ci = x_shape
     KH, KW, _, Co = w_shape
-    return [N, H, W, Ci, Co, KH, KW, strides[0], strides[1], padding[0], padding[1]]
+    return [N, H, W, Ci, Co, KH, KW, strides[0], strides[1], padding[0], padding[1], out_shape[1], out_shape[2]]
 
 
 def conv2d_fwd_direct(x, w, b, y, strides=(1, 1), padding=(0, 0), relu=False):
     nl.check(_lib().b2d_conv2d_fwd_direct(_p(x), _p(w), _p(b), _p(y),
-                                          *_conv_args(x.shape, w.shape, strides, padding),
+                                          *_conv_args(x.shape, w.shape, strides, padding, y.shape),
                                           int(relu), _s()), "conv2d_fwd_direct")
 
 
 def conv2d_dgrad_direct(dy, w, dx, strides=(1, 1), padding=(0, 0)):
     nl.check(_lib().b2d_conv2d_dgrad_direct(_p(dy), _p(w), _p(dx),
-                                            *_conv_args(dx.shape, w.shape, strides, padding), _s()),
+                                            *_conv_args(dx.shape, w.shape, strides, padding, dy.shape), _s()),
              "conv2d_dgrad_direct")
 
 
 def conv2d_wgrad_direct(x, dy, dw, strides=(1, 1), padding=(0, 0)):
     nl.check(_lib().b2d_conv2d_wgrad_direct(_p(x), _p(dy), _p(dw),
-                                            *_conv_args(x.shape, dw.shape, strides, padding), _s()),
+                                            *_conv_args(x.shape, dw.shape, strides, padding, dy.shape), _s()),
              "conv2d_wgrad_direct")
 
 
@@ -172,12 +173,14 @@ def add_act(a, b, out, relu):
 
 def maxpool_fwd(x, y, code, k, s, p):
     N, H, W, Cc = x.shape
-    nl.check(_lib().b2d_maxpool_fwd(_p(x), _p(y), _p(code), N, H, W, Cc, k, s, p, _s()), "maxpool_fwd")
+    nl.check(_lib().b2d_maxpool_fwd(_p(x), _p(y), _p(code), N, H, W, Cc, k, s, p, y.shape[1], y.shape[2], _s()),
+             "maxpool_fwd")
 
 
 def maxpool_bwd(dy, code, dx, k, s, p):
     N, H, W, Cc = dx.shape
-    nl.check(_lib().b2d_maxpool_bwd(_p(dy), _p(code), _p(dx), N, H, W, Cc, k, s, p, _s()), "maxpool_bwd")
+    nl.check(_lib().b2d_maxpool_bwd(_p(dy), _p(code), _p(dx), N, H, W, Cc, k, s, p, dy.shape[1], dy.shape[2], _s()),
+             "maxpool_bwd")
 
 
 def gap_fwd(x, y):

@@ -153,14 +153,18 @@ int b2d_maxpool2_bwd(const float* dy, const uint8_t* code, const float* y_pooled
                      int H, int W, int C, int act_relu, void* stream);
 int b2d_colsum(const float* dy, float* db, int M, int N, void* stream);          /* db += column sums */
 int b2d_relu_bwd(const float* dy, const float* y, float* dx, size_t n, void* stream);
-/* Direct (CUDA-core) convolutions: any stride / zero padding. */
+/* Direct (CUDA-core) convolutions: any stride / zero padding.  ph, pw = padding at the top / left;
+ * OH, OW = output size (<= 0: derive from symmetric padding) — TensorFlow's 'same' padding is
+ * asymmetric for even totals, which the explicit output size expresses. */
 int b2d_conv2d_fwd_direct(const float* x, const float* w, const float* bias, float* y, int N, int H,
                           int W, int Ci, int Co, int KH, int KW, int sh, int sw, int ph, int pw,
-                          int relu, void* stream);
+                          int OH, int OW, int relu, void* stream);
 int b2d_conv2d_dgrad_direct(const float* dy, const float* w, float* dx, int N, int H, int W, int Ci,
-                            int Co, int KH, int KW, int sh, int sw, int ph, int pw, void* stream);
+                            int Co, int KH, int KW, int sh, int sw, int ph, int pw, int OH, int OW,
+                            void* stream);
 int b2d_conv2d_wgrad_direct(const float* x, const float* dy, float* dw, int N, int H, int W, int Ci,
-                            int Co, int KH, int KW, int sh, int sw, int ph, int pw, void* stream);
+                            int Co, int KH, int KW, int sh, int sw, int ph, int pw, int OH, int OW,
+                            void* stream);
 /* CUDA-core GEMM with arbitrary strides (tiny / unaligned problems). */
 int b2d_sgemm_simt(const float* A, int64_t sam, int64_t sak, const float* B, int64_t sbk, int64_t sbn,
                    float* D, int64_t ldd, const float* bias, int M, int N, int K, int relu,
@@ -168,6 +172,21 @@ int b2d_sgemm_simt(const float* A, int64_t sam, int64_t sak, const float* B, int
 /* Single-replica optimizer step: w[:n_params] -= lr*g, w[n_params:] += g, g = 0 (README.md:302). */
 int b2d_sgd_apply(float* w, float* g, size_t n_params, size_t n_total, float lr, void* stream);
 int b2d_cast_f32_bf16(const float* src, void* dst, size_t n, void* stream);
+/* ResNet-family extras (BASELINE.json config 4; no counterpart in the reference README):
+ * training-mode BatchNorm over rows of x [M,C] fused with ReLU (stats/red: zeroed scratch [2C];
+ * saved: mean|rstd; moving: mean|variance), residual add (+ReLU), general max pooling
+ * (window k, stride s, top/left padding p, explicit output size), global average pooling. */
+int b2d_bn_fwd(const float* x, const float* gamma, const float* beta, float* stats, float* saved,
+               float* moving, float* y, int M, int C, float eps, float momentum, int relu, void* stream);
+int b2d_bn_bwd(const float* x, const float* y, const float* dy, const float* gamma, const float* saved,
+               float* red, float* dx, float* dgamma, float* dbeta, int M, int C, int relu, void* stream);
+int b2d_add_act(const float* a, const float* b, float* out, size_t n, int relu, void* stream);
+int b2d_maxpool_fwd(const float* x, float* y, uint8_t* code, int N, int H, int W, int C, int k, int s, int p,
+                    int OH, int OW, void* stream);
+int b2d_maxpool_bwd(const float* dy, const uint8_t* code, float* dx, int N, int H, int W, int C, int k, int s,
+                    int p, int OH, int OW, void* stream);
+int b2d_gap_fwd(const float* x, float* y, int N, int HW, int C, void* stream);
+int b2d_gap_bwd(const float* dy, float* dx, int N, int HW, int C, void* stream);
 
 /* ---------------------------------------------------------------------------------------
  * Symmetric memory over NVLink (csrc/runtime/symm.cpp): one block per GPU, POSIX-fd exchange
