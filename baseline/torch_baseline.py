@@ -15,6 +15,9 @@ import time
 
 def build_model(name: str):
     import torch.nn as nn
+    if name == "resnet50":
+        import torchvision
+        return torchvision.models.resnet50(weights=None)
     if name == "mnist_cnn":
         return nn.Sequential(nn.Conv2d(1, 32, 3), nn.ReLU(), nn.MaxPool2d(2), nn.Flatten(),
                              nn.Linear(5408, 64), nn.ReLU(), nn.Linear(64, 10))
@@ -44,14 +47,22 @@ def run(args, ClockSampler, dist_env, max_over_ranks, barrier) -> dict:
     global_batch = per_gpu * world
     n_images = args.dataset_images - args.dataset_images % global_batch
     g = torch.Generator().manual_seed(0)
-    x_host = torch.rand((n_images, 1, 28, 28), generator=g).pin_memory()          # NCHW, torch's native layout
-    y_host = torch.randint(0, 10, (n_images,), generator=g).pin_memory()
+    shape, classes = ((3, 224, 224), 1000) if args.model == "resnet50" else ((1, 28, 28), 10)
+    x_host = torch.rand((n_images, *shape), generator=g).pin_memory()              # NCHW, torch's native layout
+    y_host = torch.randint(0, classes, (n_images,), generator=g).pin_memory()
+    bf16 = bool(getattr(args, "channels_last", False))
+    if bf16:
+        model = model.to(memory_format=torch.channels_last)
     x_dev, y_dev = x_host.to(dev), y_host.to(dev)
     steps_in_src = n_images // global_batch
 
     def step(xb, yb):
         opt.zero_grad(set_to_none=True)
-        loss = F.cross_entropy(model(xb), yb)
+        if bf16:
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                loss = F.cross_entropy(model(xb.contiguous(memory_format=torch.channels_last)), yb)
+        else:
+            loss = F.cross_entropy(model(xb), yb)
         loss.backward()
         opt.step()
         return loss
@@ -119,14 +130,14 @@ def run(args, ClockSampler, dist_env, max_over_ranks, barrier) -> dict:
     out = {
         "metric": "images/sec (device-timed, max over ranks)", "value": value, "unit": "images/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "tf32", "data": "synthetic",
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16 autocast, channels_last" if bf16 else "tf32", "data": "synthetic",
         "impl": "torch-baseline" + ("+cudagraph" if graph is not None else ""),
         "config": {"model": args.model, "global_batch": global_batch, "batch_per_gpu": per_gpu,
                    "parallelism": f"dp{world}", "all_reduce": "DDP bucketed NCCL all-reduce" if world > 1 else "none",
                    "l2_policy": "inputs larger than L2 (fresh batch of a 60000-image data set every step)"},
         "clocks": clocks.summary(),
         "e2e": {"value": args.steps * global_batch / e2e_s, "unit": "images/s",
-                "h2d_bytes_per_step": per_gpu * 3136 + per_gpu * 8, "d2h_bytes_per_step": 4},
+                "h2d_bytes_per_step": per_gpu * 4 * shape[0] * shape[1] * shape[2] + per_gpu * 8, "d2h_bytes_per_step": 4},
         "gpu_launches": 0, "final_loss": losses[-1],
     }
     return out if rank == 0 else {}

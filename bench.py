@@ -124,14 +124,17 @@ def run_ours(args) -> dict:
         strategy._ensure_group()
     else:
         strategy = tf.distribute.OneDeviceStrategy()
+    shape, classes = MODEL_INPUT[args.model]
     with strategy.scope():
-        model = tf.models.mnist_cnn() if args.model == "mnist_cnn" else tf.models.scaled_cnn()
+        model = {"mnist_cnn": tf.models.mnist_cnn, "scaled_cnn": tf.models.scaled_cnn,
+                 "resnet50": lambda: tf.models.resnet50(learning_rate=0.01)}[args.model]()
 
-    # synthetic data of MNIST shape: N_IMAGES x 28 x 28 x 1 fp32 (> L2), labels int32
+    # synthetic data of the model's input shape, fp32, larger than L2; labels int32
     n_images = args.dataset_images - args.dataset_images % global_batch
+    row_bytes = 4 * shape[0] * shape[1] * shape[2]
     g = torch.Generator().manual_seed(0)
-    x_host = torch.rand((n_images, 28, 28, 1), generator=g, dtype=torch.float32).pin_memory()
-    y_host = torch.randint(0, 10, (n_images,), generator=g, dtype=torch.int32).pin_memory()
+    x_host = torch.rand((n_images, *shape), generator=g, dtype=torch.float32).pin_memory()
+    y_host = torch.randint(0, classes, (n_images,), generator=g, dtype=torch.int32).pin_memory()
     steps_in_src = n_images // global_batch
 
     # --- warm-up through the public API (builds the trainer, captures the step graphs) ---
@@ -168,22 +171,27 @@ def run_ours(args) -> dict:
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "tf32 (fp32 storage, fp32 accumulate; first conv in fp32)", "data": "synthetic",
         "impl": "distributed_b200",
-        "config": {"model": "README MNIST CNN (conv32-3x3/maxpool/dense64/dense10, SGD lr=1e-3)"
-                   if args.model == "mnist_cnn" else "scaled CNN (conv64/conv128/dense1024)",
-                   "global_batch": global_batch, "batch_per_gpu": per_gpu, "input": "28x28x1",
+        "config": {"model": MODEL_NAMES[args.model],
+                   "global_batch": global_batch, "batch_per_gpu": per_gpu, "input": "x".join(map(str, shape)),
                    "parallelism": f"dp{world}",
                    "all_reduce": trainer.comm.description,
                    "l2_policy": f"inputs larger than L2: each step reads a fresh batch of a {n_images}-image "
-                                f"({n_images * 3136 / 1e6:.0f} MB) data set",
+                                f"({n_images * row_bytes / 1e6:.0f} MB) data set",
                    "kernels_per_step": trainer.kernels_per_step, "cuda_graph": trainer.use_graph},
         "clocks": clocks.summary(),
-        "e2e": {"value": e2e, "unit": "images/s", "h2d_bytes_per_step": per_gpu * 3136 + per_gpu * 4,
+        "e2e": {"value": e2e, "unit": "images/s", "h2d_bytes_per_step": per_gpu * row_bytes + per_gpu * 4,
                 "d2h_bytes_per_step": 16, "ms_per_step": 1e3 * e2e_s / args.steps,
                 "api": "model.fit(x_pinned, y_pinned, batch_size, epochs=1, steps_per_epoch=K)"},
         "gpu_launches": int(launches),
         "final_loss": hist.history["loss"][-1],
     }
     return out if rank == 0 else {}
+
+
+MODEL_INPUT = {"mnist_cnn": ((28, 28, 1), 10), "scaled_cnn": ((28, 28, 1), 10), "resnet50": ((224, 224, 3), 1000)}
+MODEL_NAMES = {"mnist_cnn": "README MNIST CNN (conv32-3x3/maxpool/dense64/dense10, SGD lr=1e-3)",
+               "scaled_cnn": "scaled CNN (conv64/conv128/dense1024)",
+               "resnet50": "ResNet-50 v1.5, synthetic 224x224x3, 1000 classes"}
 
 
 def run_reference(args) -> dict:
@@ -204,13 +212,18 @@ def main():
     ap.add_argument("--steps", type=int, default=300)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "torch"])
-    ap.add_argument("--model", default="mnist_cnn", choices=["mnist_cnn", "scaled_cnn"])
-    ap.add_argument("--batch-per-gpu", type=int, default=64)
-    ap.add_argument("--dataset-images", type=int, default=60000)
+    ap.add_argument("--model", default="mnist_cnn", choices=["mnist_cnn", "scaled_cnn", "resnet50"])
+    ap.add_argument("--batch-per-gpu", type=int, default=None)
+    ap.add_argument("--dataset-images", type=int, default=None)
+    ap.add_argument("--channels-last", action="store_true", help="torch baseline: channels_last + bf16 autocast")
     ap.add_argument("--torch-graph", action="store_true", help="torch baseline: capture the step in a CUDA graph")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
+    if args.batch_per_gpu is None:
+        args.batch_per_gpu = 32 if args.model == "resnet50" else 64
+    if args.dataset_images is None:
+        args.dataset_images = 512 if args.model == "resnet50" else 60000        # both > 126 MB of L2
     if args.impl == "reference":
         out = run_reference(args)
         if int(os.environ.get("RANK", "0")) == 0:

@@ -48,6 +48,12 @@ struct ConvGeom {
   int w_base, h_base;      // input coordinate of tap (0,0) for output pixel (0,0)
   int tap_sign;            // +1 forward (in = out + tap - pad), -1 dgrad (in = out + pad - tap)
   int b_rows_per_tap;      // K-major B (dgrad): rows of the weight matrix per tap (= C_in)
+  int stride;              // forward only: input step per output pixel (TMA element stride)
+  // strided data gradient, one launch per output-pixel parity class: the class's taps are
+  // r = tap_r0 + tap_step * tr (same for columns) of a kw_full-wide filter, and its output pixels
+  // are (out_step * oh + out_off_h, out_step * ow + out_off_w) of an OH_full x OW_full image.
+  int tap_r0, tap_s0, tap_step, kw_full;
+  int out_step, out_off_h, out_off_w, OH_full, OW_full;
 };
 
 struct GemmArgs {
@@ -218,7 +224,7 @@ __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const __grid_constant__
           if (cv.enabled) {
             const int r = tap / cv.kw, sx = tap - r * cv.kw;
             tma_load_4d(sa, &args.tmA, &full_bar[stage], cc * BLOCK_K, cv.w_base + cv.tap_sign * sx,
-                        cv_oh0 + cv.h_base + cv.tap_sign * r, cv_n0);
+                        cv_oh0 * cv.stride + cv.h_base + cv.tap_sign * r, cv_n0);
           } else {
             tma_load_2d(sa, &args.tmA, &full_bar[stage], k0, m0);
           }
@@ -229,8 +235,11 @@ __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const __grid_constant__
                         k0);
         }
         if constexpr (!B_MN) {
-          if (cv.enabled)  // dgrad: weights [taps * C_in rows][C_out], K = C_out chunk of this tap
-            tma_load_2d(sb, &args.tmB, &full_bar[stage], cc * BLOCK_K, tap * cv.b_rows_per_tap + n0);
+          if (cv.enabled) {  // dgrad: weights [taps * C_in rows][C_out], K = C_out chunk of this tap
+            const int tr = tap / cv.kw, ts = tap - tr * cv.kw;
+            const int tap_full = (cv.tap_r0 + cv.tap_step * tr) * cv.kw_full + cv.tap_s0 + cv.tap_step * ts;
+            tma_load_2d(sb, &args.tmB, &full_bar[stage], cc * BLOCK_K, tap_full * cv.b_rows_per_tap + n0);
+          }
           else
             tma_load_2d(sb, &args.tmB, &full_bar[stage], k0, n0);
         } else {
@@ -281,7 +290,7 @@ __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const __grid_constant__
       const int h_i = t % cv.ho_t, n_i = t / cv.ho_t;
       const int oh = cv_oh0 + h_i, n = cv_n0 + n_i;
       row_ok = m < cv.rows_used && oh < cv.OH && n < cv.N_img;
-      row = (n * cv.OH + oh) * cv.OW + w_i;
+      row = (n * cv.OH_full + oh * cv.out_step + cv.out_off_h) * cv.OW_full + w_i * cv.out_step + cv.out_off_w;
     }
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
@@ -596,14 +605,16 @@ extern "C" void b2d_gemm_plan_set_timeline(b2d_gemm_plan* p, long long* buf) {
 
 static int encode_tmap_4d(CUtensorMap* tm, int dtype, const void* base, uint64_t C, uint64_t W,
                           uint64_t H, uint64_t N, uint32_t box_c, uint32_t box_w, uint32_t box_h,
-                          uint32_t box_n, bool mn_major = false) {
+                          uint32_t box_n, bool mn_major = false, uint32_t stride = 1) {
   static EncodeTiledFn fn = reinterpret_cast<EncodeTiledFn>(driver_fn("cuTensorMapEncodeTiled"));
   if (fn == nullptr) return B2D_ERR_UNSUPPORTED;
   const uint64_t es = dtype == B2D_F32 ? 4 : 2;
   const cuuint64_t dims[4] = {C, W, H, N};
   const cuuint64_t strides[3] = {C * es, W * C * es, H * W * C * es};
-  const cuuint32_t box[4] = {box_c, box_w, box_h, box_n};
-  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  // Strided convolutions: the box spans box_w*stride x box_h*stride input pixels and the TMA unit
+  // keeps every stride-th one (traversal stride), so shared memory still receives box_w x box_h.
+  const cuuint32_t box[4] = {box_c, box_w * stride, box_h * stride, box_n};
+  const cuuint32_t estr[4] = {1, stride, stride, 1};
   const CUtensorMapDataType dt =
       dtype == B2D_F32 ? CU_TENSOR_MAP_DATA_TYPE_TFLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   // channels-as-MN (wgrad) fp32 tiles need the 32-byte-chunk swizzle, like the 2-D MN-major maps
@@ -622,10 +633,20 @@ static int encode_tmap_4d(CUtensorMap* tm, int dtype, const void* base, uint64_t
 }
 
 // 1 if the tensor-core path can take this convolution (otherwise use the direct kernels).
+static inline int conv_stride(const b2d_conv_desc& d) { return d.stride > 1 ? d.stride : 1; }
+static inline int conv_out_h(const b2d_conv_desc& d) {
+  return d.OH > 0 ? d.OH : (d.H + 2 * d.pad_h - d.KH) / conv_stride(d) + 1;
+}
+static inline int conv_out_w(const b2d_conv_desc& d) {
+  return d.OW > 0 ? d.OW : (d.W + 2 * d.pad_w - d.KW) / conv_stride(d) + 1;
+}
+
 extern "C" int b2d_conv_tc_supported(const b2d_conv_desc* d, int dgrad) {
   if (d == nullptr) return 0;
   const int es = d->dtype == B2D_F32 ? 4 : 2;
-  const int OH = d->H + 2 * d->pad_h - d->KH + 1, OW = d->W + 2 * d->pad_w - d->KW + 1;
+  const int OH = conv_out_h(*d), OW = conv_out_w(*d);
+  if (conv_stride(*d) > 1 && dgrad) return 0;     // strided data gradient: direct kernels
+  if (OW * conv_stride(*d) > 256) return 0;        // TMA box limit
   const int k_ch = dgrad ? d->Co : d->Ci;       // reduction channels
   const int n_ch = dgrad ? d->Ci : d->Co;       // output channels
   const int out_w = dgrad ? d->W : OW;
@@ -641,7 +662,8 @@ static int conv_plan_create(const b2d_conv_desc& d, bool dgrad, b2d_gemm_plan** 
   B2D_REQUIRE(d.x && d.w && d.y, "conv: null tensor pointer");
   const int es = d.dtype == B2D_F32 ? 4 : 2;
   const int block_k = 128 / es;
-  const int OH = d.H + 2 * d.pad_h - d.KH + 1, OW = d.W + 2 * d.pad_w - d.KW + 1;
+  const int OH = conv_out_h(d), OW = conv_out_w(d);
+  const int stride = dgrad ? 1 : conv_stride(d);
   // geometry of the *output* of this GEMM and of the tensor the taps slide over
   const int out_h = dgrad ? d.H : OH, out_w = dgrad ? d.W : OW;
   const int in_h = dgrad ? OH : d.H, in_w = dgrad ? OW : d.W;
@@ -664,7 +686,7 @@ static int conv_plan_create(const b2d_conv_desc& d, bool dgrad, b2d_gemm_plan** 
   ConvGeom& cv = p->args.cv;
   cv.enabled = 1, cv.kw = d.KW, cv.c_chunks = k_ch / block_k;
   cv.wo_t = out_w;
-  cv.ho_t = min(out_h, kBlockM / out_w);
+  cv.ho_t = min(min(out_h, kBlockM / out_w), 256 / stride);
   cv.n_t = 1;
   if (cv.ho_t >= out_h) {
     cv.ho_t = out_h;
@@ -677,9 +699,13 @@ static int conv_plan_create(const b2d_conv_desc& d, bool dgrad, b2d_gemm_plan** 
   cv.w_base = dgrad ? d.pad_w : -d.pad_w;
   cv.h_base = dgrad ? d.pad_h : -d.pad_h;
   cv.b_rows_per_tap = d.Ci;
+  cv.stride = stride;
+  cv.tap_r0 = cv.tap_s0 = 0, cv.tap_step = 1, cv.kw_full = d.KW;
+  cv.out_step = 1, cv.out_off_h = cv.out_off_w = 0, cv.OH_full = out_h, cv.OW_full = out_w;
   g.m_tiles = cv.n_t == 1 ? d.N * cv.tiles_h : ceil_div(d.N, cv.n_t);
 
-  rc = encode_tmap_4d(&p->args.tmA, d.dtype, in_ptr, k_ch, in_w, in_h, d.N, block_k, cv.wo_t, cv.ho_t, cv.n_t);
+  rc = encode_tmap_4d(&p->args.tmA, d.dtype, in_ptr, k_ch, in_w, in_h, d.N, block_k, cv.wo_t, cv.ho_t, cv.n_t, false,
+                      stride);
   if (rc == B2D_OK) {
     const uint64_t w_rows = (uint64_t)d.KH * d.KW * d.Ci;
     if (!dgrad)   // MN-major B: dims {Co, rows}, box {one 128-byte atom of Co, BLOCK_K rows}
@@ -715,6 +741,95 @@ static int conv_plan_create(const b2d_conv_desc& d, bool dgrad, b2d_gemm_plan** 
   return B2D_OK;
 }
 
+// Strided data gradient, one output-parity class (a, b) in [0, stride)^2 per plan:
+//   dx[n, s*i+a, s*j+b, :] = sum over the taps r == (a+ph) mod s, c == (b+pw) mod s of
+//                            dy[n, i + (a+ph-r)/s, j + (b+pw-c)/s, :] . W[r, c, :, :]^T
+// i.e. a unit-stride convolution of dy with a sub-sampled filter, written to every s-th pixel.
+// *out is set to NULL (rc = OK) for a class without taps: those pixels are zero — the caller
+// clears dx first (b2d_memset_async).
+extern "C" int b2d_conv_dgrad_class_plan_create(const b2d_conv_desc* dp, int a, int b, b2d_gemm_plan** out) {
+  B2D_REQUIRE(dp != nullptr && out != nullptr, "conv_dgrad_class_plan_create: null argument");
+  const b2d_conv_desc& d = *dp;
+  *out = nullptr;
+  const int st = conv_stride(d);
+  B2D_REQUIRE(a >= 0 && a < st && b >= 0 && b < st, "conv_dgrad_class: class (%d,%d) out of range", a, b);
+  const int es = d.dtype == B2D_F32 ? 4 : 2;
+  const int block_k = 128 / es;
+  B2D_REQUIRE((d.Co * es) % 128 == 0 && d.Ci % 4 == 0, "conv_dgrad_class: channel counts not supported");
+  const int OH = conv_out_h(d), OW = conv_out_w(d);
+  const int Hc = (d.H - a + st - 1) / st, Wc = (d.W - b + st - 1) / st;   // pixels of this class
+  if (Hc <= 0 || Wc <= 0) return B2D_OK;
+  const int r0 = (a + d.pad_h) % st, s0 = (b + d.pad_w) % st;
+  const int ntr = r0 < d.KH ? (d.KH - r0 + st - 1) / st : 0;
+  const int nts = s0 < d.KW ? (d.KW - s0 + st - 1) / st : 0;
+  if (ntr == 0 || nts == 0) return B2D_OK;
+  B2D_REQUIRE(Wc <= kBlockM, "conv_dgrad_class: class width %d exceeds the M tile", Wc);
+
+  b2d_gemm_desc gd{};
+  gd.dtype = d.dtype, gd.out_dtype = d.out_dtype;
+  gd.M = d.N * Hc * Wc, gd.N = d.Ci, gd.K = ntr * nts * d.Co;
+  gd.lda = d.Co, gd.ldb = d.Co, gd.ldd = d.Ci, gd.ldmask = d.Ci;
+  gd.b_mn_major = 0, gd.splits = 1;
+  b2d_gemm_geometry g;
+  int rc = resolve(gd, &g);
+  if (rc != B2D_OK) return rc;
+  b2d_gemm_plan* p = new (std::nothrow) b2d_gemm_plan();
+  B2D_REQUIRE(p != nullptr, "conv_dgrad_class: out of host memory");
+  ConvGeom& cv = p->args.cv;
+  cv.enabled = 1, cv.kw = nts, cv.c_chunks = d.Co / block_k;
+  cv.wo_t = Wc;
+  cv.ho_t = min(Hc, kBlockM / Wc);
+  cv.n_t = 1;
+  if (cv.ho_t >= Hc) {
+    cv.ho_t = Hc;
+    cv.n_t = max(1, min(d.N, kBlockM / (Wc * Hc)));
+  }
+  cv.rows_used = cv.wo_t * cv.ho_t * cv.n_t;
+  cv.OH = Hc, cv.OW = Wc, cv.N_img = d.N;
+  cv.tiles_h = ceil_div(Hc, cv.ho_t);
+  cv.tap_sign = -1;
+  cv.h_base = (a + d.pad_h - r0) / st, cv.w_base = (b + d.pad_w - s0) / st;
+  cv.b_rows_per_tap = d.Ci, cv.stride = 1;
+  cv.tap_r0 = r0, cv.tap_s0 = s0, cv.tap_step = st, cv.kw_full = d.KW;
+  cv.out_step = st, cv.out_off_h = a, cv.out_off_w = b, cv.OH_full = d.H, cv.OW_full = d.W;
+  g.m_tiles = cv.n_t == 1 ? d.N * cv.tiles_h : ceil_div(d.N, cv.n_t);
+  rc = encode_tmap_4d(&p->args.tmA, d.dtype, d.y, d.Co, OW, OH, d.N, block_k, cv.wo_t, cv.ho_t, cv.n_t);
+  if (rc == B2D_OK)
+    rc = encode_tmap_2d(&p->args.tmB, d.dtype, d.w, d.Co, (uint64_t)d.KH * d.KW * d.Ci, (uint64_t)d.Co * es, block_k,
+                        g.block_n, false);
+  if (rc != B2D_OK) {
+    delete p;
+    return rc;
+  }
+  GemmArgs& ar = p->args;
+  ar.D = const_cast<void*>(d.x), ar.bias = nullptr, ar.mask = d.mask, ar.ws = nullptr, ar.counters = nullptr;
+  ar.ldd = d.Ci, ar.ldmask = d.Ci, ar.ldws = 0;
+  ar.M = d.N * d.H * d.W, ar.N = gd.N, ar.K = gd.K;
+  ar.kb_total = g.k_blocks, ar.kb_per_split = g.k_blocks, ar.splits = 1;
+  ar.flags = (d.out_dtype == B2D_BF16 ? kFlagOutBf16 : 0);
+  ar.stages = g.stages;
+  p->launch_smem = g.smem_bytes;
+  p->geo = g;
+  if (d.dtype == B2D_F32)
+    select_major<MmaKind::TF32>(false, false, g.block_n, &p->kernel, &p->smem_bytes);
+  else
+    select_major<MmaKind::F16>(false, false, g.block_n, &p->kernel, &p->smem_bytes);
+  cudaError_t e = cudaFuncSetAttribute(reinterpret_cast<const void*>(p->kernel),
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem_bytes);
+  if (e != cudaSuccess) {
+    set_error("conv_dgrad_class: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e));
+    delete p;
+    return B2D_ERR_CUDA;
+  }
+  *out = p;
+  return B2D_OK;
+}
+
+extern "C" int b2d_memset_async(void* ptr, int value, size_t bytes, void* stream) {
+  B2D_CUDA_CHECK(cudaMemsetAsync(ptr, value, bytes, static_cast<cudaStream_t>(stream)));
+  return B2D_OK;
+}
+
 extern "C" int b2d_conv_fwd_plan_create(const b2d_conv_desc* d, b2d_gemm_plan** out) {
   B2D_REQUIRE(d != nullptr && out != nullptr, "conv_fwd_plan_create: null argument");
   return conv_plan_create(*d, false, out);
@@ -741,7 +856,7 @@ struct WgradArgs {
   CUtensorMap tmDy;  // dims {Co, OW, OH, N}
   CUtensorMap tmX;   // dims {Ci, W,  H,  N}
   float* dw;
-  int Ci, Co, KW, pad_h, pad_w;
+  int Ci, Co, KW, pad_h, pad_w, stride;
   int rows;          // pixels per k-block = OW * ho_t
   int ho_t, tiles_h; // box height, boxes per image
   int tiles_total;   // N * tiles_h
@@ -829,7 +944,7 @@ __global__ void __launch_bounds__(256, 1) conv_wgrad_tc_kernel(const __grid_cons
 #pragma unroll
         for (int a = 0; a < B_ATOMS; ++a)
           tma_load_4d(sb + a * atom_bytes, &args.tmX, &full_bar[stage], ci0 + a * ATOM, sx - args.pad_w,
-                      oh0 + r - args.pad_h, n);
+                      oh0 * args.stride + r - args.pad_h, n);
       }
     }
   } else if (warp == 1) {
@@ -892,8 +1007,9 @@ extern "C" int b2d_conv_wgrad_plan_create(const b2d_conv_desc* dp, b2d_conv_wgra
   const b2d_conv_desc& d = *dp;
   const int es = d.dtype == B2D_F32 ? 4 : 2;
   const int atom = 128 / es, umma_k = 32 / es;
-  const int OH = d.H + 2 * d.pad_h - d.KH + 1, OW = d.W + 2 * d.pad_w - d.KW + 1;
-  B2D_REQUIRE(OH > 0 && OW > 0 && OW <= 256, "conv_wgrad: unsupported output size %dx%d", OH, OW);
+  const int OH = conv_out_h(d), OW = conv_out_w(d);
+  const int stride = conv_stride(d);
+  B2D_REQUIRE(OH > 0 && OW > 0 && OW * stride <= 256, "conv_wgrad: unsupported output size %dx%d", OH, OW);
   B2D_REQUIRE((d.Ci * es) % 16 == 0 && (d.Co * es) % 16 == 0,
               "conv_wgrad: channel counts must make pixels 16-byte aligned (Ci=%d Co=%d)", d.Ci, d.Co);
   B2D_REQUIRE(d.x && d.w && d.y, "conv_wgrad: null tensor pointer");
@@ -903,11 +1019,12 @@ extern "C" int b2d_conv_wgrad_plan_create(const b2d_conv_desc* dp, b2d_conv_wgra
   // Box height: smallest h making OW*h a multiple of the MMA K, scaled up towards ~96 pixels.
   const int h_unit = umma_k / gcd_int(OW, umma_k);
   int ho_t = h_unit;
-  while (OW * (ho_t + h_unit) <= 96 && ho_t + h_unit <= 256 && ho_t < OH) ho_t += h_unit;
+  while (OW * (ho_t + h_unit) <= 96 && (ho_t + h_unit) * stride <= 256 && ho_t < OH) ho_t += h_unit;
+  B2D_REQUIRE(ho_t * stride <= 256, "conv_wgrad: pixel box too tall for a strided TMA box");
   a.ho_t = ho_t, a.rows = OW * ho_t;
   a.tiles_h = ceil_div(OH, ho_t);
   a.tiles_total = d.N * a.tiles_h;
-  a.Ci = d.Ci, a.Co = d.Co, a.KW = d.KW, a.pad_h = d.pad_h, a.pad_w = d.pad_w;
+  a.Ci = d.Ci, a.Co = d.Co, a.KW = d.KW, a.pad_h = d.pad_h, a.pad_w = d.pad_w, a.stride = stride;
   a.dw = static_cast<float*>(const_cast<void*>(d.w));
   const int block_n = d.Ci <= 32 && atom <= 32 ? 32 : (d.Ci <= 64 ? 64 : 128);
   a.m_tiles = ceil_div(d.Co, kBlockM), a.n_tiles = ceil_div(d.Ci, block_n);
@@ -926,7 +1043,7 @@ extern "C" int b2d_conv_wgrad_plan_create(const b2d_conv_desc* dp, b2d_conv_wgra
   chunks = ceil_div(a.tiles_total, a.tiles_per_cta);
   p->grid = dim3(fixed, chunks);
   int rc = encode_tmap_4d(&a.tmDy, d.dtype, d.y, d.Co, OW, OH, d.N, atom, OW, ho_t, 1, true);
-  if (rc == B2D_OK) rc = encode_tmap_4d(&a.tmX, d.dtype, d.x, d.Ci, d.W, d.H, d.N, atom, OW, ho_t, 1, true);
+  if (rc == B2D_OK) rc = encode_tmap_4d(&a.tmX, d.dtype, d.x, d.Ci, d.W, d.H, d.N, atom, OW, ho_t, 1, true, stride);
   if (rc != B2D_OK) {
     delete p;
     return rc;

@@ -1196,3 +1196,50 @@ extern "C" int b2d_gap_bwd(const float* dy, float* dx, int N, int HW, int C, voi
                             static_cast<cudaStream_t>(stream), dy, dx, N, HW, C));
   return B2D_OK;
 }
+
+// =======================================================================================
+// im2col for convolutions whose channel count is too small for the implicit-GEMM tensor-core
+// path (a pixel is less than one 128-byte TMA row, e.g. the 3-channel stem of ResNet): the
+// patch matrix col[pixel][tap*Ci + ci] (row pitch padded to a multiple of 4 floats, padding
+// columns zero) is materialised once per step and feeds the tcgen05 GEMM core for both the
+// forward product (col . W) and the filter gradient (col^T . dy).
+// =======================================================================================
+namespace b2d {
+__global__ void __launch_bounds__(256) im2col_kernel(const float* __restrict__ x, float* __restrict__ col,
+                                                      ConvShape s, int kpad) {
+  pdl_wait();
+  pdl_trigger();
+  const int K = s.KH * s.KW * s.Ci;
+  const size_t npix = (size_t)s.N * s.OH * s.OW;
+  const int lane = threadIdx.x & 31;
+  const size_t warp0 = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5;
+  const size_t nwarps = ((size_t)gridDim.x * blockDim.x) >> 5;
+  for (size_t p = warp0; p < npix; p += nwarps) {
+    const int ow = p % s.OW;
+    const int oh = (p / s.OW) % s.OH;
+    const int n = p / ((size_t)s.OW * s.OH);
+    float* row = col + p * kpad;
+    for (int k = lane; k < kpad; k += 32) {
+      float v = 0.f;
+      if (k < K) {
+        const int ci = k % s.Ci;
+        const int kw = (k / s.Ci) % s.KW;
+        const int kh = k / (s.Ci * s.KW);
+        const int ih = oh * s.sh - s.ph + kh, iw = ow * s.sw - s.pw + kw;
+        if (ih >= 0 && ih < s.H && iw >= 0 && iw < s.W) v = x[(((size_t)n * s.H + ih) * s.W + iw) * s.Ci + ci];
+      }
+      row[k] = v;
+    }
+  }
+}
+}  // namespace b2d
+
+extern "C" int b2d_im2col(const float* x, float* col, int N, int H, int W, int Ci, int KH, int KW, int sh, int sw,
+                          int ph, int pw, int OH, int OW, int kpad, void* stream) {
+  const ConvShape s = make_shape(N, H, W, Ci, /*Co=*/0, KH, KW, sh, sw, ph, pw, OH, OW);
+  B2D_REQUIRE(kpad >= KH * KW * Ci && kpad % 4 == 0, "im2col: kpad must be >= KH*KW*Ci and a multiple of 4");
+  const size_t npix = (size_t)N * s.OH * s.OW;
+  B2D_CUDA_CHECK(launch_pdl(im2col_kernel, dim3(grid_for(npix * 32, 256, 148 * 16)), dim3(256), 0,
+                            static_cast<cudaStream_t>(stream), x, col, s, kpad));
+  return B2D_OK;
+}

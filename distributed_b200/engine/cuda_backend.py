@@ -44,19 +44,21 @@ class CudaBackend:
         ci = layer.input_shape[2]
         x_shape = (1, *layer.input_shape)
         w_shape = (*layer.kernel_size, ci, layer.filters)
-        if self._conv_tc_ok(x_shape, w_shape, layer.strides, layer.pad_amounts()):
+        if self._conv_tc_ok(x_shape, w_shape, layer.strides, layer.pad_amounts(), out_hw=layer.output_shape[:2]):
             return "tcgen05 tf32 implicit GEMM (4-D TMA taps)"
         return "direct conv (CUDA cores)"
 
     @staticmethod
-    def _conv_tc_ok(x_shape, w_shape, strides, pad, dgrad=False):
+    def _conv_tc_ok(x_shape, w_shape, strides, pad, dgrad=False, out_hw=None):
         from ..ops import conv as tc
         if os.environ.get("B200DIST_CONV", "") == "direct":
             return False
-        kh, kw = w_shape[0], w_shape[1]
-        if tuple(strides) == (1, 1) and tuple(pad) != (0, 0) and ((kh - 1) % 2 or (kw - 1) % 2):
-            return False        # 'same' with an even kernel pads asymmetrically: direct kernels only
-        return tc.tc_supported(tuple(x_shape), tuple(w_shape), pad, torch.float32, dgrad=dgrad, strides=strides)
+        if dgrad and out_hw is not None and tuple(strides) == (1, 1):
+            # the unit-stride data gradient assumes symmetric padding
+            if (x_shape[1] + 2 * pad[0] - w_shape[0] + 1, x_shape[2] + 2 * pad[1] - w_shape[1] + 1) != tuple(out_hw):
+                return False
+        return tc.tc_supported(tuple(x_shape), tuple(w_shape), pad, torch.float32, dgrad=dgrad, strides=strides,
+                               out_hw=out_hw)
 
     def describe_dense(self, b, k, n):
         return "tcgen05 tf32 GEMM" if self._tc_ok(k, n) else "CUDA-core GEMM"
@@ -76,19 +78,52 @@ class CudaBackend:
     # ---- general conv (direct fallback; implicit-GEMM path plugs in here) --------------
     def conv2d_fwd(self, x, w, b, y, strides, pad, relu):
         from ..ops import conv as tc
-        if self._conv_tc_ok(x.shape, w.shape, strides, pad):
-            plan = tc.ConvFwdPlan(x, w, y, pad, bias=b, relu=relu)
+        if self._conv_tc_ok(x.shape, w.shape, strides, pad, out_hw=y.shape[1:3]):
+            plan = tc.ConvFwdPlan(x, w, y, pad, bias=b, relu=relu, stride=strides[0])
             self.plans.append(plan)
             return plan.run
+        if self._im2col_ok(x, w, y):
+            # small C_in (e.g. the 3-channel ResNet stem): patch matrix once, then tensor-core GEMMs
+            col = self._col_for(x, w, y, strides, pad)
+            k = w.shape[0] * w.shape[1] * w.shape[2]
+            gemm = self._plan(col[:, :k], w.view(k, w.shape[3]), y.view(-1, y.shape[3]), b_mn_major=True, bias=b,
+                              relu=relu)
+            kh_kw, st, pd, ohw = (w.shape[0], w.shape[1]), tuple(strides), tuple(pad), (y.shape[1], y.shape[2])
+
+            def run():
+                nn.im2col(x, col, kh_kw, st, pd, ohw)
+                gemm()
+            return run
         return lambda: nn.conv2d_fwd_direct(x, w, b, y, strides, pad, relu)
+
+    def _im2col_ok(self, x, w, y):
+        k = w.shape[0] * w.shape[1] * w.shape[2]
+        return (os.environ.get("B200DIST_CONV", "") != "direct" and (x.shape[3] * 4) % 128 != 0 and k >= 32
+                and w.shape[3] % 4 == 0 and y.numel() // y.shape[3] >= 1024)
+
+    def _col_for(self, x, w, y, strides, pad):
+        """One patch matrix per (input tensor, geometry): written by the forward, reused by wgrad."""
+        k = w.shape[0] * w.shape[1] * w.shape[2]
+        key = (x.data_ptr(), tuple(w.shape[:3]), tuple(strides), tuple(pad), y.shape[1], y.shape[2])
+        cache = self.__dict__.setdefault("_cols", {})
+        if key not in cache:
+            cache[key] = self.alloc((y.numel() // y.shape[3], (k + 3) // 4 * 4))
+        return cache[key]
 
     def conv2d_wgrad(self, x, dy, dw, db, strides, pad):
         from ..ops import conv as tc
         dy2 = dy.view(-1, dy.shape[-1])
-        if self._conv_tc_ok(x.shape, dw.shape, strides, pad) and x.shape[3] % 4 == 0 and dw.shape[3] % 4 == 0:
-            plan = tc.ConvWgradPlan(x, dy, dw, pad)
+        if (self._conv_tc_ok(x.shape, dw.shape, strides, pad, out_hw=dy.shape[1:3]) and x.shape[3] % 4 == 0
+                and dw.shape[3] % 4 == 0):
+            plan = tc.ConvWgradPlan(x, dy, dw, pad, stride=strides[0])
             self.plans.append(plan)
             wgrad = plan.run
+        elif self._im2col_ok(x, dw, dy):
+            col = self._col_for(x, dw, dy, strides, pad)        # filled by this step's forward pass
+            k = dw.shape[0] * dw.shape[1] * dw.shape[2]
+            # the padding columns of col are excluded by the view; its row pitch stays 16-byte aligned
+            wgrad = self._plan(col[:, :k], dy2, dw.view(k, dw.shape[3]), a_mn_major=True, b_mn_major=True,
+                               accumulate=True)
         else:
             def wgrad():
                 nn.conv2d_wgrad_direct(x, dy, dw, strides, pad)
@@ -101,7 +136,12 @@ class CudaBackend:
 
     def conv2d_dgrad(self, dy, w, dx, strides, pad, mask=None):
         from ..ops import conv as tc
-        if self._conv_tc_ok(dx.shape, w.shape, strides, pad, dgrad=True):
+        if (strides[0] == strides[1] and strides[0] > 1 and os.environ.get("B200DIST_CONV", "") != "direct"
+                and tc.dgrad_strided_supported(dx.shape, w.shape, strides[0], torch.float32)):
+            plan = tc.ConvDgradStridedPlan(dy, w, dx, pad, strides[0], mask=mask)
+            self.plans.append(plan)
+            return plan.run
+        if self._conv_tc_ok(dx.shape, w.shape, strides, pad, dgrad=True, out_hw=dy.shape[1:3]):
             plan = tc.ConvDgradPlan(dy, w, dx, pad, mask=mask)     # ReLU mask fused in the epilogue
             self.plans.append(plan)
             return plan.run

@@ -20,7 +20,8 @@ class ConvDesc(C.Structure):
                 ("N", C.c_int), ("H", C.c_int), ("W", C.c_int), ("Ci", C.c_int), ("Co", C.c_int),
                 ("KH", C.c_int), ("KW", C.c_int), ("pad_h", C.c_int), ("pad_w", C.c_int),
                 ("x", C.c_void_p), ("w", C.c_void_p), ("y", C.c_void_p),
-                ("bias", C.c_void_p), ("mask", C.c_void_p), ("relu", C.c_int)]
+                ("bias", C.c_void_p), ("mask", C.c_void_p), ("relu", C.c_int),
+                ("stride", C.c_int), ("OH", C.c_int), ("OW", C.c_int)]
 
 
 _declared = False
@@ -33,6 +34,8 @@ def _lib():
         lib.b2d_conv_tc_supported.argtypes = [C.POINTER(ConvDesc), C.c_int]
         lib.b2d_conv_fwd_plan_create.argtypes = [C.POINTER(ConvDesc), C.POINTER(C.c_void_p)]
         lib.b2d_conv_dgrad_plan_create.argtypes = [C.POINTER(ConvDesc), C.POINTER(C.c_void_p)]
+        lib.b2d_conv_dgrad_class_plan_create.argtypes = [C.POINTER(ConvDesc), C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        lib.b2d_memset_async.argtypes = [C.c_void_p, C.c_int, C.c_size_t, C.c_void_p]
         lib.b2d_conv_wgrad_plan_create.argtypes = [C.POINTER(ConvDesc), C.POINTER(C.c_void_p)]
         lib.b2d_conv_wgrad_plan_run.argtypes = [C.c_void_p, C.c_void_p]
         lib.b2d_conv_wgrad_plan_destroy.argtypes = [C.c_void_p]
@@ -41,7 +44,7 @@ def _lib():
     return lib
 
 
-def _desc(x, w, y, padding, bias=None, mask=None, relu=False):
+def _desc(x, w, y, padding, bias=None, mask=None, relu=False, stride=1):
     N, H, W, Ci = x.shape
     KH, KW, Ci2, Co = w.shape
     assert Ci == Ci2 and x.dtype == w.dtype
@@ -53,13 +56,17 @@ def _desc(x, w, y, padding, bias=None, mask=None, relu=False):
     d.bias = bias.data_ptr() if bias is not None else None
     d.mask = mask.data_ptr() if mask is not None else None
     d.relu = int(relu)
+    d.stride, d.OH, d.OW = int(stride), y.shape[1], y.shape[2]
     return d
 
 
-def tc_supported(x_shape, w_shape, padding, dtype, dgrad=False, strides=(1, 1)) -> bool:
-    if tuple(strides) != (1, 1) or dtype not in _DT:
+def tc_supported(x_shape, w_shape, padding, dtype, dgrad=False, strides=(1, 1), out_hw=None) -> bool:
+    if strides[0] != strides[1] or dtype not in _DT:
         return False
     d = ConvDesc()
+    d.stride = int(strides[0])
+    if out_hw is not None:
+        d.OH, d.OW = out_hw
     d.dtype = d.out_dtype = _DT[dtype]
     d.N, d.H, d.W, d.Ci = x_shape
     d.KH, d.KW, _, d.Co = w_shape
@@ -88,8 +95,8 @@ class _Plan:
 class ConvFwdPlan(_Plan):
     """y = act(conv2d(x, w) + bias), x [N,H,W,Ci], w [KH,KW,Ci,Co], y [N,OH,OW,Co]."""
 
-    def __init__(self, x, w, y, padding=(0, 0), bias=None, relu=False):
-        super().__init__(_lib().b2d_conv_fwd_plan_create, _desc(x, w, y, padding, bias, None, relu),
+    def __init__(self, x, w, y, padding=(0, 0), bias=None, relu=False, stride=1):
+        super().__init__(_lib().b2d_conv_fwd_plan_create, _desc(x, w, y, padding, bias, None, relu, stride),
                          [x, w, y, bias])
 
 
@@ -101,12 +108,57 @@ class ConvDgradPlan(_Plan):
                          [dy, w, dx, mask])
 
 
+class ConvDgradStridedPlan:
+    """dx for a strided convolution: stride^2 unit-stride sub-convolutions of dy, one per parity
+    class of the output pixel; classes without taps are covered by clearing dx first."""
+
+    def __init__(self, dy, w, dx, padding, stride, mask=None):
+        self._lib = _lib()
+        self._keep = [dy, w, dx, mask]
+        d = _desc(dx, w, dy, padding, None, mask, False, stride)
+        self._plans, self._need_clear = [], False
+        for a in range(stride):
+            for b in range(stride):
+                h = C.c_void_p()
+                nl.check(self._lib.b2d_conv_dgrad_class_plan_create(C.byref(d), a, b, C.byref(h)),
+                         "conv dgrad class plan create")
+                if h.value:
+                    self._plans.append(h)
+                else:
+                    self._need_clear = True
+        self._dx = dx
+
+    def run(self, stream=None):
+        st = _stream_ptr(stream)
+        if self._need_clear:
+            nl.check(self._lib.b2d_memset_async(self._dx.data_ptr(), 0, self._dx.numel() * self._dx.element_size(), st),
+                     "memset")
+        for h in self._plans:
+            nl.check(self._lib.b2d_gemm_plan_run(h, st), "conv dgrad class run")
+
+    __call__ = run
+
+    def __del__(self):
+        for h in getattr(self, "_plans", []):
+            self._lib.b2d_gemm_plan_destroy(h)
+        self._plans = []
+
+
+def dgrad_strided_supported(dx_shape, w_shape, stride, dtype) -> bool:
+    if dtype not in _DT or stride < 2:
+        return False
+    es = 4 if dtype == torch.float32 else 2
+    _, H, W, Ci = dx_shape
+    Co = w_shape[3]
+    return (Co * es) % 128 == 0 and Ci % 4 == 0 and (W + stride - 1) // stride <= 128
+
+
 class ConvWgradPlan:
     """dw += x (*) dy over all pixels (fp32 accumulation into dw [KH,KW,Ci,Co])."""
 
-    def __init__(self, x, dy, dw, padding=(0, 0)):
+    def __init__(self, x, dy, dw, padding=(0, 0), stride=1):
         self._lib = _lib()
-        d = _desc(x, dw, dy, padding)
+        d = _desc(x, dw, dy, padding, stride=stride)
         d.dtype = _DT[x.dtype]
         h = C.c_void_p()
         nl.check(self._lib.b2d_conv_wgrad_plan_create(C.byref(d), C.byref(h)), "conv wgrad plan create")

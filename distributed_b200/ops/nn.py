@@ -42,6 +42,7 @@ def _lib():
         lib.b2d_maxpool_bwd.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, i, i, vp]
         lib.b2d_gap_fwd.argtypes = [vp, vp, i, i, i, vp]
         lib.b2d_gap_bwd.argtypes = [vp, vp, i, i, i, vp]
+        lib.b2d_im2col.argtypes = [vp, vp] + [i] * 13 + [vp]
         _declared = True
     return lib
 
@@ -191,3 +192,10 @@ def gap_fwd(x, y):
 def gap_bwd(dy, dx):
     N, H, W, Cc = dx.shape
     nl.check(_lib().b2d_gap_bwd(_p(dy), _p(dx), N, H * W, Cc, _s()), "gap_bwd")
+
+
+def im2col(x, col, kernel, strides, padding, out_hw):
+    """col[pixel, :] = flattened (kh, kw, ci) patch of x for every output pixel; col is [N*OH*OW, kpad]."""
+    N, H, W, Ci = x.shape
+    nl.check(_lib().b2d_im2col(_p(x), _p(col), N, H, W, Ci, kernel[0], kernel[1], strides[0], strides[1],
+                               padding[0], padding[1], out_hw[0], out_hw[1], col.shape[1], _s()), "im2col")

@@ -103,7 +103,8 @@ size_t b2d_gemm_noalloc_max_workspace_floats(void);
 size_t b2d_gemm_noalloc_max_tiles(void);
 
 /* ---------------------------------------------------------------------------------------
- * Implicit-GEMM convolution on the same tensor-core kernel (Conv2D, README.md:293; stride 1).
+ * Implicit-GEMM convolution on the same tensor-core kernel (Conv2D, README.md:293).  Forward and
+ * filter gradient take any stride (TMA traversal stride); the data gradient is unit-stride.
  * forward: x [N,H,W,Ci], w [KH,KW,Ci,Co] -> y [N,OH,OW,Co] (+bias, ReLU)
  * dgrad  : x is the OUTPUT dx, y is the INPUT dy; optional ReLU mask shaped like dx
  * wgrad  : w is the OUTPUT dW (fp32, accumulated), y is dy
@@ -120,11 +121,18 @@ typedef struct b2d_conv_desc {
   const float* bias;
   const float* mask;
   int relu;
+  int stride;   /* forward / wgrad: input step per output pixel (0 or 1 = unit stride)          */
+  int OH, OW;   /* output size; 0 = derive from symmetric padding (TF 'same' may be asymmetric:  */
+                /* pad_h / pad_w are the top / left amounts, the output size fixes the rest)    */
 } b2d_conv_desc;
 typedef struct b2d_conv_wgrad_plan b2d_conv_wgrad_plan;
 int b2d_conv_tc_supported(const b2d_conv_desc* desc, int dgrad);
 int b2d_conv_fwd_plan_create(const b2d_conv_desc* desc, b2d_gemm_plan** out);
 int b2d_conv_dgrad_plan_create(const b2d_conv_desc* desc, b2d_gemm_plan** out);
+/* Strided data gradient: one plan per output-pixel parity class (a, b) in [0, stride)^2; *out is
+ * NULL for a class without filter taps (clear dx first with b2d_memset_async). */
+int b2d_conv_dgrad_class_plan_create(const b2d_conv_desc* desc, int a, int b, b2d_gemm_plan** out);
+int b2d_memset_async(void* ptr, int value, size_t bytes, void* stream);
 int b2d_conv_wgrad_plan_create(const b2d_conv_desc* desc, b2d_conv_wgrad_plan** out);
 int b2d_conv_wgrad_plan_run(const b2d_conv_wgrad_plan* plan, void* stream);
 void b2d_conv_wgrad_plan_destroy(b2d_conv_wgrad_plan* plan);
@@ -165,6 +173,9 @@ int b2d_conv2d_dgrad_direct(const float* dy, const float* w, float* dx, int N, i
 int b2d_conv2d_wgrad_direct(const float* x, const float* dy, float* dw, int N, int H, int W, int Ci,
                             int Co, int KH, int KW, int sh, int sw, int ph, int pw, int OH, int OW,
                             void* stream);
+/* Patch matrix for small-channel convolutions (feeds the tcgen05 GEMM): col[pixel][kpad], kpad >= KH*KW*Ci. */
+int b2d_im2col(const float* x, float* col, int N, int H, int W, int Ci, int KH, int KW, int sh, int sw, int ph,
+               int pw, int OH, int OW, int kpad, void* stream);
 /* CUDA-core GEMM with arbitrary strides (tiny / unaligned problems). */
 int b2d_sgemm_simt(const float* A, int64_t sam, int64_t sak, const float* B, int64_t sbk, int64_t sbn,
                    float* D, int64_t ldd, const float* bias, int M, int N, int K, int relu,

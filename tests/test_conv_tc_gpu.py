@@ -46,3 +46,37 @@ def test_conv_forward_dgrad_wgrad(N, H, W, Ci, Co, K, pad):
     dw = torch.ones_like(w)
     ConvWgradPlan(x.detach(), dpre, dw, (pad, pad)).run()
     assert (dw - 1 - w.grad).abs().max().item() < 3e-3 * w.grad.abs().max().item()
+
+
+@pytest.mark.parametrize("N,H,W,Ci,Co,K,stride", [(4, 56, 56, 64, 128, 1, 2), (3, 28, 28, 128, 128, 3, 2),
+                                                  (2, 14, 14, 256, 64, 3, 2), (2, 15, 15, 32, 64, 3, 2)])
+def test_strided_conv_forward_and_wgrad(N, H, W, Ci, Co, K, stride):
+    """TensorFlow 'same' padding with stride 2: top/left pad = total // 2, the rest at the end."""
+    import math
+    from distributed_b200.ops.conv import ConvFwdPlan, ConvWgradPlan, tc_supported
+    g = torch.Generator(device="cuda").manual_seed(N + H + Co)
+    x = (torch.randn((N, H, W, Ci), device="cuda", generator=g) * 0.5).requires_grad_()
+    w = (torch.randn((K, K, Ci, Co), device="cuda", generator=g) * 0.1).requires_grad_()
+    OH = math.ceil(H / stride)
+    total = max((OH - 1) * stride + K - H, 0)
+    p0 = total // 2
+    xp = F.pad(x.permute(0, 3, 1, 2), (p0, total - p0, p0, total - p0))
+    ref = F.conv2d(xp, w.permute(3, 2, 0, 1), None, stride=stride).permute(0, 2, 3, 1).contiguous()
+    assert ref.shape[1] == OH
+    assert tc_supported(x.shape, w.shape, (p0, p0), torch.float32, strides=(stride, stride), out_hw=(OH, OH))
+    y = torch.full(ref.shape, float("nan"), device="cuda")
+    ConvFwdPlan(x.detach(), w.detach(), y, (p0, p0), stride=stride).run()
+    assert (y - ref).abs().max().item() < 3e-3 * ref.abs().max().item()
+    dy = torch.randn(ref.shape, device="cuda", generator=g)
+    ref.backward(dy)
+    dw = torch.zeros_like(w)
+    ConvWgradPlan(x.detach(), dy, dw, (p0, p0), stride=stride).run()
+    assert (dw - w.grad).abs().max().item() < 3e-3 * w.grad.abs().max().item()
+    from distributed_b200.ops.conv import ConvDgradStridedPlan, dgrad_strided_supported
+    assert dgrad_strided_supported(x.shape, w.shape, stride, torch.float32)
+    dx = torch.full(x.shape, float("nan"), device="cuda")
+    ConvDgradStridedPlan(dy, w.detach(), dx, (p0, p0), stride).run()
+    assert (dx - x.grad).abs().max().item() < 3e-3 * x.grad.abs().max().item()
+    mask = torch.randn(x.shape, device="cuda", generator=g)
+    ConvDgradStridedPlan(dy, w.detach(), dx, (p0, p0), stride, mask=mask).run()
+    assert (dx - x.grad * (mask > 0)).abs().max().item() < 3e-3 * x.grad.abs().max().item()
