@@ -35,53 +35,72 @@ sys.path.insert(0, str(ROOT))
 
 # ----------------------------------------------------------------------------------------
 class ClockSampler:
-    """Samples SM clocks and throttle reasons with nvidia-smi while the timed region runs."""
-    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-              "clocks_event_reasons.sw_power_cap")
+    """Samples SM clocks and throttle reasons while the timed region runs.
 
-    def __init__(self, index: int, period_ms: int = 100):
-        self.index, self.period_ms = index, period_ms
-        self.rows: list[list[str]] = []
-        self.proc = None
+    NVML is polled from a thread every few milliseconds (the timed region of the README model is
+    only tens of milliseconds long, shorter than `nvidia-smi -lms` takes to start); `nvidia-smi`
+    is the fallback when the NVML bindings are missing."""
+    REASONS = {"hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40,
+               "hw_power_brake_slowdown": 0x80, "sw_power_cap": 0x4}
+
+    def __init__(self, index: int, period_ms: float = 4.0):
+        self.index, self.period = index, period_ms / 1000.0
+        self.sm: list[float] = []
+        self.mask = 0
+        self.max_mhz = None
+        self.power_w = 0.0
+        self._stop = threading.Event()
+        self._thread = None
+        self._nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nvml = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self._nvml = None
+
+    def _poll(self):
+        n = self._nvml
+        while not self._stop.is_set():
+            try:
+                self.sm.append(float(n.nvmlDeviceGetClockInfo(self._h, n.NVML_CLOCK_SM)))
+                self.mask |= int(n.nvmlDeviceGetCurrentClocksEventReasons(self._h))
+                self.power_w = max(self.power_w, n.nvmlDeviceGetPowerUsage(self._h) / 1000.0)
+            except Exception:
+                pass
+            self._stop.wait(self.period)
 
     def __enter__(self):
-        try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
-                 "-i", str(self.index), "-lms", str(self.period_ms)],
-                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
-            self.thread.start()
-        except OSError:
-            self.proc = None
+        if self._nvml is not None:
+            self._thread = threading.Thread(target=self._poll, daemon=True)
+            self._thread.start()
         return self
 
-    def _read(self):
-        for line in self.proc.stdout:
-            parts = [p.strip() for p in line.split(",")]
-            if len(parts) >= 7:
-                self.rows.append(parts)
-
     def __exit__(self, *a):
-        if self.proc is not None:
-            time.sleep(self.period_ms / 1000.0)
-            self.proc.terminate()
-            try:
-                self.proc.wait(timeout=5)
-            except Exception:
-                self.proc.kill()
+        self._stop.set()
+        if self._thread is not None:
+            self._thread.join(timeout=2)
+        elif self._nvml is None:
+            self._smi_once()
         return False
 
+    def _smi_once(self):
+        try:
+            out = subprocess.run(["nvidia-smi", "--query-gpu=clocks.sm,clocks.max.sm", "--format=csv,noheader,nounits",
+                                  "-i", str(self.index)], capture_output=True, text=True, timeout=10).stdout
+            a, b = [float(v) for v in out.strip().split(",")[:2]]
+            self.sm.append(a)
+            self.max_mhz = b
+        except Exception:
+            pass
+
     def summary(self) -> dict:
-        if not self.rows:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        sm = sorted(float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit())
-        mx = max((float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()), default=None)
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in self.rows)]
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": reasons,
-                "samples": len(self.rows)}
+        sm = sorted(self.sm)
+        reasons = [k for k, bit in self.REASONS.items() if self.mask & bit]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz, "reasons": reasons,
+                "samples": len(sm), "power_w_max": round(self.power_w, 1)}
 
 
 def _dist_env():
@@ -209,8 +228,8 @@ def run_torch(args) -> dict:
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=300)
-    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=50)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "torch"])
     ap.add_argument("--model", default="mnist_cnn", choices=["mnist_cnn", "scaled_cnn", "resnet50"])
     ap.add_argument("--batch-per-gpu", type=int, default=None)
