@@ -144,6 +144,7 @@ def run_ours(args) -> dict:
     else:
         strategy = tf.distribute.OneDeviceStrategy()
     shape, classes = MODEL_INPUT[args.model]
+    tf.keras.mixed_precision.set_global_policy("mixed_bfloat16" if args.dtype == "bf16" else "float32")
     with strategy.scope():
         model = {"mnist_cnn": tf.models.mnist_cnn, "scaled_cnn": tf.models.scaled_cnn,
                  "resnet50": lambda: tf.models.resnet50(learning_rate=0.01)}[args.model]()
@@ -188,7 +189,9 @@ def run_ours(args) -> dict:
         "metric": "images/sec (device-timed, max over ranks)", "value": value, "unit": "images/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "tf32 (fp32 storage, fp32 accumulate; first conv in fp32)", "data": "synthetic",
+        "dtype": ("bf16 (bf16 activations / activation gradients / conv operands, fp32 accumulate, fp32 master "
+                  "weights and statistics; Dense head tf32)" if args.dtype == "bf16"
+                  else "tf32 (fp32 storage, fp32 accumulate; first conv in fp32)"), "data": "synthetic",
         "impl": "distributed_b200",
         "config": {"model": MODEL_NAMES[args.model],
                    "global_batch": global_batch, "batch_per_gpu": per_gpu, "input": "x".join(map(str, shape)),
@@ -234,11 +237,16 @@ def main():
     ap.add_argument("--model", default="mnist_cnn", choices=["mnist_cnn", "scaled_cnn", "resnet50"])
     ap.add_argument("--batch-per-gpu", type=int, default=None)
     ap.add_argument("--dataset-images", type=int, default=None)
+    ap.add_argument("--dtype", default=None, choices=["tf32", "bf16"],
+                    help="ours: storage/compute type of the convolutional stack (default: bf16 for resnet50 as "
+                         "BASELINE.json names it, tf32-on-fp32 for the MNIST CNNs as the reference trains in float32)")
     ap.add_argument("--channels-last", action="store_true", help="torch baseline: channels_last + bf16 autocast")
     ap.add_argument("--torch-graph", action="store_true", help="torch baseline: capture the step in a CUDA graph")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
+    if args.dtype is None:
+        args.dtype = "bf16" if args.model == "resnet50" else "tf32"
     if args.batch_per_gpu is None:
         args.batch_per_gpu = 32 if args.model == "resnet50" else 64
     if args.dataset_images is None:

@@ -49,10 +49,12 @@ struct ConvShape {
   int N, H, W, Ci, Co, KH, KW, OH, OW, sh, sw, ph, pw;
 };
 
+// ph, pw = padding at the top / left; OH, OW = output size (<= 0: derive from symmetric padding).
+// TensorFlow's 'same' padding is asymmetric for even totals, which the explicit size expresses.
 ConvShape make_shape(int N, int H, int W, int Ci, int Co, int KH, int KW, int sh, int sw, int ph,
-                     int pw) {
-  return ConvShape{N, H, W, Ci, Co, KH, KW, (H + 2 * ph - KH) / sh + 1, (W + 2 * pw - KW) / sw + 1,
-                   sh, sw, ph, pw};
+                     int pw, int OH, int OW) {
+  return ConvShape{N, H, W, Ci, Co, KH, KW, OH > 0 ? OH : (H + 2 * ph - KH) / sh + 1,
+                   OW > 0 ? OW : (W + 2 * pw - KW) / sw + 1, sh, sw, ph, pw};
 }
 
 }  // namespace
@@ -62,8 +64,8 @@ B2C_API void b2c_set_num_threads(int n) { g_threads = n; }
 // y[n,oh,ow,:] = act(b + sum_{kh,kw,ci} x[n,ih,iw,ci] * w[kh,kw,ci,:])               [K1]
 B2C_API void b2c_conv2d_fwd(const float* x, const float* w, const float* bias, float* y, int N, int H,
                             int W, int Ci, int Co, int KH, int KW, int sh, int sw, int ph, int pw,
-                            int relu) {
-  const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw);
+                            int OH, int OW, int relu) {
+  const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw, OH, OW);
   parallel_for((int64_t)N * s.OH, 4, [&](int64_t b, int64_t e) {
     std::vector<float> acc(Co);
     for (int64_t r = b; r < e; ++r) {
@@ -94,8 +96,9 @@ B2C_API void b2c_conv2d_fwd(const float* x, const float* w, const float* bias, f
 
 // dW[kh,kw,ci,:] += sum x[n,ih,iw,ci] * dy[n,oh,ow,:] ;  db[:] += sum dy            [K9]
 B2C_API void b2c_conv2d_wgrad(const float* x, const float* dy, float* dw, float* db, int N, int H,
-                              int W, int Ci, int Co, int KH, int KW, int sh, int sw, int ph, int pw) {
-  const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw);
+                              int W, int Ci, int Co, int KH, int KW, int sh, int sw, int ph, int pw,
+                              int OH, int OW) {
+  const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw, OH, OW);
   // Parallel over filter taps (kh, kw, ci): each owns a disjoint dW row, so no reduction.
   parallel_for((int64_t)KH * KW * Ci, 1, [&](int64_t b, int64_t e) {
     for (int64_t tap = b; tap < e; ++tap) {
@@ -124,8 +127,8 @@ B2C_API void b2c_conv2d_wgrad(const float* x, const float* dy, float* dw, float*
 
 // dx[n,ih,iw,ci] = sum_{kh,kw,co} dy[n,oh,ow,co] * w[kh,kw,ci,co]                     [K10]
 B2C_API void b2c_conv2d_dgrad(const float* dy, const float* w, float* dx, int N, int H, int W, int Ci,
-                              int Co, int KH, int KW, int sh, int sw, int ph, int pw) {
-  const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw);
+                              int Co, int KH, int KW, int sh, int sw, int ph, int pw, int OH, int OW) {
+  const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw, OH, OW);
   parallel_for((int64_t)N * H, 4, [&](int64_t b, int64_t e) {
     for (int64_t r = b; r < e; ++r) {
       const int n = r / H, ih = r % H;

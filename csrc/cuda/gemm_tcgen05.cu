@@ -32,6 +32,7 @@ enum GemmFlags : int {
   kFlagAccumulate = 2,  // D += tile via fp32 vector atomics
   kFlagFinalize = 4,    // split-K: meet in workspace, last CTA applies the epilogue
   kFlagOutBf16 = 8,
+  kFlagMaskBf16 = 16,   // the ReLU mask tensor is bf16 (same row pitch convention, in elements)
 };
 
 // Implicit-GEMM convolution view of the A operand (stride-1 NHWC convolutions): the M tile is a
@@ -64,7 +65,7 @@ struct GemmArgs {
   int stages;
   void* D;
   const float* bias;
-  const float* mask;
+  const void* mask;
   float* ws;
   uint32_t* counters;
   long long ldd;
@@ -104,7 +105,15 @@ __device__ __forceinline__ void epilogue_store4(const GemmArgs& a, int row, int 
     v0 = fmaxf(v0, 0.f), v1 = fmaxf(v1, 0.f), v2 = fmaxf(v2, 0.f), v3 = fmaxf(v3, 0.f);
   }
   if (a.mask != nullptr) {
-    const float4 m = *reinterpret_cast<const float4*>(a.mask + (long long)row * a.ldmask + col);
+    float4 m;
+    if (a.flags & kFlagMaskBf16) {
+      const uint2 t = *reinterpret_cast<const uint2*>(static_cast<const uint16_t*>(a.mask) +
+                                                      (long long)row * a.ldmask + col);
+      m = make_float4(__uint_as_float(t.x << 16), __uint_as_float(t.x & 0xffff0000u),
+                      __uint_as_float(t.y << 16), __uint_as_float(t.y & 0xffff0000u));
+    } else {
+      m = *reinterpret_cast<const float4*>(static_cast<const float*>(a.mask) + (long long)row * a.ldmask + col);
+    }
     v0 = m.x > 0.f ? v0 : 0.f, v1 = m.y > 0.f ? v1 : 0.f;
     v2 = m.z > 0.f ? v2 : 0.f, v3 = m.w > 0.f ? v3 : 0.f;
   }
@@ -119,6 +128,41 @@ __device__ __forceinline__ void epilogue_store4(const GemmArgs& a, int row, int 
     *reinterpret_cast<float4*>(reinterpret_cast<float*>(a.D) + (long long)row * a.ldd + col) =
         make_float4(v0, v1, v2, v3);
   }
+}
+
+// bf16 output, eight consecutive columns of one row as ONE 16-byte store (plain store only: no
+// accumulate / split-K).  Requires col + 8 <= N and 16-byte aligned rows (ldd % 8 == 0).
+__device__ __forceinline__ void epilogue_store8_bf16(const GemmArgs& a, int row, int col, float (&v)[8]) {
+  if (a.bias != nullptr) {
+    const float4 b0 = *reinterpret_cast<const float4*>(a.bias + col);
+    const float4 b1 = *reinterpret_cast<const float4*>(a.bias + col + 4);
+    v[0] += b0.x, v[1] += b0.y, v[2] += b0.z, v[3] += b0.w;
+    v[4] += b1.x, v[5] += b1.y, v[6] += b1.z, v[7] += b1.w;
+  }
+  if (a.flags & kFlagRelu) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
+  }
+  if (a.mask != nullptr) {
+    float m[8];
+    if (a.flags & kFlagMaskBf16) {
+      const uint4 t = *reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(a.mask) +
+                                                      (long long)row * a.ldmask + col);
+      const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) m[2 * k] = __uint_as_float(w[k] << 16), m[2 * k + 1] = __uint_as_float(w[k] & 0xffff0000u);
+    } else {
+      const float* mp = static_cast<const float*>(a.mask) + (long long)row * a.ldmask + col;
+      const float4 m0 = *reinterpret_cast<const float4*>(mp), m1 = *reinterpret_cast<const float4*>(mp + 4);
+      m[0] = m0.x, m[1] = m0.y, m[2] = m0.z, m[3] = m0.w, m[4] = m1.x, m[5] = m1.y, m[6] = m1.z, m[7] = m1.w;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = m[k] > 0.f ? v[k] : 0.f;
+  }
+  uint4 p;
+  p.x = pack_bf16x2(v[0], v[1]), p.y = pack_bf16x2(v[2], v[3]);
+  p.z = pack_bf16x2(v[4], v[5]), p.w = pack_bf16x2(v[6], v[7]);
+  *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(a.D) + (long long)row * a.ldd + col) = p;
 }
 
 template <MmaKind KIND, bool A_MN, bool B_MN, int BLOCK_N>
@@ -296,6 +340,9 @@ __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const __grid_constant__
     tc_fence_after();
     if (dbg != nullptr && threadIdx.x == 128) dbg[5] = gtime_ns();   // accumulator visible to the epilogue
     const bool finalize = (args.flags & kFlagFinalize) != 0;
+    // bf16 output written directly (no split-K meeting, no accumulation): 16-byte stores
+    const bool wide_bf16 = (args.flags & (kFlagOutBf16 | kFlagFinalize | kFlagAccumulate)) == kFlagOutBf16 &&
+                           (args.ldd & 7) == 0 && (args.mask == nullptr || (args.ldmask & 7) == 0);
     // Each thread owns one accumulator row (TMEM lane) and stores 32 consecutive columns per chunk.
     // (A shared-memory transposed, fully coalesced variant measured the same latency on the small
     // GEMMs and 9% lower throughput at 8192^3, so the direct form stays.)
@@ -306,16 +353,26 @@ __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const __grid_constant__
       tmem_ld_wait();
       const int col0 = n0 + c * 32;
       if (row_ok) {
+        if (wide_bf16 && col0 + 32 <= args.N) {
 #pragma unroll
-        for (int g = 0; g < 8; ++g) {
-          const int col = col0 + g * 4;
-          if (col < args.N) {
-            const float f0 = __uint_as_float(v[g * 4 + 0]), f1 = __uint_as_float(v[g * 4 + 1]);
-            const float f2 = __uint_as_float(v[g * 4 + 2]), f3 = __uint_as_float(v[g * 4 + 3]);
-            if (finalize)
-              red_add_f4(args.ws + (long long)row * args.ldws + col, f0, f1, f2, f3);
-            else
-              epilogue_store4(args, row, col, f0, f1, f2, f3);
+          for (int g = 0; g < 4; ++g) {
+            float f[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) f[k] = __uint_as_float(v[g * 8 + k]);
+            epilogue_store8_bf16(args, row, col0 + g * 8, f);
+          }
+        } else {
+#pragma unroll
+          for (int g = 0; g < 8; ++g) {
+            const int col = col0 + g * 4;
+            if (col < args.N) {
+              const float f0 = __uint_as_float(v[g * 4 + 0]), f1 = __uint_as_float(v[g * 4 + 1]);
+              const float f2 = __uint_as_float(v[g * 4 + 2]), f3 = __uint_as_float(v[g * 4 + 3]);
+              if (finalize)
+                red_add_f4(args.ws + (long long)row * args.ldws + col, f0, f1, f2, f3);
+              else
+                epilogue_store4(args, row, col, f0, f1, f2, f3);
+            }
           }
         }
       }
@@ -559,7 +616,8 @@ extern "C" int b2d_gemm_plan_create(const b2d_gemm_desc* desc, b2d_gemm_plan** o
   a.M = d.M, a.N = d.N, a.K = d.K;
   a.kb_total = g.k_blocks, a.kb_per_split = ceil_div(g.k_blocks, g.splits), a.splits = g.splits;
   a.flags = (d.relu ? kFlagRelu : 0) | (d.accumulate ? kFlagAccumulate : 0) |
-            (finalize ? kFlagFinalize : 0) | (d.out_dtype == B2D_BF16 ? kFlagOutBf16 : 0);
+            (finalize ? kFlagFinalize : 0) | (d.out_dtype == B2D_BF16 ? kFlagOutBf16 : 0) |
+            (d.mask != nullptr && d.mask_dtype == B2D_BF16 ? kFlagMaskBf16 : 0);
   a.stages = g.stages;
   p->launch_smem = g.smem_bytes;
   p->geo = g;
@@ -722,7 +780,8 @@ static int conv_plan_create(const b2d_conv_desc& d, bool dgrad, b2d_gemm_plan** 
   a.ldd = n_ch, a.ldmask = n_ch, a.ldws = 0;
   a.M = gd.M, a.N = gd.N, a.K = gd.K;
   a.kb_total = g.k_blocks, a.kb_per_split = g.k_blocks, a.splits = 1;
-  a.flags = (d.relu ? kFlagRelu : 0) | (d.out_dtype == B2D_BF16 ? kFlagOutBf16 : 0);
+  a.flags = (d.relu ? kFlagRelu : 0) | (d.out_dtype == B2D_BF16 ? kFlagOutBf16 : 0) |
+            (d.mask != nullptr && d.mask_dtype == B2D_BF16 ? kFlagMaskBf16 : 0);
   a.stages = g.stages;
   p->launch_smem = g.smem_bytes;
   p->geo = g;
@@ -806,7 +865,8 @@ extern "C" int b2d_conv_dgrad_class_plan_create(const b2d_conv_desc* dp, int a, 
   ar.ldd = d.Ci, ar.ldmask = d.Ci, ar.ldws = 0;
   ar.M = d.N * d.H * d.W, ar.N = gd.N, ar.K = gd.K;
   ar.kb_total = g.k_blocks, ar.kb_per_split = g.k_blocks, ar.splits = 1;
-  ar.flags = (d.out_dtype == B2D_BF16 ? kFlagOutBf16 : 0);
+  ar.flags = (d.out_dtype == B2D_BF16 ? kFlagOutBf16 : 0) |
+            (d.mask != nullptr && d.mask_dtype == B2D_BF16 ? kFlagMaskBf16 : 0);
   ar.stages = g.stages;
   p->launch_smem = g.smem_bytes;
   p->geo = g;
@@ -1181,7 +1241,8 @@ extern "C" int b2d_gemm_noalloc(const b2d_gemm_desc* desc, void* stream) {
   a.M = d.M, a.N = d.N, a.K = d.K;
   a.kb_total = g.k_blocks, a.kb_per_split = ceil_div(g.k_blocks, g.splits), a.splits = g.splits;
   a.flags = (d.relu ? kFlagRelu : 0) | (d.accumulate ? kFlagAccumulate : 0) |
-            (finalize ? kFlagFinalize : 0) | (d.out_dtype == B2D_BF16 ? kFlagOutBf16 : 0);
+            (finalize ? kFlagFinalize : 0) | (d.out_dtype == B2D_BF16 ? kFlagOutBf16 : 0) |
+            (d.mask != nullptr && d.mask_dtype == B2D_BF16 ? kFlagMaskBf16 : 0);
   a.stages = g.stages;
   if (d.dtype == B2D_F32)
     select_major<MmaKind::TF32>(d.a_mn_major, d.b_mn_major, g.block_n, &plan.kernel, &plan.smem_bytes);

@@ -859,387 +859,3 @@ extern "C" int b2d_cast_f32_bf16(const float* src, void* dst, size_t n, void* st
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;
 }
-
-// =======================================================================================
-// ResNet-family extras (BASELINE.json config 4; none of these appear in the reference README):
-// BatchNormalization (training statistics) fused with ReLU, residual add + ReLU, general max
-// pooling with overlapping windows, global average pooling.  All NHWC fp32; activations are
-// viewed as [M = N*H*W rows][C channels].
-// =======================================================================================
-namespace b2d {
-
-// Per-channel sum and sum of squares over M rows (C % 4 == 0): stats[0:C] += sum, stats[C:2C] += sumsq.
-__global__ void __launch_bounds__(256) bn_stats_kernel(const float* __restrict__ x, float* __restrict__ stats,
-                                                        int M, int C, int rows_per_cta) {
-  pdl_wait();
-  pdl_trigger();
-  __shared__ float4 ps[8][32], pq[8][32];
-  const int lane = threadIdx.x & 31, wy = threadIdx.x >> 5;
-  const int col = blockIdx.x * 128 + lane * 4;
-  const int r0 = blockIdx.y * rows_per_cta, r1 = min(M, r0 + rows_per_cta);
-  float4 s = make_float4(0.f, 0.f, 0.f, 0.f), q = s;
-  if (col < C)
-    for (int r = r0 + wy; r < r1; r += 8) {
-      const float4 v = *reinterpret_cast<const float4*>(x + (size_t)r * C + col);
-      s.x += v.x, s.y += v.y, s.z += v.z, s.w += v.w;
-      q.x += v.x * v.x, q.y += v.y * v.y, q.z += v.z * v.z, q.w += v.w * v.w;
-    }
-  ps[wy][lane] = s, pq[wy][lane] = q;
-  __syncthreads();
-  if (wy == 0 && col < C) {
-    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      a.x += ps[k][lane].x, a.y += ps[k][lane].y, a.z += ps[k][lane].z, a.w += ps[k][lane].w;
-      b.x += pq[k][lane].x, b.y += pq[k][lane].y, b.z += pq[k][lane].z, b.w += pq[k][lane].w;
-    }
-    atomicAdd(&stats[col], a.x), atomicAdd(&stats[col + 1], a.y), atomicAdd(&stats[col + 2], a.z), atomicAdd(&stats[col + 3], a.w);
-    atomicAdd(&stats[C + col], b.x), atomicAdd(&stats[C + col + 1], b.y), atomicAdd(&stats[C + col + 2], b.z), atomicAdd(&stats[C + col + 3], b.w);
-  }
-}
-
-// y = act(gamma * (x - mean) * rstd + beta); also writes mean/rstd (saved for backward), updates
-// the moving statistics, and clears `stats` for the next step.
-__global__ void bn_apply_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
-                                const float* __restrict__ beta, float* __restrict__ stats,
-                                float* __restrict__ saved, float* __restrict__ moving, float* __restrict__ y,
-                                int M, int C, float eps, float momentum, int relu) {
-  pdl_wait();
-  pdl_trigger();
-  const size_t total4 = (size_t)M * C / 4;
-  const float inv_m = 1.f / (float)M;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total4; i += (size_t)gridDim.x * blockDim.x) {
-    const int c = (int)((i * 4) % C);
-    const float4 v = reinterpret_cast<const float4*>(x)[i];
-    float o[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const float mean = stats[c + k] * inv_m;
-      const float var = fmaxf(stats[C + c + k] * inv_m - mean * mean, 0.f);
-      const float rstd = rsqrtf(var + eps);
-      o[k] = gamma[c + k] * (o[k] - mean) * rstd + beta[c + k];
-      if (relu) o[k] = fmaxf(o[k], 0.f);
-    }
-    reinterpret_cast<float4*>(y)[i] = make_float4(o[0], o[1], o[2], o[3]);
-  }
-}
-
-// One thread per channel: mean / rstd for backward, moving statistics; must run after bn_apply
-// consumers are done with `stats` — it zeroes them.
-__global__ void bn_finalize_kernel(float* __restrict__ stats, float* __restrict__ saved,
-                                   float* __restrict__ moving, int M, int C, float eps, float momentum) {
-  pdl_wait();
-  pdl_trigger();
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  const float inv_m = 1.f / (float)M;
-  const float mean = stats[c] * inv_m;
-  const float var = fmaxf(stats[C + c] * inv_m - mean * mean, 0.f);
-  saved[c] = mean, saved[C + c] = rsqrtf(var + eps);
-  if (moving != nullptr) {
-    const float unbiased = M > 1 ? var * (float)M / (float)(M - 1) : var;
-    moving[c] = momentum * moving[c] + (1.f - momentum) * mean;
-    moving[C + c] = momentum * moving[C + c] + (1.f - momentum) * unbiased;
-  }
-  stats[c] = 0.f, stats[C + c] = 0.f;
-}
-
-// Backward pass 1: dbeta[c] += sum g, dgamma[c] += sum g * xhat, with g = dy * (y > 0 if relu);
-// red[0:C] / red[C:2C] receive the same sums for pass 2.
-__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const float* __restrict__ x, const float* __restrict__ y,
-                                                             const float* __restrict__ dy, const float* __restrict__ saved,
-                                                             float* __restrict__ red, int M, int C, int rows_per_cta,
-                                                             int relu) {
-  pdl_wait();
-  pdl_trigger();
-  __shared__ float4 ps[8][32], pq[8][32];
-  const int lane = threadIdx.x & 31, wy = threadIdx.x >> 5;
-  const int col = blockIdx.x * 128 + lane * 4;
-  const int r0 = blockIdx.y * rows_per_cta, r1 = min(M, r0 + rows_per_cta);
-  float4 s = make_float4(0.f, 0.f, 0.f, 0.f), q = s;
-  if (col < C) {
-    const float4 mean = *reinterpret_cast<const float4*>(saved + col);
-    const float4 rstd = *reinterpret_cast<const float4*>(saved + C + col);
-    for (int r = r0 + wy; r < r1; r += 8) {
-      const size_t o = (size_t)r * C + col;
-      float4 g = *reinterpret_cast<const float4*>(dy + o);
-      const float4 xv = *reinterpret_cast<const float4*>(x + o);
-      if (relu) {
-        const float4 yv = *reinterpret_cast<const float4*>(y + o);
-        g.x = yv.x > 0.f ? g.x : 0.f, g.y = yv.y > 0.f ? g.y : 0.f, g.z = yv.z > 0.f ? g.z : 0.f, g.w = yv.w > 0.f ? g.w : 0.f;
-      }
-      s.x += g.x, s.y += g.y, s.z += g.z, s.w += g.w;
-      q.x += g.x * (xv.x - mean.x) * rstd.x, q.y += g.y * (xv.y - mean.y) * rstd.y;
-      q.z += g.z * (xv.z - mean.z) * rstd.z, q.w += g.w * (xv.w - mean.w) * rstd.w;
-    }
-  }
-  ps[wy][lane] = s, pq[wy][lane] = q;
-  __syncthreads();
-  if (wy == 0 && col < C) {
-    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      a.x += ps[k][lane].x, a.y += ps[k][lane].y, a.z += ps[k][lane].z, a.w += ps[k][lane].w;
-      b.x += pq[k][lane].x, b.y += pq[k][lane].y, b.z += pq[k][lane].z, b.w += pq[k][lane].w;
-    }
-    atomicAdd(&red[col], a.x), atomicAdd(&red[col + 1], a.y), atomicAdd(&red[col + 2], a.z), atomicAdd(&red[col + 3], a.w);
-    atomicAdd(&red[C + col], b.x), atomicAdd(&red[C + col + 1], b.y), atomicAdd(&red[C + col + 2], b.z), atomicAdd(&red[C + col + 3], b.w);
-  }
-}
-
-// Backward pass 2: dx = gamma * rstd * (g - sum_g/M - xhat * sum_gxhat/M).
-__global__ void bn_bwd_apply_kernel(const float* __restrict__ x, const float* __restrict__ y,
-                                    const float* __restrict__ dy, const float* __restrict__ gamma,
-                                    const float* __restrict__ saved, const float* __restrict__ red,
-                                    float* __restrict__ dx, int M, int C, int relu) {
-  pdl_wait();
-  pdl_trigger();
-  const size_t total4 = (size_t)M * C / 4;
-  const float inv_m = 1.f / (float)M;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total4; i += (size_t)gridDim.x * blockDim.x) {
-    const int c = (int)((i * 4) % C);
-    const float4 xv = reinterpret_cast<const float4*>(x)[i];
-    float4 g = reinterpret_cast<const float4*>(dy)[i];
-    if (relu) {
-      const float4 yv = reinterpret_cast<const float4*>(y)[i];
-      g.x = yv.x > 0.f ? g.x : 0.f, g.y = yv.y > 0.f ? g.y : 0.f, g.z = yv.z > 0.f ? g.z : 0.f, g.w = yv.w > 0.f ? g.w : 0.f;
-    }
-    const float xs[4] = {xv.x, xv.y, xv.z, xv.w}, gs[4] = {g.x, g.y, g.z, g.w};
-    float o[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const float mean = saved[c + k], rstd = saved[C + c + k];
-      const float xhat = (xs[k] - mean) * rstd;
-      o[k] = gamma[c + k] * rstd * (gs[k] - red[c + k] * inv_m - xhat * red[C + c + k] * inv_m);
-    }
-    reinterpret_cast<float4*>(dx)[i] = make_float4(o[0], o[1], o[2], o[3]);
-  }
-}
-
-// dgamma += red[C:2C], dbeta += red[0:C]; red is cleared for the next step.
-__global__ void bn_bwd_finalize_kernel(float* __restrict__ red, float* __restrict__ dgamma,
-                                       float* __restrict__ dbeta, int C) {
-  pdl_wait();
-  pdl_trigger();
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  dbeta[c] += red[c], dgamma[c] += red[C + c];
-  red[c] = 0.f, red[C + c] = 0.f;
-}
-
-// out = relu?(a + b)    /    dz = dy * (out > 0)    /    c = a + b
-__global__ void add_act_kernel(const float4* __restrict__ a, const float4* __restrict__ b, float4* __restrict__ out,
-                               size_t n4, int relu) {
-  pdl_wait();
-  pdl_trigger();
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
-    const float4 x = a[i], y = b[i];
-    float4 o = make_float4(x.x + y.x, x.y + y.y, x.z + y.z, x.w + y.w);
-    if (relu) o.x = fmaxf(o.x, 0.f), o.y = fmaxf(o.y, 0.f), o.z = fmaxf(o.z, 0.f), o.w = fmaxf(o.w, 0.f);
-    out[i] = o;
-  }
-}
-
-// General max pooling (window k, stride s, symmetric zero... -inf padding p), NHWC.  code = index of
-// the winning tap inside the window (kh * k + kw).
-__global__ void maxpool_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, uint8_t* __restrict__ code,
-                                   int N, int H, int W, int C, int OH, int OW, int k, int s, int p) {
-  pdl_wait();
-  pdl_trigger();
-  const size_t total = (size_t)N * OH * OW * C;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const int c = i % C;
-    size_t t = i / C;
-    const int ow = t % OW;
-    t /= OW;
-    const int oh = t % OH;
-    const int n = t / OH;
-    float best = -INFINITY;
-    int arg = 0;
-    for (int kh = 0; kh < k; ++kh) {
-      const int ih = oh * s - p + kh;
-      if (ih < 0 || ih >= H) continue;
-      for (int kw = 0; kw < k; ++kw) {
-        const int iw = ow * s - p + kw;
-        if (iw < 0 || iw >= W) continue;
-        const float v = x[(((size_t)n * H + ih) * W + iw) * C + c];
-        if (v > best) best = v, arg = kh * k + kw;
-      }
-    }
-    y[i] = best;
-    code[i] = (uint8_t)arg;
-  }
-}
-
-// Gather form of the backward pass (windows may overlap): dx[pixel] = sum of dy over the windows
-// whose arg-max is this pixel.
-__global__ void maxpool_bwd_kernel(const float* __restrict__ dy, const uint8_t* __restrict__ code,
-                                   float* __restrict__ dx, int N, int H, int W, int C, int OH, int OW, int k,
-                                   int s, int p) {
-  pdl_wait();
-  pdl_trigger();
-  const size_t total = (size_t)N * H * W * C;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const int c = i % C;
-    size_t t = i / C;
-    const int iw = t % W;
-    t /= W;
-    const int ih = t % H;
-    const int n = t / H;
-    float g = 0.f;
-    for (int kh = 0; kh < k; ++kh) {
-      const int th = ih + p - kh;
-      if (th < 0 || th % s) continue;
-      const int oh = th / s;
-      if (oh >= OH) continue;
-      for (int kw = 0; kw < k; ++kw) {
-        const int tw = iw + p - kw;
-        if (tw < 0 || tw % s) continue;
-        const int ow = tw / s;
-        if (ow >= OW) continue;
-        const size_t o = (((size_t)n * OH + oh) * OW + ow) * C + c;
-        if (code[o] == kh * k + kw) g += dy[o];
-      }
-    }
-    dx[i] = g;
-  }
-}
-
-// Global average pooling: y[n,c] = mean over H*W; backward: dx[n,h,w,c] = dy[n,c] / (H*W).
-__global__ void gap_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int N, int HW, int C) {
-  pdl_wait();
-  pdl_trigger();
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= N * C) return;
-  const int n = i / C, c = i % C;
-  float s = 0.f;
-  for (int p = 0; p < HW; ++p) s += x[((size_t)n * HW + p) * C + c];
-  y[i] = s / (float)HW;
-}
-__global__ void gap_bwd_kernel(const float* __restrict__ dy, float* __restrict__ dx, int N, int HW, int C) {
-  pdl_wait();
-  pdl_trigger();
-  const size_t total = (size_t)N * HW * C;
-  const float inv = 1.f / (float)HW;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const int c = i % C;
-    const int n = i / ((size_t)HW * C);
-    dx[i] = dy[(size_t)n * C + c] * inv;
-  }
-}
-
-}  // namespace b2d
-
-extern "C" int b2d_bn_fwd(const float* x, const float* gamma, const float* beta, float* stats, float* saved,
-                          float* moving, float* y, int M, int C, float eps, float momentum, int relu,
-                          void* stream) {
-  B2D_REQUIRE(C % 4 == 0, "bn_fwd: C must be a multiple of 4");
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int rows = max(64, ceil_div(M, 512));
-  B2D_CUDA_CHECK(launch_pdl(bn_stats_kernel, dim3(ceil_div(C, 128), ceil_div(M, rows)), dim3(256), 0, st, x, stats, M, C, rows));
-  B2D_CUDA_CHECK(launch_pdl(bn_apply_kernel, dim3(grid_for((size_t)M * C / 4, 256, 148 * 16)), dim3(256), 0, st, x, gamma,
-                            beta, stats, saved, moving, y, M, C, eps, momentum, relu));
-  B2D_CUDA_CHECK(launch_pdl(bn_finalize_kernel, dim3(ceil_div(C, 256)), dim3(256), 0, st, stats, saved, moving, M, C, eps,
-                            momentum));
-  return B2D_OK;
-}
-
-extern "C" int b2d_bn_bwd(const float* x, const float* y, const float* dy, const float* gamma, const float* saved,
-                          float* red, float* dx, float* dgamma, float* dbeta, int M, int C, int relu, void* stream) {
-  B2D_REQUIRE(C % 4 == 0, "bn_bwd: C must be a multiple of 4");
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int rows = max(64, ceil_div(M, 512));
-  B2D_CUDA_CHECK(launch_pdl(bn_bwd_reduce_kernel, dim3(ceil_div(C, 128), ceil_div(M, rows)), dim3(256), 0, st, x, y, dy,
-                            saved, red, M, C, rows, relu));
-  if (dx != nullptr)
-    B2D_CUDA_CHECK(launch_pdl(bn_bwd_apply_kernel, dim3(grid_for((size_t)M * C / 4, 256, 148 * 16)), dim3(256), 0, st, x, y,
-                              dy, gamma, saved, red, dx, M, C, relu));
-  B2D_CUDA_CHECK(launch_pdl(bn_bwd_finalize_kernel, dim3(ceil_div(C, 256)), dim3(256), 0, st, red, dgamma, dbeta, C));
-  return B2D_OK;
-}
-
-extern "C" int b2d_add_act(const float* a, const float* b, float* out, size_t n, int relu, void* stream) {
-  B2D_REQUIRE(n % 4 == 0, "add_act: element count must be a multiple of 4");
-  B2D_CUDA_CHECK(launch_pdl(add_act_kernel, dim3(grid_for(n / 4, 256, 148 * 16)), dim3(256), 0,
-                            static_cast<cudaStream_t>(stream), reinterpret_cast<const float4*>(a),
-                            reinterpret_cast<const float4*>(b), reinterpret_cast<float4*>(out), n / 4, relu));
-  return B2D_OK;
-}
-
-// p = padding at the top / left; OH, OW = output size (<= 0: derive from symmetric padding).
-extern "C" int b2d_maxpool_fwd(const float* x, float* y, uint8_t* code, int N, int H, int W, int C, int k, int s,
-                               int p, int OH, int OW, void* stream) {
-  if (OH <= 0) OH = (H + 2 * p - k) / s + 1;
-  if (OW <= 0) OW = (W + 2 * p - k) / s + 1;
-  B2D_CUDA_CHECK(launch_pdl(maxpool_fwd_kernel, dim3(grid_for((size_t)N * OH * OW * C, 256, 148 * 16)), dim3(256), 0,
-                            static_cast<cudaStream_t>(stream), x, y, code, N, H, W, C, OH, OW, k, s, p));
-  return B2D_OK;
-}
-
-extern "C" int b2d_maxpool_bwd(const float* dy, const uint8_t* code, float* dx, int N, int H, int W, int C, int k,
-                               int s, int p, int OH, int OW, void* stream) {
-  if (OH <= 0) OH = (H + 2 * p - k) / s + 1;
-  if (OW <= 0) OW = (W + 2 * p - k) / s + 1;
-  B2D_CUDA_CHECK(launch_pdl(maxpool_bwd_kernel, dim3(grid_for((size_t)N * H * W * C, 256, 148 * 16)), dim3(256), 0,
-                            static_cast<cudaStream_t>(stream), dy, code, dx, N, H, W, C, OH, OW, k, s, p));
-  return B2D_OK;
-}
-
-extern "C" int b2d_gap_fwd(const float* x, float* y, int N, int HW, int C, void* stream) {
-  B2D_CUDA_CHECK(launch_pdl(gap_fwd_kernel, dim3(ceil_div(N * C, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), x,
-                            y, N, HW, C));
-  return B2D_OK;
-}
-
-extern "C" int b2d_gap_bwd(const float* dy, float* dx, int N, int HW, int C, void* stream) {
-  B2D_CUDA_CHECK(launch_pdl(gap_bwd_kernel, dim3(grid_for((size_t)N * HW * C, 256, 148 * 16)), dim3(256), 0,
-                            static_cast<cudaStream_t>(stream), dy, dx, N, HW, C));
-  return B2D_OK;
-}
-
-// =======================================================================================
-// im2col for convolutions whose channel count is too small for the implicit-GEMM tensor-core
-// path (a pixel is less than one 128-byte TMA row, e.g. the 3-channel stem of ResNet): the
-// patch matrix col[pixel][tap*Ci + ci] (row pitch padded to a multiple of 4 floats, padding
-// columns zero) is materialised once per step and feeds the tcgen05 GEMM core for both the
-// forward product (col . W) and the filter gradient (col^T . dy).
-// =======================================================================================
-namespace b2d {
-__global__ void __launch_bounds__(256) im2col_kernel(const float* __restrict__ x, float* __restrict__ col,
-                                                      ConvShape s, int kpad) {
-  pdl_wait();
-  pdl_trigger();
-  const int K = s.KH * s.KW * s.Ci;
-  const size_t npix = (size_t)s.N * s.OH * s.OW;
-  const int lane = threadIdx.x & 31;
-  const size_t warp0 = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5;
-  const size_t nwarps = ((size_t)gridDim.x * blockDim.x) >> 5;
-  for (size_t p = warp0; p < npix; p += nwarps) {
-    const int ow = p % s.OW;
-    const int oh = (p / s.OW) % s.OH;
-    const int n = p / ((size_t)s.OW * s.OH);
-    float* row = col + p * kpad;
-    for (int k = lane; k < kpad; k += 32) {
-      float v = 0.f;
-      if (k < K) {
-        const int ci = k % s.Ci;
-        const int kw = (k / s.Ci) % s.KW;
-        const int kh = k / (s.Ci * s.KW);
-        const int ih = oh * s.sh - s.ph + kh, iw = ow * s.sw - s.pw + kw;
-        if (ih >= 0 && ih < s.H && iw >= 0 && iw < s.W) v = x[(((size_t)n * s.H + ih) * s.W + iw) * s.Ci + ci];
-      }
-      row[k] = v;
-    }
-  }
-}
-}  // namespace b2d
-
-extern "C" int b2d_im2col(const float* x, float* col, int N, int H, int W, int Ci, int KH, int KW, int sh, int sw,
-                          int ph, int pw, int OH, int OW, int kpad, void* stream) {
-  const ConvShape s = make_shape(N, H, W, Ci, /*Co=*/0, KH, KW, sh, sw, ph, pw, OH, OW);
-  B2D_REQUIRE(kpad >= KH * KW * Ci && kpad % 4 == 0, "im2col: kpad must be >= KH*KW*Ci and a multiple of 4");
-  const size_t npix = (size_t)N * s.OH * s.OW;
-  B2D_CUDA_CHECK(launch_pdl(im2col_kernel, dim3(grid_for(npix * 32, 256, 148 * 16)), dim3(256), 0,
-                            static_cast<cudaStream_t>(stream), x, col, s, kpad));
-  return B2D_OK;
-}

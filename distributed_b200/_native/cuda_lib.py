@@ -27,6 +27,7 @@ class GemmDesc(C.Structure):
         ("bias", C.c_void_p), ("mask", C.c_void_p), ("ldmask", C.c_int64),
         ("relu", C.c_int), ("accumulate", C.c_int), ("splits", C.c_int),
         ("workspace", C.c_void_p), ("counters", C.c_void_p),
+        ("mask_dtype", C.c_int),
     ]
 
 

@@ -10,9 +10,10 @@ class CpuBackend:
     name = "cpu"
     device = torch.device("cpu")
     supports_conv_c1_pool = False
+    act_dtype = torch.float32
 
     def alloc(self, shape, dtype=torch.float32):
-        return torch.zeros(shape, dtype=dtype)
+        return torch.zeros(shape, dtype=dtype or torch.float32)
 
     def supports_fused_head(self, k_in, units):
         return False
@@ -66,11 +67,34 @@ class CpuBackend:
     def relu_bwd(self, dy, y, dx):
         return lambda: cpu.relu_bwd(dy, y, dx)
 
-    def __getattr__(self, name):
-        if name in ("bn_fwd", "bn_bwd", "add_act", "copy", "maxpool_fwd", "maxpool_bwd", "gap_fwd", "gap_bwd"):
-            raise NotImplementedError(f"{name}: BatchNormalization / Residual / general pooling layers run on the "
-                                      "CUDA backend only (the CPU backend covers the reference's layer set)")
-        raise AttributeError(name)
+    # ---- ResNet-family layers (fp32; the dtype policy only affects the CUDA backend) --------------
+    def batchnorm(self, x2d, y2d, gamma, beta, *, eps, momentum, relu, stats=None, saved=None, red=None,
+                  moving=None, moving_grads=None, inv_lr=0.0, inference=False, dy2d=None, dx2d=None,
+                  dgamma=None, dbeta=None):
+        def fwd():
+            cpu.bn_fwd(x2d, gamma, beta, y2d, saved, moving, moving_grads, eps, momentum, inv_lr, relu, inference)
+
+        def bwd():
+            cpu.bn_bwd(x2d, y2d, dy2d, gamma, saved, dx2d, dgamma, dbeta, relu)
+        return fwd, bwd
+
+    def add_act(self, a, b, out, mode, mask=None):
+        return lambda: cpu.add_act(a, b, out, mode, mask)
+
+    def cast(self, src, dst):
+        return lambda: dst.copy_(src)
+
+    def maxpool_fwd(self, x, y, code, k, s, p):
+        return lambda: cpu.maxpool_fwd(x, y, code, k, s, p)
+
+    def maxpool_bwd(self, dy, code, dx, k, s, p):
+        return lambda: cpu.maxpool_bwd(dy, code, dx, k, s, p)
+
+    def gap_fwd(self, x, y):
+        return lambda: cpu.gap_fwd(x, y)
+
+    def gap_bwd(self, dy, dx, mask=None):
+        return lambda: cpu.gap_bwd(dy, dx, mask)
 
     def sgd_apply(self, params, grads, n_params, lr):
         return lambda: cpu.sgd_apply(params, grads, n_params, lr)

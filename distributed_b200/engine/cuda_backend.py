@@ -3,6 +3,10 @@
 Dense layers go to the tcgen05 GEMM core whenever their shapes meet TMA's 16-byte row
 alignment; the tiny/unaligned remainder (e.g. an unfused Dense(10)) uses the CUDA-core GEMM.
 Every callable launches on the *current* torch stream, so the executor can capture them.
+
+``act_dtype`` selects the storage type of the convolutional part of the network: fp32 (tf32
+tensor-core math) or bf16 (the ``mixed_bfloat16`` policy: bf16 activations, activation gradients
+and a bf16 shadow of the weights, fp32 master weights / weight gradients / statistics).
 """
 from __future__ import annotations
 
@@ -21,12 +25,38 @@ class CudaBackend:
     name = "cuda"
     supports_conv_c1_pool = True
 
-    def __init__(self, device):
+    def __init__(self, device, act_dtype=torch.float32):
         self.device = torch.device(device)
-        self.plans = []     # keep GemmPlans (TMA descriptors) alive
+        self.act_dtype = act_dtype      # storage type of 4-D activations (fp32, or bf16 = mixed precision)
+        self.plans = []                 # keep GemmPlans (TMA descriptors) alive
+        self._params = self._shadow = None
+        self._cols, self._casts = {}, {}
 
     def alloc(self, shape, dtype=torch.float32):
-        return torch.zeros(shape, dtype=dtype, device=self.device)
+        return torch.zeros(shape, dtype=dtype or torch.float32, device=self.device)
+
+    # ---- mixed precision: bf16 shadow of the fp32 master weights ---------------------------
+    def begin_step(self, params):
+        """First launch of a step under the bf16 policy: refresh the bf16 copy of the whole weight
+        arena (one streaming kernel; the fp32 masters are what the optimizer updates)."""
+        if self.act_dtype != torch.bfloat16:
+            return None
+        if self._params is None or self._params.data_ptr() != params.data_ptr():
+            self._params = params
+            self._shadow = torch.zeros(params.numel(), dtype=torch.bfloat16, device=self.device)
+        shadow = self._shadow
+        return lambda: nn.cast(params, shadow)
+
+    def _w_for(self, w, dtype):
+        """The weight tensor in the operand type of a `dtype` convolution."""
+        if w.dtype == dtype:
+            return w
+        if self._params is None:
+            raise RuntimeError("bf16 convolution requested before begin_step() bound the weight arena")
+        off = (w.data_ptr() - self._params.data_ptr()) // 4
+        if not 0 <= off <= self._params.numel() - w.numel():
+            raise RuntimeError("bf16 convolution weight does not live in the bound weight arena")
+        return self._shadow[off:off + w.numel()].view(w.shape)
 
     def supports_fused_head(self, k_in, units):
         smem = (2 * k_in * units + 17 * k_in + 8 * _HEAD_MAX_C + 16) * 4
@@ -40,16 +70,19 @@ class CudaBackend:
         return all(d % 4 == 0 for d in dims)
 
     def describe_conv(self, layer):
-        from ..ops import conv as tc
         ci = layer.input_shape[2]
         x_shape = (1, *layer.input_shape)
         w_shape = (*layer.kernel_size, ci, layer.filters)
-        if self._conv_tc_ok(x_shape, w_shape, layer.strides, layer.pad_amounts(), out_hw=layer.output_shape[:2]):
-            return "tcgen05 tf32 implicit GEMM (4-D TMA taps)"
+        kind = "bf16" if self.act_dtype == torch.bfloat16 else "tf32"
+        if self._conv_tc_ok(x_shape, w_shape, layer.strides, layer.pad_amounts(), out_hw=layer.output_shape[:2],
+                            dtype=self.act_dtype):
+            return f"tcgen05 {kind} implicit GEMM (4-D TMA taps)"
+        if self.act_dtype == torch.bfloat16 or (ci * 4) % 128 != 0:
+            return f"im2col + tcgen05 {kind} GEMM"
         return "direct conv (CUDA cores)"
 
     @staticmethod
-    def _conv_tc_ok(x_shape, w_shape, strides, pad, dgrad=False, out_hw=None):
+    def _conv_tc_ok(x_shape, w_shape, strides, pad, dgrad=False, out_hw=None, dtype=torch.float32):
         from ..ops import conv as tc
         if os.environ.get("B200DIST_CONV", "") == "direct":
             return False
@@ -57,7 +90,7 @@ class CudaBackend:
             # the unit-stride data gradient assumes symmetric padding
             if (x_shape[1] + 2 * pad[0] - w_shape[0] + 1, x_shape[2] + 2 * pad[1] - w_shape[1] + 1) != tuple(out_hw):
                 return False
-        return tc.tc_supported(tuple(x_shape), tuple(w_shape), pad, torch.float32, dgrad=dgrad, strides=strides,
+        return tc.tc_supported(tuple(x_shape), tuple(w_shape), pad, dtype, dgrad=dgrad, strides=strides,
                                out_hw=out_hw)
 
     def describe_dense(self, b, k, n):
@@ -75,18 +108,27 @@ class CudaBackend:
     def conv_c1_pool_bwd(self, x, dy, code, dw, db):
         return lambda: nn.conv_c1_pool_bwd(x, dy, code, dw, db)
 
-    # ---- general conv (direct fallback; implicit-GEMM path plugs in here) --------------
+    # ---- general conv: implicit GEMM on tcgen05, im2col + GEMM for small C_in, direct fallback ----
+    @staticmethod
+    def _unsupported_bf16(what, x, w):
+        raise NotImplementedError(
+            f"mixed_bfloat16: {what} of a convolution with input {tuple(x.shape)} and kernel {tuple(w.shape)} has no "
+            "bf16 kernel — interior Conv2D layers need C_in % 64 == 0 and C_out % 8 == 0 (the first layer may have "
+            "any C_in); use the float32 policy for this model")
+
     def conv2d_fwd(self, x, w, b, y, strides, pad, relu):
         from ..ops import conv as tc
-        if self._conv_tc_ok(x.shape, w.shape, strides, pad, out_hw=y.shape[1:3]):
-            plan = tc.ConvFwdPlan(x, w, y, pad, bias=b, relu=relu, stride=strides[0])
+        dt = y.dtype
+        wk = self._w_for(w, dt)
+        if x.dtype == dt and self._conv_tc_ok(x.shape, w.shape, strides, pad, out_hw=y.shape[1:3], dtype=dt):
+            plan = tc.ConvFwdPlan(x, wk, y, pad, bias=b, relu=relu, stride=strides[0])
             self.plans.append(plan)
             return plan.run
         if self._im2col_ok(x, w, y):
             # small C_in (e.g. the 3-channel ResNet stem): patch matrix once, then tensor-core GEMMs
             col = self._col_for(x, w, y, strides, pad)
             k = w.shape[0] * w.shape[1] * w.shape[2]
-            gemm = self._plan(col[:, :k], w.view(k, w.shape[3]), y.view(-1, y.shape[3]), b_mn_major=True, bias=b,
+            gemm = self._plan(col[:, :k], wk.view(k, w.shape[3]), y.view(-1, y.shape[3]), b_mn_major=True, bias=b,
                               relu=relu)
             kh_kw, st, pd, ohw = (w.shape[0], w.shape[1]), tuple(strides), tuple(pad), (y.shape[1], y.shape[2])
 
@@ -94,27 +136,34 @@ class CudaBackend:
                 nn.im2col(x, col, kh_kw, st, pd, ohw)
                 gemm()
             return run
+        if dt != torch.float32:
+            self._unsupported_bf16("the forward pass", x, w)
         return lambda: nn.conv2d_fwd_direct(x, w, b, y, strides, pad, relu)
 
     def _im2col_ok(self, x, w, y):
         k = w.shape[0] * w.shape[1] * w.shape[2]
-        return (os.environ.get("B200DIST_CONV", "") != "direct" and (x.shape[3] * 4) % 128 != 0 and k >= 32
-                and w.shape[3] % 4 == 0 and y.numel() // y.shape[3] >= 1024)
+        if os.environ.get("B200DIST_CONV", "") == "direct" or k < 32 or y.numel() // y.shape[3] < 1024:
+            return False
+        if y.dtype == torch.bfloat16:       # every convolution the implicit-GEMM path does not take
+            return w.shape[3] % 8 == 0
+        return (x.shape[3] * 4) % 128 != 0 and w.shape[3] % 4 == 0
 
     def _col_for(self, x, w, y, strides, pad):
         """One patch matrix per (input tensor, geometry): written by the forward, reused by wgrad."""
         k = w.shape[0] * w.shape[1] * w.shape[2]
-        key = (x.data_ptr(), tuple(w.shape[:3]), tuple(strides), tuple(pad), y.shape[1], y.shape[2])
-        cache = self.__dict__.setdefault("_cols", {})
-        if key not in cache:
-            cache[key] = self.alloc((y.numel() // y.shape[3], (k + 3) // 4 * 4))
-        return cache[key]
+        key = (x.data_ptr(), tuple(w.shape[:3]), tuple(strides), tuple(pad), y.shape[1], y.shape[2], y.dtype)
+        if key not in self._cols:
+            vec = 4 if y.dtype == torch.float32 else 8
+            self._cols[key] = self.alloc((y.numel() // y.shape[3], (k + vec - 1) // vec * vec), y.dtype)
+        return self._cols[key]
 
     def conv2d_wgrad(self, x, dy, dw, db, strides, pad):
         from ..ops import conv as tc
+        dt = dy.dtype
+        vec = 4 if dt == torch.float32 else 8
         dy2 = dy.view(-1, dy.shape[-1])
-        if (self._conv_tc_ok(x.shape, dw.shape, strides, pad, out_hw=dy.shape[1:3]) and x.shape[3] % 4 == 0
-                and dw.shape[3] % 4 == 0):
+        if (x.dtype == dt and self._conv_tc_ok(x.shape, dw.shape, strides, pad, out_hw=dy.shape[1:3], dtype=dt)
+                and x.shape[3] % vec == 0 and dw.shape[3] % vec == 0):
             plan = tc.ConvWgradPlan(x, dy, dw, pad, stride=strides[0])
             self.plans.append(plan)
             wgrad = plan.run
@@ -124,6 +173,8 @@ class CudaBackend:
             # the padding columns of col are excluded by the view; its row pitch stays 16-byte aligned
             wgrad = self._plan(col[:, :k], dy2, dw.view(k, dw.shape[3]), a_mn_major=True, b_mn_major=True,
                                accumulate=True)
+        elif dt != torch.float32:
+            self._unsupported_bf16("the filter gradient", x, dw)
         else:
             def wgrad():
                 nn.conv2d_wgrad_direct(x, dy, dw, strides, pad)
@@ -131,20 +182,27 @@ class CudaBackend:
         def run():
             wgrad()
             if db is not None:
-                nn.colsum(dy2, db)
+                if dt == torch.float32:
+                    nn.colsum(dy2, db)
+                else:
+                    nn.colsum_t(dy2, db)
         return run
 
     def conv2d_dgrad(self, dy, w, dx, strides, pad, mask=None):
         from ..ops import conv as tc
+        dt = dx.dtype
+        wk = self._w_for(w, dt)
         if (strides[0] == strides[1] and strides[0] > 1 and os.environ.get("B200DIST_CONV", "") != "direct"
-                and tc.dgrad_strided_supported(dx.shape, w.shape, strides[0], torch.float32)):
-            plan = tc.ConvDgradStridedPlan(dy, w, dx, pad, strides[0], mask=mask)
+                and tc.dgrad_strided_supported(dx.shape, w.shape, strides[0], dt)):
+            plan = tc.ConvDgradStridedPlan(dy, wk, dx, pad, strides[0], mask=mask)
             self.plans.append(plan)
             return plan.run
-        if self._conv_tc_ok(dx.shape, w.shape, strides, pad, dgrad=True, out_hw=dy.shape[1:3]):
-            plan = tc.ConvDgradPlan(dy, w, dx, pad, mask=mask)     # ReLU mask fused in the epilogue
+        if self._conv_tc_ok(dx.shape, w.shape, strides, pad, dgrad=True, out_hw=dy.shape[1:3], dtype=dt):
+            plan = tc.ConvDgradPlan(dy, wk, dx, pad, mask=mask)     # ReLU mask fused in the epilogue
             self.plans.append(plan)
             return plan.run
+        if dt != torch.float32:
+            self._unsupported_bf16("the data gradient", dx, w)
 
         def run():
             nn.conv2d_dgrad_direct(dy, w, dx, strides, pad)
@@ -193,21 +251,22 @@ class CudaBackend:
         return lambda: nn.dense_xent_head(h, w, b, labels, dh, dw, db, metrics, scale, relu_mask, logits,
                                           dh_colsum)
 
-    # ---- ResNet-family ops --------------------------------------------------------------
-    def bn_fwd(self, x2d, gamma, beta, stats, saved, moving, y2d, eps, momentum, relu):
-        return lambda: nn.bn_fwd(x2d, gamma, beta, stats, saved, moving, y2d, eps, momentum, relu)
+    # ---- ResNet-family ops (fp32 or bf16 storage) -------------------------------------------
+    def batchnorm(self, x2d, y2d, gamma, beta, **kw):
+        bn = nn.BatchNorm(x2d, y2d, gamma, beta, **kw)
+        self.plans.append(bn)
+        return bn.forward, bn.backward
 
-    def bn_bwd(self, x2d, y2d, dy2d, gamma, saved, red, dx2d, dgamma, dbeta, relu):
-        return lambda: nn.bn_bwd(x2d, y2d, dy2d, gamma, saved, red, dx2d, dgamma, dbeta, relu)
-
-    def add_act(self, a, b, out, relu):
-        return lambda: nn.add_act(a, b, out, relu)
+    def add_act(self, a, b, out, mode, mask=None):
+        return lambda: nn.add_act(a, b, out, mode, mask)
 
     def relu_bwd(self, dy, y, dx):
-        return lambda: nn.relu_bwd(dy, y, dx)
+        if dy.dtype == torch.float32:
+            return lambda: nn.relu_bwd(dy, y, dx)
+        return lambda: nn.add_act(dy, None, dx, 2, y)
 
-    def copy(self, src, dst):
-        return lambda: dst.copy_(src)          # contiguous D2D: a memcpy node, not a kernel
+    def cast(self, src, dst):
+        return lambda: nn.cast(src, dst)
 
     def maxpool_fwd(self, x, y, code, k, s, p):
         return lambda: nn.maxpool_fwd(x, y, code, k, s, p)
@@ -218,8 +277,8 @@ class CudaBackend:
     def gap_fwd(self, x, y):
         return lambda: nn.gap_fwd(x, y)
 
-    def gap_bwd(self, dy, dx):
-        return lambda: nn.gap_bwd(dy, dx)
+    def gap_bwd(self, dy, dx, mask=None):
+        return lambda: nn.gap_bwd(dy, dx, mask)
 
     def softmax_xent(self, logits, labels, dlogits, metrics, scale):
         return lambda: nn.softmax_xent(logits, labels, dlogits, metrics, scale)

@@ -17,7 +17,15 @@ Conventions
   use atomics without a memset per step.
 * Fusions (CUDA backend): first-layer Conv2D(C_in=1)+bias+ReLU+MaxPool in one kernel each
   way [K1+K2, K8+K9]; final Dense(C<=32)+softmax-xent+all gradients in one kernel [K4+K5+K6];
-  BatchNorm+ReLU; residual add+ReLU.
+  BatchNorm+ReLU; residual add+ReLU, whose backward mask is applied by the kernel that writes the
+  block's output gradient (the next block's gradient sum, or the pooling backward).
+* Storage types: 4-D activations and their gradients use the backend's ``act_dtype`` (fp32, or
+  bf16 under the ``mixed_bfloat16`` policy); 2-D (Dense) activations, parameters, parameter
+  gradients and all per-channel statistics are fp32.  Flatten / GlobalAveragePooling2D are the
+  boundaries where the conversion happens.
+* BatchNormalization moving statistics are non-trainable arena slots; the forward kernel writes a
+  pseudo-gradient for them so that the (replica-averaging) optimizer update performs
+  ``m = momentum * m + (1 - momentum) * mean_over_replicas(batch statistic)``.
 """
 from __future__ import annotations
 
@@ -55,9 +63,11 @@ class _State:
 
 
 class _Lowerer:
-    def __init__(self, batch, be, layout, params, grads, labels, training):
+    def __init__(self, batch, be, layout, params, grads, labels, training, lr=0.0):
         self.batch, self.be, self.layout = batch, be, layout
         self.params, self.grads, self.labels, self.training = params, grads, labels, training
+        self.inv_lr = 1.0 / lr if lr else 0.0
+        self.act_dtype = getattr(be, "act_dtype", torch.float32)
         self.prog = StepProgram()
         self.metrics = grads[layout.n_params:layout.n_total]
         self.grad_scale = 1.0 / batch
@@ -84,24 +94,40 @@ class _Lowerer:
         elif prog.early_forward == 0:
             prog.early_forward = len(prog.forward)     # everything so far needs only the first layer's weights
 
-    def alloc_grad(self, shape):
-        return self.be.alloc(shape) if self.training else None
+    def alloc_grad(self, shape, dtype=torch.float32):
+        return self.be.alloc(shape, dtype) if self.training else None
+
+    def act(self, shape):
+        """A 4-D activation buffer in the backend's activation storage type."""
+        return self.be.alloc(shape, self.act_dtype)
+
+    def act_grad(self, shape, final_dy=None):
+        """Gradient buffer of a 4-D activation; ``final_dy`` (the enclosing residual block's output
+        gradient) is used instead when the layer is the last one of a branch."""
+        if not self.training:
+            return None
+        return final_dy if final_dy is not None else self.be.alloc(shape, self.act_dtype)
+
+    def relu_mask(self, d_buf, act):
+        """In-place d_buf *= (act > 0) for consumers that cannot fuse the mask."""
+        return self.be.relu_bwd(d_buf, act, d_buf)
 
     # -- a list of layers --------------------------------------------------------------
-    def sequence(self, layers, st: _State, top_level: bool) -> _State:
+    def sequence(self, layers, st: _State, top_level: bool, final_dy=None) -> _State:
+        """Lower ``layers`` starting from state ``st``.  ``final_dy``: gradient buffer the LAST layer
+        must use for its output (a residual branch reads the block's output gradient directly)."""
         be, batch, prog, training = self.be, self.batch, self.prog, self.training
         i, n = 0, len(layers)
         while i < n:
             layer = layers[i]
             nxt = layers[i + 1] if i + 1 < n else None
             is_last = top_level and i == n - 1
+            fdy = final_dy if i == n - 1 else None
             if isinstance(layer, L.InputLayer):
                 i += 1
                 continue
             if isinstance(layer, L.Flatten):
-                st = _State(st.cur.view(batch, -1), st.d_cur.view(batch, -1) if st.d_cur is not None else None,
-                            st.post_relu)
-                prog.description.append(f"flatten -> {tuple(st.cur.shape)} (view)")
+                st = self.flatten(st)
                 i += 1
                 continue
             if isinstance(layer, (L.Conv2D, L.Dense, L.BatchNormalization)):
@@ -112,9 +138,11 @@ class _Lowerer:
                 dw, db = self.kernel_bias(self.grads, layer)
                 ci = layer.input_shape[2]
                 fuse_pool = (be.supports_conv_c1_pool and st.d_cur is None and ci == 1 and b is not None
+                             and self.act_dtype == torch.float32
                              and layer.kernel_size in ((3, 3), (5, 5)) and layer.strides == (1, 1)
                              and layer.padding == "valid" and layer.activation == "relu"
-                             and isinstance(nxt, L.MaxPooling2D) and nxt.is_default_2x2)
+                             and isinstance(nxt, L.MaxPooling2D) and nxt.is_default_2x2
+                             and not (final_dy is not None and i + 1 == n - 1))
                 if fuse_pool:
                     ph, pw, co = nxt.output_shape
                     y = be.alloc((batch, ph, pw, co))
@@ -129,8 +157,8 @@ class _Lowerer:
                     i += 2
                     continue
                 oh, ow, co = layer.output_shape
-                y = be.alloc((batch, oh, ow, co))
-                dy = self.alloc_grad((batch, oh, ow, co))
+                y = self.act((batch, oh, ow, co))
+                dy = self.act_grad((batch, oh, ow, co), fdy)
                 pad = layer.pad_amounts()
                 relu = layer.activation == "relu"
                 prog.forward.append(be.conv2d_fwd(st.cur, w, b, y, layer.strides, pad, relu))
@@ -149,10 +177,10 @@ class _Lowerer:
 
             if isinstance(layer, L.MaxPooling2D):
                 ph, pw, c = layer.output_shape
-                y = be.alloc((batch, ph, pw, c))
+                y = self.act((batch, ph, pw, c))
                 code = be.alloc((batch, ph, pw, c), torch.uint8)
-                dy = self.alloc_grad((batch, ph, pw, c))
-                if layer.is_default_2x2:
+                dy = self.act_grad((batch, ph, pw, c), fdy)
+                if layer.is_default_2x2 and self.act_dtype == torch.float32:
                     prog.forward.append(be.maxpool2_fwd(st.cur, y, code))
                     if training:
                         self.stages.append([be.maxpool2_bwd(dy, code, y, st.d_cur, st.post_relu)]
@@ -165,7 +193,7 @@ class _Lowerer:
                         if st.d_cur is not None:
                             stage.append(be.maxpool_bwd(dy, code, st.d_cur, k, s, p))
                             if st.post_relu:
-                                stage.append(be.relu_bwd(st.d_cur, st.cur, st.d_cur))
+                                stage.append(self.relu_mask(st.d_cur, st.cur))
                         self.stages.append(stage)
                 prog.description.append(f"maxpool{layer.pool_size[0]}/s{layer.strides[0]} -> {tuple(y.shape)}")
                 # max(relu(x)) == relu(max(x)): the pool backward already applied the producer's mask
@@ -174,55 +202,32 @@ class _Lowerer:
                 continue
 
             if isinstance(layer, L.BatchNormalization):
-                gamma, beta = self.pview(self.params, layer)
-                dgamma, dbeta = self.pview(self.grads, layer)
-                c = layer.input_shape[-1]
-                relu = layer.activation == "relu"
-                y = be.alloc(tuple(st.cur.shape))
-                dy = self.alloc_grad(tuple(st.cur.shape))
-                stats, saved, red = be.alloc((2 * c,)), be.alloc((2 * c,)), be.alloc((2 * c,))
-                if getattr(layer, "_moving", None) is None or layer._moving.device != st.cur.device:
-                    moving = be.alloc((2 * c,))
-                    moving[c:] = 1.0
-                    layer._moving = moving          # moving_mean | moving_variance, exported with the weights
-                moving = layer._moving
-                x2d, y2d = st.cur.view(-1, c), y.view(-1, c)
-                prog.forward.append(be.bn_fwd(x2d, gamma, beta, stats, saved, moving if training else None, y2d,
-                                              layer.epsilon, layer.momentum, relu))
-                if training:
-                    dx2d = st.d_cur.view(-1, c) if st.d_cur is not None else None
-                    stage = [be.bn_bwd(x2d, y2d, dy.view(-1, c), gamma, saved, red, dx2d, dgamma, dbeta, relu)]
-                    if st.d_cur is not None and st.post_relu:
-                        stage.append(be.relu_bwd(st.d_cur, st.cur, st.d_cur))
-                    self.stages.append(stage)
-                prog.description.append(f"batchnorm{'+relu' if relu else ''} [C={c}]")
-                st = _State(y, dy, False)          # owns its ReLU mask
+                st = self.batchnorm(layer, st, fdy)
                 i += 1
                 continue
 
             if isinstance(layer, L.GlobalAveragePooling2D):
                 c = layer.input_shape[-1]
-                y = be.alloc((batch, c))
-                dy = self.alloc_grad((batch, c))
+                y = be.alloc((batch, c))                    # fp32 from here on
+                dy = self.alloc_grad((batch, c)) if fdy is None else fdy
                 prog.forward.append(be.gap_fwd(st.cur, y))
                 if training:
-                    stage = []
-                    if st.d_cur is not None:
-                        stage.append(be.gap_bwd(dy, st.d_cur))
-                        if st.post_relu:
-                            stage.append(be.relu_bwd(st.d_cur, st.cur, st.d_cur))
-                    self.stages.append(stage)
+                    self.stages.append([be.gap_bwd(dy, st.d_cur, st.cur if st.post_relu else None)]
+                                       if st.d_cur is not None else [])
                 prog.description.append(f"global_average_pool -> {tuple(y.shape)}")
                 st = _State(y, dy, False)
                 i += 1
                 continue
 
             if isinstance(layer, L.Residual):
-                st = self.residual(layer, st)
+                st = self.residual(layer, st, fdy)
                 i += 1
                 continue
 
             if isinstance(layer, L.Dense):
+                if st.cur.dim() != 2 or st.cur.dtype != torch.float32:
+                    raise ValueError("Dense expects a flattened fp32 input: put Flatten or "
+                                     "GlobalAveragePooling2D before it")
                 w, b = self.kernel_bias(self.params, layer)
                 dw, db = self.kernel_bias(self.grads, layer)
                 k_in, units = w.shape
@@ -240,7 +245,7 @@ class _Lowerer:
                     i += 1
                     continue
                 y = be.alloc((batch, units))
-                dy = self.alloc_grad((batch, units))
+                dy = self.alloc_grad((batch, units)) if fdy is None else fdy
                 relu = layer.activation == "relu"
                 prog.forward.append(be.dense_fwd(st.cur, w, b, y, relu))
                 if training:
@@ -262,47 +267,102 @@ class _Lowerer:
             raise NotImplementedError(f"layer type {type(layer).__name__} is not supported by the engine")
         return st
 
+    # -- Flatten: a view in fp32; the fp32 <-> bf16 boundary under the mixed policy -----------
+    def flatten(self, st: _State) -> _State:
+        be, batch, prog = self.be, self.batch, self.prog
+        if st.cur.dtype == torch.float32:
+            prog.description.append(f"flatten -> {tuple(st.cur.view(batch, -1).shape)} (view)")
+            return _State(st.cur.view(batch, -1), st.d_cur.view(batch, -1) if st.d_cur is not None else None,
+                          st.post_relu)
+        flat = st.cur.view(batch, -1)
+        y = be.alloc(tuple(flat.shape))
+        dy = self.alloc_grad(tuple(flat.shape))
+        prog.forward.append(be.cast(flat, y))
+        if self.training:
+            stage = []
+            if st.d_cur is not None:
+                stage.append(be.cast(dy, st.d_cur.view(batch, -1)))
+                if st.post_relu:
+                    stage.append(self.relu_mask(st.d_cur, st.cur))
+            self.stages.append(stage)
+        prog.description.append(f"flatten -> {tuple(y.shape)} (bf16 -> fp32)")
+        return _State(y, dy, False)
+
+    # -- BatchNormalization (+ReLU) ----------------------------------------------------------
+    def batchnorm(self, layer, st: _State, fdy) -> _State:
+        be, prog, training = self.be, self.prog, self.training
+        gamma, beta, mmean, mvar = self.pview(self.params, layer)
+        dgamma, dbeta, g_mmean, g_mvar = self.pview(self.grads, layer)
+        c = layer.input_shape[-1]
+        relu = layer.activation == "relu"
+        shape = tuple(st.cur.shape)
+        y = be.alloc(shape, st.cur.dtype)
+        dy = (fdy if fdy is not None else be.alloc(shape, st.cur.dtype)) if training else None
+        x2d, y2d = st.cur.view(-1, c), y.view(-1, c)
+        if training:
+            stats, saved, red = be.alloc((2 * c,)), be.alloc((2 * c,)), be.alloc((2 * c,))
+            dx2d = st.d_cur.view(-1, c) if st.d_cur is not None else None
+            fwd, bwd = be.batchnorm(x2d, y2d, gamma, beta, eps=layer.epsilon, momentum=layer.momentum, relu=relu,
+                                    stats=stats, saved=saved, red=red, moving=(mmean, mvar),
+                                    moving_grads=(g_mmean, g_mvar), inv_lr=self.inv_lr, inference=False,
+                                    dy2d=dy.view(-1, c), dx2d=dx2d, dgamma=dgamma, dbeta=dbeta)
+            stage = [bwd]
+            if st.d_cur is not None and st.post_relu:
+                stage.append(self.relu_mask(st.d_cur, st.cur))
+            self.stages.append(stage)
+        else:
+            fwd, _ = be.batchnorm(x2d, y2d, gamma, beta, eps=layer.epsilon, momentum=layer.momentum, relu=relu,
+                                  moving=(mmean, mvar), inference=True)
+        prog.forward.append(fwd)
+        prog.description.append(f"batchnorm{'+relu' if relu else ''} [C={c}]"
+                                f"{'' if training else ' (moving statistics)'}")
+        return _State(y, dy, False)          # owns its ReLU mask
+
     # -- relu(main(x) + shortcut(x)) ----------------------------------------------------
-    def residual(self, layer, st: _State) -> _State:
+    def residual(self, layer, st: _State, fdy=None) -> _State:
+        """Forward: y = act(main(x) + shortcut(x)).  Backward: the block's output gradient dy arrives
+        already masked by (y > 0) — ``post_relu`` on the returned state makes its writer do that — and
+        is read directly by the last layer of BOTH branches, so the block costs no ReLU-backward pass
+        and no copy; d_x = d_main + d_shortcut is one (masked) add."""
         be, training, prog = self.be, self.training, self.prog
         x, shape = st.cur, tuple(st.cur.shape)
         need_dx = training and st.d_cur is not None
-        d_main_in = be.alloc(shape) if need_dx else None
-        d_sc_in = be.alloc(shape) if (need_dx and layer.shortcut) else None
+        relu = layer.activation == "relu"
+        d_main_in = be.alloc(shape, x.dtype) if need_dx else None
+        d_sc_in = be.alloc(shape, x.dtype) if (need_dx and layer.shortcut) else None
+        out_shape = (self.batch, *layer.output_shape)
+        y = be.alloc(out_shape, x.dtype)
+        dy = (fdy if fdy is not None else be.alloc(out_shape, x.dtype)) if training else None
         sum_stage: list[Callable] = []
         self.stages.append(sum_stage)               # runs LAST in backward: d_x = d_main_in + d_shortcut_in
         prog.description.append(f"residual block {layer.name}:")
-        m = self.sequence(layer.main, _State(x, d_main_in, False), top_level=False)
-        s = self.sequence(layer.shortcut, _State(x, d_sc_in, False), top_level=False) if layer.shortcut else None
+        m = self.sequence(layer.main, _State(x, d_main_in, False), top_level=False, final_dy=dy)
+        s = (self.sequence(layer.shortcut, _State(x, d_sc_in, False), top_level=False, final_dy=dy)
+             if layer.shortcut else None)
         if m.post_relu or (s is not None and s.post_relu):
             raise ValueError("the last layer of a residual branch must not carry an activation")
-        out_shape = tuple(m.cur.shape)
-        y = be.alloc(out_shape)
-        dy = self.alloc_grad(out_shape)
-        relu = layer.activation == "relu"
+        if tuple(m.cur.shape) != out_shape or (s is not None and tuple(s.cur.shape) != out_shape):
+            raise ValueError(f"residual block {layer.name}: branch output shapes differ")
         sc_out = s.cur if s is not None else x
-        prog.forward.append(be.add_act(m.cur, sc_out, y, relu))
-        if training:
-            # dz = dy * (y > 0) is the gradient of BOTH branches' outputs: computed once into the main
-            # branch's buffer and copied for the shortcut branch.
-            dz = m.d_cur
-            stage = [be.relu_bwd(dy, y, dz)] if relu else [be.copy(dy, dz)]
-            if s is not None:
-                stage.append(be.copy(dz, s.d_cur))
-            self.stages.append(stage)
-            if need_dx:
-                other = d_sc_in if s is not None else dz
-                sum_stage.append(be.add_act(d_main_in, other, st.d_cur, False))
-                if st.post_relu:
-                    sum_stage.append(be.relu_bwd(st.d_cur, x, st.d_cur))
+        prog.forward.append(be.add_act(m.cur, sc_out, y, 1 if relu else 0))
+        if need_dx:
+            other = d_sc_in if s is not None else dy
+            if st.post_relu:
+                sum_stage.append(be.add_act(d_main_in, other, st.d_cur, 2, mask=x))
+            else:
+                sum_stage.append(be.add_act(d_main_in, other, st.d_cur, 0))
         prog.description.append(f"  add{'+relu' if relu else ''} -> {out_shape}")
-        return _State(y, dy, False)
+        return _State(y, dy, relu)
 
 
 def lower(layers, batch: int, be, layout: ArenaLayout, params, grads, x_in, labels,
-          training: bool = True) -> StepProgram:
-    """Build the step over ``x_in`` [B,H,W,C] / ``labels`` [B] for backend ``be``."""
-    lw = _Lowerer(batch, be, layout, params, grads, labels, training)
+          training: bool = True, lr: float = 0.0) -> StepProgram:
+    """Build the step over ``x_in`` [B,H,W,C] / ``labels`` [B] for backend ``be``.  ``lr`` is the
+    optimizer's learning rate (scales the BatchNorm moving-statistics pseudo-gradients)."""
+    lw = _Lowerer(batch, be, layout, params, grads, labels, training, lr)
+    begin = be.begin_step(params) if hasattr(be, "begin_step") else None
+    if begin is not None:
+        lw.prog.forward.append(begin)
     st = lw.sequence(layers, _State(x_in, None, False), top_level=True)
     prog = lw.prog
     if not lw.head_done:
@@ -316,4 +376,6 @@ def lower(layers, batch: int, be, layout: ArenaLayout, params, grads, x_in, labe
             prog.description.append("softmax_xent (+grad, +accuracy count)")
     for stage in reversed(lw.stages):
         prog.backward.extend(stage)
+    if begin is not None:
+        prog.early_forward = 0       # the step starts by re-reading every weight: nothing to overlap
     return prog

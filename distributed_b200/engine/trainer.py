@@ -56,8 +56,11 @@ class Trainer:
         self.backend_name = strategy.backend_name
         if self.backend_name == "cuda":
             from .cuda_backend import CudaBackend
+            from ..keras import mixed_precision
             torch.cuda.set_device(strategy.device)
-            self.be = CudaBackend(strategy.device)
+            self.policy = mixed_precision.global_policy()
+            self.be = CudaBackend(strategy.device, torch.bfloat16 if self.policy.compute_dtype == "bfloat16"
+                                  else torch.float32)
         else:
             from .cpu_backend import CpuBackend
             self.be = CpuBackend()
@@ -95,7 +98,7 @@ class Trainer:
         self.y_bytes = self.y_in[0].numel() * 4
         if self.backend_name != "cuda":
             self.progs.append(lower(self.layers, self.batch, be, lay, self.params, self.grads,
-                                    self.x_in[0], self.y_in[0]))
+                                    self.x_in[0], self.y_in[0], lr=self.lr))
             self.updates.append(self.comm.make_update(be, self.params, self.grads, lay.n_params, self.lr))
             return
         from .._native import cuda_lib as nl
@@ -120,7 +123,7 @@ class Trainer:
             for slot in range(n_slots):
                 g_slot = self.grad_bufs[slot % len(self.grad_bufs)]
                 prog = lower(self.layers, self.batch, be, lay, self.params, g_slot,
-                             self.x_in[slot], self.y_in[slot])
+                             self.x_in[slot], self.y_in[slot], lr=self.lr)
                 if len(self.grad_bufs) > 1:
                     g_other = self.grad_bufs[(slot + 1) % 2]
                     upd = self.comm.make_update(be, self.params, g_slot, lay.n_params, self.lr,

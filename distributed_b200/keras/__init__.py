@@ -1,5 +1,5 @@
 """``tf.keras`` facade: exactly the symbols the reference uses."""
-from . import callbacks, datasets, layers, losses, metrics, models, optimizers  # noqa: F401
+from . import callbacks, datasets, layers, losses, metrics, mixed_precision, models, optimizers  # noqa: F401
 from .models import History, Model, Sequential  # noqa: F401
 
 

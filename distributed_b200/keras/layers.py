@@ -77,6 +77,9 @@ class Layer:
     def count_params(self) -> int:
         return sum(p.size for p in self.param_specs())
 
+    def count_trainable_params(self) -> int:
+        return sum(p.size for p in self.param_specs() if p.trainable)
+
     def get_config(self) -> dict:
         return {"name": self.name}
 
@@ -229,7 +232,12 @@ class BatchNormalization(Layer):
 
     def param_specs(self):
         c = self.input_shape[-1]
-        return [ParamSpec(f"{self.name}/gamma:0", (c,), "ones"), ParamSpec(f"{self.name}/beta:0", (c,), "zeros")]
+        # Keras weight order.  The moving statistics are non-trainable arena slots: they are mirrored
+        # variables like the rest, exported / loaded with the weights, and kept identical on every
+        # replica by the same fused all-reduce that updates the trainable ones (engine/lowering.py).
+        return [ParamSpec(f"{self.name}/gamma:0", (c,), "ones"), ParamSpec(f"{self.name}/beta:0", (c,), "zeros"),
+                ParamSpec(f"{self.name}/moving_mean:0", (c,), "zeros", trainable=False),
+                ParamSpec(f"{self.name}/moving_variance:0", (c,), "ones", trainable=False)]
 
 
 class GlobalAveragePooling2D(Layer):

@@ -110,10 +110,16 @@ class Sequential(Model):
         return sum(l.count_params() for l in self.layers)
 
     @property
-    def trainable_weights(self):
+    def weights(self):
         return [s for l in self.layers for s in l.param_specs()]
 
-    weights = trainable_weights
+    @property
+    def trainable_weights(self):
+        return [s for s in self.weights if s.trainable]
+
+    @property
+    def non_trainable_weights(self):
+        return [s for s in self.weights if not s.trainable]
 
     def summary(self, print_fn=print):
         print_fn(f'Model: "{self.name}"')
@@ -125,7 +131,9 @@ class Sequential(Model):
             print_fn(f"{l.name + ' (' + type(l).__name__ + ')':<29}{shp:<26}{l.count_params():<10}")
         print_fn("=" * 65)
         print_fn(f"Total params: {self.count_params():,}")
-        print_fn(f"Trainable params: {self.count_params():,}")
+        trainable = sum(l.count_trainable_params() for l in self.layers)
+        print_fn(f"Trainable params: {trainable:,}")
+        print_fn(f"Non-trainable params: {self.count_params() - trainable:,}")
 
     # ---- compile -----------------------------------------------------------------------
     def compile(self, optimizer="sgd", loss=None, metrics=None, **kwargs):

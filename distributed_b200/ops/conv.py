@@ -21,7 +21,7 @@ class ConvDesc(C.Structure):
                 ("KH", C.c_int), ("KW", C.c_int), ("pad_h", C.c_int), ("pad_w", C.c_int),
                 ("x", C.c_void_p), ("w", C.c_void_p), ("y", C.c_void_p),
                 ("bias", C.c_void_p), ("mask", C.c_void_p), ("relu", C.c_int),
-                ("stride", C.c_int), ("OH", C.c_int), ("OW", C.c_int)]
+                ("stride", C.c_int), ("OH", C.c_int), ("OW", C.c_int), ("mask_dtype", C.c_int)]
 
 
 _declared = False
@@ -47,14 +47,15 @@ def _lib():
 def _desc(x, w, y, padding, bias=None, mask=None, relu=False, stride=1):
     N, H, W, Ci = x.shape
     KH, KW, Ci2, Co = w.shape
-    assert Ci == Ci2 and x.dtype == w.dtype
+    assert Ci == Ci2
     d = ConvDesc()
-    d.dtype, d.out_dtype = _DT[x.dtype], _DT[x.dtype]
+    d.dtype, d.out_dtype = _DT[x.dtype], _DT[y.dtype]
     d.N, d.H, d.W, d.Ci, d.Co, d.KH, d.KW = N, H, W, Ci, Co, KH, KW
     d.pad_h, d.pad_w = padding
     d.x, d.w, d.y = x.data_ptr(), w.data_ptr(), y.data_ptr()
     d.bias = bias.data_ptr() if bias is not None else None
     d.mask = mask.data_ptr() if mask is not None else None
+    d.mask_dtype = _DT[mask.dtype] if mask is not None else 0
     d.relu = int(relu)
     d.stride, d.OH, d.OW = int(stride), y.shape[1], y.shape[2]
     return d

@@ -11,24 +11,25 @@ def _p(t):
     return None if t is None else t.data_ptr()
 
 
-def _conv_args(x_shape, w_shape, strides, padding):
+def _conv_args(x_shape, w_shape, strides, padding, out_shape):
+    """padding = (top, left); the output tensor's own height / width fix the bottom / right padding."""
     N, H, W, Ci = x_shape
     KH, KW, _, Co = w_shape
-    return [N, H, W, Ci, Co, KH, KW, strides[0], strides[1], padding[0], padding[1]]
+    return [N, H, W, Ci, Co, KH, KW, strides[0], strides[1], padding[0], padding[1], out_shape[1], out_shape[2]]
 
 
 def conv2d_fwd(x, w, b, y, strides=(1, 1), padding=(0, 0), relu=False):
-    cpu_lib.lib().b2c_conv2d_fwd(_p(x), _p(w), _p(b), _p(y), *_conv_args(x.shape, w.shape, strides, padding),
+    cpu_lib.lib().b2c_conv2d_fwd(_p(x), _p(w), _p(b), _p(y), *_conv_args(x.shape, w.shape, strides, padding, y.shape),
                                  int(relu))
 
 
 def conv2d_wgrad(x, dy, dw, db, strides=(1, 1), padding=(0, 0)):
     cpu_lib.lib().b2c_conv2d_wgrad(_p(x), _p(dy), _p(dw), _p(db),
-                                   *_conv_args(x.shape, dw.shape, strides, padding))
+                                   *_conv_args(x.shape, dw.shape, strides, padding, dy.shape))
 
 
 def conv2d_dgrad(dy, w, dx, strides=(1, 1), padding=(0, 0)):
-    cpu_lib.lib().b2c_conv2d_dgrad(_p(dy), _p(w), _p(dx), *_conv_args(dx.shape, w.shape, strides, padding))
+    cpu_lib.lib().b2c_conv2d_dgrad(_p(dy), _p(w), _p(dx), *_conv_args(dx.shape, w.shape, strides, padding, dy.shape))
 
 
 def maxpool2_fwd(x, y, code):
@@ -66,3 +67,42 @@ def colsum(dy2d, db):
 
 def sgd_apply(w, g, n_params, lr):
     cpu_lib.lib().b2c_sgd_apply(_p(w), _p(g), n_params, w.numel(), float(lr))
+
+
+# ---- ResNet-family layers (csrc/cpu/resnet_ops.cpp) -------------------------------------------
+def bn_fwd(x2d, gamma, beta, y2d, saved, moving, moving_grads, eps, momentum, inv_lr, relu, inference):
+    M, C = x2d.shape
+    mm, mv = moving if moving is not None else (None, None)
+    gm, gv = moving_grads if moving_grads is not None else (None, None)
+    cpu_lib.lib().b2c_bn_fwd(_p(x2d), _p(gamma), _p(beta), _p(y2d), _p(saved), _p(mm), _p(mv), _p(gm), _p(gv),
+                             M, C, float(eps), float(momentum), float(inv_lr), int(relu), int(inference))
+
+
+def bn_bwd(x2d, y2d, dy2d, gamma, saved, dx2d, dgamma, dbeta, relu):
+    M, C = x2d.shape
+    cpu_lib.lib().b2c_bn_bwd(_p(x2d), _p(y2d), _p(dy2d), _p(gamma), _p(saved), _p(dx2d), _p(dgamma), _p(dbeta),
+                             M, C, int(relu))
+
+
+def add_act(a, b, out, mode, mask=None):
+    cpu_lib.lib().b2c_add_act(_p(a), _p(b), _p(mask), _p(out), a.numel(), int(mode))
+
+
+def maxpool_fwd(x, y, code, k, s, p):
+    N, H, W, C = x.shape
+    cpu_lib.lib().b2c_maxpool_fwd(_p(x), _p(y), _p(code), N, H, W, C, k, s, p, y.shape[1], y.shape[2])
+
+
+def maxpool_bwd(dy, code, dx, k, s, p):
+    N, H, W, C = dx.shape
+    cpu_lib.lib().b2c_maxpool_bwd(_p(dy), _p(code), _p(dx), N, H, W, C, k, s, p, dy.shape[1], dy.shape[2])
+
+
+def gap_fwd(x, y):
+    N, H, W, C = x.shape
+    cpu_lib.lib().b2c_gap_fwd(_p(x), _p(y), N, H * W, C)
+
+
+def gap_bwd(dy, dx, mask=None):
+    N, H, W, C = dx.shape
+    cpu_lib.lib().b2c_gap_bwd(_p(dy), _p(mask), _p(dx), N, H * W, C)

@@ -53,8 +53,8 @@ class GemmPlan:
         desc.D, desc.ldd = d.data_ptr(), d.stride(0)
         desc.bias = bias.data_ptr() if bias is not None else None
         if mask is not None:
-            assert mask.dtype == torch.float32 and mask.stride(1) == 1
-            desc.mask, desc.ldmask = mask.data_ptr(), mask.stride(0)
+            assert mask.dtype in _DT and mask.stride(1) == 1
+            desc.mask, desc.ldmask, desc.mask_dtype = mask.data_ptr(), mask.stride(0), _DT[mask.dtype]
         desc.relu, desc.accumulate, desc.splits = int(relu), int(accumulate), int(splits)
         lib = nl.lib()
         self.geometry = nl.GemmGeometry()

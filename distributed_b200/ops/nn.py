@@ -13,6 +13,19 @@ import torch
 from .._native import cuda_lib as nl
 
 _declared = False
+_DT = {torch.float32: 0, torch.bfloat16: 1}
+
+
+class BnDesc(C.Structure):
+    """Mirror of b2d_bn_desc (include/b200dist.h)."""
+    _fields_ = [("dtype", C.c_int), ("M", C.c_int), ("C", C.c_int), ("relu", C.c_int), ("inference", C.c_int),
+                ("eps", C.c_float), ("momentum", C.c_float), ("inv_lr", C.c_float),
+                ("x", C.c_void_p), ("y", C.c_void_p), ("dy", C.c_void_p), ("dx", C.c_void_p),
+                ("gamma", C.c_void_p), ("beta", C.c_void_p),
+                ("moving_mean", C.c_void_p), ("moving_var", C.c_void_p),
+                ("moving_mean_grad", C.c_void_p), ("moving_var_grad", C.c_void_p),
+                ("stats", C.c_void_p), ("saved", C.c_void_p), ("red", C.c_void_p),
+                ("dgamma", C.c_void_p), ("dbeta", C.c_void_p)]
 
 
 def _lib():
@@ -35,14 +48,16 @@ def _lib():
         lib.b2d_sgemm_simt.argtypes = [vp, i64, i64, vp, i64, i64, vp, i64, vp, i, i, i, i, i, vp]
         lib.b2d_sgd_apply.argtypes = [vp, vp, sz, sz, f, vp]
         lib.b2d_cast_f32_bf16.argtypes = [vp, vp, sz, vp]
-        lib.b2d_bn_fwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, i, i, f, f, i, vp]
-        lib.b2d_bn_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp]
-        lib.b2d_add_act.argtypes = [vp, vp, vp, sz, i, vp]
-        lib.b2d_maxpool_fwd.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, i, i, vp]
-        lib.b2d_maxpool_bwd.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, i, i, vp]
-        lib.b2d_gap_fwd.argtypes = [vp, vp, i, i, i, vp]
-        lib.b2d_gap_bwd.argtypes = [vp, vp, i, i, i, vp]
-        lib.b2d_im2col.argtypes = [vp, vp] + [i] * 13 + [vp]
+        lib.b2d_bn_forward.argtypes = [C.POINTER(BnDesc), vp]
+        lib.b2d_bn_backward.argtypes = [C.POINTER(BnDesc), vp]
+        lib.b2d_add_act.argtypes = [i, vp, vp, vp, vp, sz, i, vp]
+        lib.b2d_maxpool_fwd.argtypes = [i, vp, vp, vp, i, i, i, i, i, i, i, i, i, vp]
+        lib.b2d_maxpool_bwd.argtypes = [i, vp, vp, vp, i, i, i, i, i, i, i, i, i, vp]
+        lib.b2d_gap_fwd.argtypes = [i, vp, vp, i, i, i, vp]
+        lib.b2d_gap_bwd.argtypes = [i, vp, vp, vp, i, i, i, vp]
+        lib.b2d_im2col.argtypes = [i, i, vp, vp] + [i] * 13 + [vp]
+        lib.b2d_cast.argtypes = [i, i, vp, vp, sz, vp]
+        lib.b2d_colsum_t.argtypes = [i, vp, vp, i, i, vp]
         _declared = True
     return lib
 
@@ -153,49 +168,82 @@ def cast_f32_bf16(src, dst):
     nl.check(_lib().b2d_cast_f32_bf16(_p(src), _p(dst), src.numel(), _s()), "cast_f32_bf16")
 
 
-# ---- ResNet-family extras (BASELINE.json config 4) ---------------------------------------
-def bn_fwd(x2d, gamma, beta, stats, saved, moving, y2d, eps, momentum, relu):
-    """Training-mode BatchNorm over rows of x2d [M, C] (+ReLU).  stats [2C] scratch (kept zero),
-    saved [2C] receives mean / rstd, moving [2C] (mean, variance) is updated in place."""
-    M, Cc = x2d.shape
-    nl.check(_lib().b2d_bn_fwd(_p(x2d), _p(gamma), _p(beta), _p(stats), _p(saved), _p(moving), _p(y2d),
-                               M, Cc, float(eps), float(momentum), int(relu), _s()), "bn_fwd")
+# ---- ResNet-family kernels (BASELINE.json config 4; csrc/cuda/resnet_kernels.cu) -------------
+class BatchNorm:
+    """One BatchNormalization layer instance over x2d [M, C] (fp32 or bf16 storage): owns the
+    descriptor, so forward / backward are one C call each with no per-step host work.
+
+    ``moving`` = (mean, var) fp32 [C] tensors; ``moving_grads`` = matching gradient-arena slots (the
+    optimizer then performs the moving-average update, averaged over replicas) or None to update
+    ``moving`` in place.  ``stats``/``saved``/``red`` are zero-initialised [2C] scratch tensors."""
+
+    def __init__(self, x2d, y2d, gamma, beta, *, eps, momentum, relu, stats=None, saved=None, red=None,
+                 moving=None, moving_grads=None, inv_lr=0.0, inference=False,
+                 dy2d=None, dx2d=None, dgamma=None, dbeta=None):
+        M, Cc = x2d.shape
+        d = BnDesc()
+        d.dtype, d.M, d.C, d.relu, d.inference = _DT[x2d.dtype], M, Cc, int(relu), int(inference)
+        d.eps, d.momentum, d.inv_lr = float(eps), float(momentum), float(inv_lr)
+        d.x, d.y, d.dy, d.dx = _p(x2d), _p(y2d), _p(dy2d), _p(dx2d)
+        d.gamma, d.beta = _p(gamma), _p(beta)
+        if moving is not None:
+            d.moving_mean, d.moving_var = _p(moving[0]), _p(moving[1])
+        if moving_grads is not None:
+            d.moving_mean_grad, d.moving_var_grad = _p(moving_grads[0]), _p(moving_grads[1])
+        d.stats, d.saved, d.red, d.dgamma, d.dbeta = _p(stats), _p(saved), _p(red), _p(dgamma), _p(dbeta)
+        self.desc = d
+        self._keep = [x2d, y2d, gamma, beta, stats, saved, red, moving, moving_grads, dy2d, dx2d, dgamma, dbeta]
+        self._lib = _lib()
+
+    def forward(self):
+        nl.check(self._lib.b2d_bn_forward(C.byref(self.desc), _s()), "bn_forward")
+
+    def backward(self):
+        nl.check(self._lib.b2d_bn_backward(C.byref(self.desc), _s()), "bn_backward")
 
 
-def bn_bwd(x2d, y2d, dy2d, gamma, saved, red, dx2d, dgamma, dbeta, relu):
-    M, Cc = x2d.shape
-    nl.check(_lib().b2d_bn_bwd(_p(x2d), _p(y2d), _p(dy2d), _p(gamma), _p(saved), _p(red), _p(dx2d),
-                               _p(dgamma), _p(dbeta), M, Cc, int(relu), _s()), "bn_bwd")
-
-
-def add_act(a, b, out, relu):
-    nl.check(_lib().b2d_add_act(_p(a), _p(b), _p(out), a.numel(), int(relu), _s()), "add_act")
+def add_act(a, b, out, mode, mask=None):
+    """mode 0: out = a + b; 1: relu(a + b); 2: (a + b) where mask > 0 else 0.  ``b`` may be None."""
+    nl.check(_lib().b2d_add_act(_DT[a.dtype], _p(a), _p(b), _p(mask), _p(out), a.numel(), int(mode), _s()), "add_act")
 
 
 def maxpool_fwd(x, y, code, k, s, p):
     N, H, W, Cc = x.shape
-    nl.check(_lib().b2d_maxpool_fwd(_p(x), _p(y), _p(code), N, H, W, Cc, k, s, p, y.shape[1], y.shape[2], _s()),
-             "maxpool_fwd")
+    nl.check(_lib().b2d_maxpool_fwd(_DT[x.dtype], _p(x), _p(y), _p(code), N, H, W, Cc, k, s, p, y.shape[1],
+                                    y.shape[2], _s()), "maxpool_fwd")
 
 
 def maxpool_bwd(dy, code, dx, k, s, p):
     N, H, W, Cc = dx.shape
-    nl.check(_lib().b2d_maxpool_bwd(_p(dy), _p(code), _p(dx), N, H, W, Cc, k, s, p, dy.shape[1], dy.shape[2], _s()),
-             "maxpool_bwd")
+    nl.check(_lib().b2d_maxpool_bwd(_DT[dx.dtype], _p(dy), _p(code), _p(dx), N, H, W, Cc, k, s, p, dy.shape[1],
+                                    dy.shape[2], _s()), "maxpool_bwd")
 
 
 def gap_fwd(x, y):
+    """y [N, C] fp32 = mean over H, W of x [N, H, W, C] (fp32 or bf16)."""
     N, H, W, Cc = x.shape
-    nl.check(_lib().b2d_gap_fwd(_p(x), _p(y), N, H * W, Cc, _s()), "gap_fwd")
+    nl.check(_lib().b2d_gap_fwd(_DT[x.dtype], _p(x), _p(y), N, H * W, Cc, _s()), "gap_fwd")
 
 
-def gap_bwd(dy, dx):
+def gap_bwd(dy, dx, mask=None):
     N, H, W, Cc = dx.shape
-    nl.check(_lib().b2d_gap_bwd(_p(dy), _p(dx), N, H * W, Cc, _s()), "gap_bwd")
+    nl.check(_lib().b2d_gap_bwd(_DT[dx.dtype], _p(dy), _p(mask), _p(dx), N, H * W, Cc, _s()), "gap_bwd")
 
 
 def im2col(x, col, kernel, strides, padding, out_hw):
     """col[pixel, :] = flattened (kh, kw, ci) patch of x for every output pixel; col is [N*OH*OW, kpad]."""
     N, H, W, Ci = x.shape
-    nl.check(_lib().b2d_im2col(_p(x), _p(col), N, H, W, Ci, kernel[0], kernel[1], strides[0], strides[1],
-                               padding[0], padding[1], out_hw[0], out_hw[1], col.shape[1], _s()), "im2col")
+    nl.check(_lib().b2d_im2col(_DT[x.dtype], _DT[col.dtype], _p(x), _p(col), N, H, W, Ci, kernel[0], kernel[1],
+                               strides[0], strides[1], padding[0], padding[1], out_hw[0], out_hw[1], col.shape[1],
+                               _s()), "im2col")
+
+
+def cast(src, dst):
+    """dst = src converted between fp32 and bf16 (same element count)."""
+    nl.check(_lib().b2d_cast(_DT[src.dtype], _DT[dst.dtype], _p(src), _p(dst), src.numel(), _s()), "cast")
+
+
+def colsum_t(dy2d, db):
+    """db += column sums of dy2d [M, C] (fp32 or bf16 storage, C a multiple of 4 / 8)."""
+    M, Cc = dy2d.shape
+    nl.check(_lib().b2d_colsum_t(_DT[dy2d.dtype], _p(dy2d), _p(db), M, Cc, _s()), "colsum_t")

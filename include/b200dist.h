@@ -63,13 +63,14 @@ typedef struct b2d_gemm_desc {
   void* D;
   int64_t ldd;
   const float* bias;  /* optional, [N]                                     */
-  const float* mask;  /* optional, fp32 [M][ldmask]                        */
+  const void* mask;   /* optional, [M][ldmask] of mask_dtype: D = 0 where mask <= 0 */
   int64_t ldmask;
   int relu;
   int accumulate;     /* 1: D += result (fp32 atomics; D must be fp32)     */
   int splits;         /* 0 = choose automatically                          */
   float* workspace;   /* split-K scratch, b2d_gemm_workspace_bytes()       */
   uint32_t* counters; /* split-K tile counters, b2d_gemm_counter_count()   */
+  int mask_dtype;     /* b2d_dtype of mask (0 = fp32)                      */
 } b2d_gemm_desc;
 
 typedef struct b2d_gemm_plan b2d_gemm_plan;
@@ -119,11 +120,12 @@ typedef struct b2d_conv_desc {
   const void* w;
   void* y;
   const float* bias;
-  const float* mask;
+  const void* mask; /* optional ReLU mask of the output (dgrad): same shape as the output, mask_dtype */
   int relu;
   int stride;   /* forward / wgrad: input step per output pixel (0 or 1 = unit stride)          */
   int OH, OW;   /* output size; 0 = derive from symmetric padding (TF 'same' may be asymmetric:  */
                 /* pad_h / pad_w are the top / left amounts, the output size fixes the rest)    */
+  int mask_dtype;
 } b2d_conv_desc;
 typedef struct b2d_conv_wgrad_plan b2d_conv_wgrad_plan;
 int b2d_conv_tc_supported(const b2d_conv_desc* desc, int dgrad);
@@ -173,9 +175,6 @@ int b2d_conv2d_dgrad_direct(const float* dy, const float* w, float* dx, int N, i
 int b2d_conv2d_wgrad_direct(const float* x, const float* dy, float* dw, int N, int H, int W, int Ci,
                             int Co, int KH, int KW, int sh, int sw, int ph, int pw, int OH, int OW,
                             void* stream);
-/* Patch matrix for small-channel convolutions (feeds the tcgen05 GEMM): col[pixel][kpad], kpad >= KH*KW*Ci. */
-int b2d_im2col(const float* x, float* col, int N, int H, int W, int Ci, int KH, int KW, int sh, int sw, int ph,
-               int pw, int OH, int OW, int kpad, void* stream);
 /* CUDA-core GEMM with arbitrary strides (tiny / unaligned problems). */
 int b2d_sgemm_simt(const float* A, int64_t sam, int64_t sak, const float* B, int64_t sbk, int64_t sbn,
                    float* D, int64_t ldd, const float* bias, int M, int N, int K, int relu,
@@ -183,21 +182,60 @@ int b2d_sgemm_simt(const float* A, int64_t sam, int64_t sak, const float* B, int
 /* Single-replica optimizer step: w[:n_params] -= lr*g, w[n_params:] += g, g = 0 (README.md:302). */
 int b2d_sgd_apply(float* w, float* g, size_t n_params, size_t n_total, float lr, void* stream);
 int b2d_cast_f32_bf16(const float* src, void* dst, size_t n, void* stream);
-/* ResNet-family extras (BASELINE.json config 4; no counterpart in the reference README):
- * training-mode BatchNorm over rows of x [M,C] fused with ReLU (stats/red: zeroed scratch [2C];
- * saved: mean|rstd; moving: mean|variance), residual add (+ReLU), general max pooling
- * (window k, stride s, top/left padding p, explicit output size), global average pooling. */
-int b2d_bn_fwd(const float* x, const float* gamma, const float* beta, float* stats, float* saved,
-               float* moving, float* y, int M, int C, float eps, float momentum, int relu, void* stream);
-int b2d_bn_bwd(const float* x, const float* y, const float* dy, const float* gamma, const float* saved,
-               float* red, float* dx, float* dgamma, float* dbeta, int M, int C, int relu, void* stream);
-int b2d_add_act(const float* a, const float* b, float* out, size_t n, int relu, void* stream);
-int b2d_maxpool_fwd(const float* x, float* y, uint8_t* code, int N, int H, int W, int C, int k, int s, int p,
-                    int OH, int OW, void* stream);
-int b2d_maxpool_bwd(const float* dy, const uint8_t* code, float* dx, int N, int H, int W, int C, int k, int s,
+/* ---------------------------------------------------------------------------------------
+ * ResNet-family kernels (csrc/cuda/resnet_kernels.cu; BASELINE.json config 4 — none of these
+ * layers has a counterpart in the reference README).  `dtype` is the storage type of the
+ * activations (B2D_F32 or B2D_BF16, arithmetic is fp32); per-channel vectors stay fp32.
+ * Channel counts must be multiples of the 16-byte vector: 4 (fp32) or 8 (bf16).
+ * ------------------------------------------------------------------------------------- */
+typedef struct b2d_bn_desc {
+  int dtype;
+  int M, C;                  /* x, y, dy, dx are [M rows][C channels]                              */
+  int relu;                  /* fuse ReLU: y = max(.., 0); backward masks dy with y > 0             */
+  int inference;             /* 1: normalise with moving_mean / moving_var, touch nothing else      */
+  float eps, momentum;
+  float inv_lr;              /* see moving_*_grad                                                   */
+  const void* x;
+  void* y;
+  const void* dy;
+  void* dx;                  /* NULL: parameter gradients only                                      */
+  const float* gamma;
+  const float* beta;
+  /* Moving statistics [C] each.  Training with moving_*_grad == NULL updates them in place
+   * (m = momentum*m + (1-momentum)*batch).  With moving_*_grad set, the kernel instead stores the
+   * pseudo-gradient (1-momentum)*(m - batch)*inv_lr there, so that the optimizer's w -= lr*mean_r(g)
+   * — fused into the cross-replica all-reduce — performs the same update with the batch statistics
+   * AVERAGED OVER REPLICAS (what MirroredStrategy does for BatchNorm moving averages). */
+  float* moving_mean;
+  float* moving_var;
+  float* moving_mean_grad;
+  float* moving_var_grad;
+  /* Scratch [2C] each, zero before the first call: `stats` (batch sums; cleared by backward),
+   * `red` (backward sums; cleared by the next forward), `saved` (mean | rstd for backward). */
+  float* stats;
+  float* saved;
+  float* red;
+  float* dgamma;             /* += */
+  float* dbeta;              /* += */
+} b2d_bn_desc;
+int b2d_bn_forward(const b2d_bn_desc* d, void* stream);    /* 2 launches (1 in inference mode)       */
+int b2d_bn_backward(const b2d_bn_desc* d, void* stream);   /* 2 launches                             */
+/* mode 0: out = a + b; 1: out = relu(a + b); 2: out = (a + b) where mask > 0 else 0.  b may be NULL. */
+int b2d_add_act(int dtype, const void* a, const void* b, const void* mask, void* out, size_t n, int mode,
+                void* stream);
+/* General max pooling: window k, stride s, top/left padding p, explicit output size (<= 0: derive). */
+int b2d_maxpool_fwd(int dtype, const void* x, void* y, uint8_t* code, int N, int H, int W, int C, int k, int s,
                     int p, int OH, int OW, void* stream);
-int b2d_gap_fwd(const float* x, float* y, int N, int HW, int C, void* stream);
-int b2d_gap_bwd(const float* dy, float* dx, int N, int HW, int C, void* stream);
+int b2d_maxpool_bwd(int dtype, const void* dy, const uint8_t* code, void* dx, int N, int H, int W, int C, int k,
+                    int s, int p, int OH, int OW, void* stream);
+/* Global average pooling: y / dy are fp32 [N, C]; dx is zeroed where mask <= 0 (mask may be NULL). */
+int b2d_gap_fwd(int dtype, const void* x, float* y, int N, int HW, int C, void* stream);
+int b2d_gap_bwd(int dtype, const float* dy, const void* mask, void* dx, int N, int HW, int C, void* stream);
+/* Patch matrix for small-channel convolutions (feeds the tcgen05 GEMM): col[pixel][kpad], kpad >= KH*KW*Ci. */
+int b2d_im2col(int in_dtype, int out_dtype, const void* x, void* col, int N, int H, int W, int Ci, int KH, int KW,
+               int sh, int sw, int ph, int pw, int OH, int OW, int kpad, void* stream);
+int b2d_cast(int src_dtype, int dst_dtype, const void* src, void* dst, size_t n, void* stream);
+int b2d_colsum_t(int dtype, const void* dy, float* db, int M, int C, void* stream);   /* db += column sums */
 
 /* ---------------------------------------------------------------------------------------
  * Symmetric memory over NVLink (csrc/runtime/symm.cpp): one block per GPU, POSIX-fd exchange
@@ -279,12 +317,13 @@ int b2d_host_free(void* p);
  * CPU backend (libb200dist_cpu.so): C++ reference ops + shared-memory fused all-reduce/SGD.
  * ------------------------------------------------------------------------------------- */
 void b2c_set_num_threads(int n);
+/* ph, pw = padding at the top / left; OH, OW = output size (<= 0: derive from symmetric padding). */
 void b2c_conv2d_fwd(const float* x, const float* w, const float* bias, float* y, int N, int H, int W,
-                    int Ci, int Co, int KH, int KW, int sh, int sw, int ph, int pw, int relu);
+                    int Ci, int Co, int KH, int KW, int sh, int sw, int ph, int pw, int OH, int OW, int relu);
 void b2c_conv2d_wgrad(const float* x, const float* dy, float* dw, float* db, int N, int H, int W, int Ci,
-                      int Co, int KH, int KW, int sh, int sw, int ph, int pw);
+                      int Co, int KH, int KW, int sh, int sw, int ph, int pw, int OH, int OW);
 void b2c_conv2d_dgrad(const float* dy, const float* w, float* dx, int N, int H, int W, int Ci, int Co,
-                      int KH, int KW, int sh, int sw, int ph, int pw);
+                      int KH, int KW, int sh, int sw, int ph, int pw, int OH, int OW);
 void b2c_maxpool2_fwd(const float* x, float* y, uint8_t* code, int N, int H, int W, int C);
 void b2c_maxpool2_bwd(const float* dy, const uint8_t* code, const float* y_pooled, float* dx, int N,
                       int H, int W, int C, int act_relu);
@@ -295,6 +334,19 @@ void b2c_softmax_xent(const float* z, const int32_t* labels, float* dz, float* m
 void b2c_relu_bwd(const float* dy, const float* y, float* dx, int64_t n);
 void b2c_colsum(const float* dy, float* db, int M, int N);
 void b2c_sgd_apply(float* w, float* g, int64_t n_params, int64_t n_total, float lr);
+/* ResNet-family layers on the CPU (csrc/cpu/resnet_ops.cpp): same semantics as the b2d_* kernels above. */
+void b2c_bn_fwd(const float* x, const float* gamma, const float* beta, float* y, float* saved, float* moving_mean,
+                float* moving_var, float* g_mean, float* g_var, int64_t M, int C, float eps, float momentum,
+                float inv_lr, int relu, int inference);
+void b2c_bn_bwd(const float* x, const float* y, const float* dy, const float* gamma, const float* saved, float* dx,
+                float* dgamma, float* dbeta, int64_t M, int C, int relu);
+void b2c_add_act(const float* a, const float* b, const float* mask, float* out, int64_t n, int mode);
+void b2c_maxpool_fwd(const float* x, float* y, uint8_t* code, int N, int H, int W, int C, int k, int s, int p,
+                     int OH, int OW);
+void b2c_maxpool_bwd(const float* dy, const uint8_t* code, float* dx, int N, int H, int W, int C, int k, int s,
+                     int p, int OH, int OW);
+void b2c_gap_fwd(const float* x, float* y, int N, int HW, int C);
+void b2c_gap_bwd(const float* dy, const float* mask, float* dx, int N, int HW, int C);
 typedef struct b2c_shm_comm b2c_shm_comm;
 const char* b2c_last_error(void);
 b2c_shm_comm* b2c_shm_create(const char* name, int rank, int world, int64_t capacity_floats, double timeout_s);

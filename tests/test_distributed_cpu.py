@@ -77,3 +77,37 @@ def test_shm_allreduce_three_ranks_odd_sizes():
     res = [json.loads(s) for s in barrier_apply(_shm_allreduce, 3, timeout=120)]
     for out, same, diff in res:
         assert all(out) and same is True and diff is False
+
+
+def _train_bn(ctx, num_workers, per_worker=8):
+    """A BatchNorm model: per-replica batch statistics, moving statistics averaged over replicas."""
+    import os
+    os.environ["B200DIST_BACKEND"] = "cpu"
+    os.environ["TF_CONFIG"] = json.dumps(ctx.tf_config(base_port=int(ctx.address[0].split(":")[1]) % 20000 + 20000))
+    import numpy as np
+    import distributed_b200 as tf
+    L = tf.keras.layers
+    strategy = tf.distribute.experimental.MultiWorkerMirroredStrategy()
+    rng = np.random.default_rng(5)
+    x = rng.standard_normal((per_worker * num_workers, 8, 8, 4)).astype(np.float32)
+    x[per_worker:] += 3.0                      # the second replica's shard has a different mean
+    y = rng.integers(0, 10, len(x))
+    with strategy.scope():
+        model = tf.keras.Sequential([L.BatchNormalization(momentum=0.5, input_shape=(8, 8, 4)), L.ReLU(),
+                                     L.GlobalAveragePooling2D(), L.Dense(10)])
+        model.compile(loss=tf.keras.losses.SparseCategoricalCrossentropy(from_logits=True),
+                      optimizer=tf.keras.optimizers.SGD(0.1), metrics=["accuracy"])
+    model.fit(x, y, batch_size=len(x), epochs=1, steps_per_epoch=1, verbose=0)
+    w = dict(zip(model.weight_names(), model.get_weights()))
+    shard_means = [x[r * per_worker:(r + 1) * per_worker].mean((0, 1, 2)).tolist() for r in range(num_workers)]
+    return json.dumps({"mm": w["batch_normalization/moving_mean:0"].tolist(),
+                       "mv": w["batch_normalization/moving_variance:0"].tolist(),
+                       "gamma": w["batch_normalization/gamma:0"].tolist(), "shard_means": shard_means})
+
+
+def test_batchnorm_moving_statistics_are_averaged_over_replicas():
+    r = [json.loads(s) for s in barrier_apply(lambda ctx: _train_bn(ctx, 2), 2, timeout=300)]
+    assert r[0]["mm"] == r[1]["mm"] and r[0]["mv"] == r[1]["mv"] and r[0]["gamma"] == r[1]["gamma"]
+    # moving_mean = 0.5 * 0 + 0.5 * mean over replicas of the per-replica batch mean
+    expect = 0.5 * np.mean(np.asarray(r[0]["shard_means"]), axis=0)
+    assert np.allclose(r[0]["mm"], expect, atol=1e-5)
