@@ -14,10 +14,10 @@
 // Moving statistics: with g_mean / g_var given, the pseudo-gradient (1-momentum)*(m - batch)*inv_lr is
 // stored there (the optimizer's w -= lr*g then performs the moving-average update, averaged over
 // replicas by the gradient all-reduce); otherwise they are updated in place.  Inference: normalise
-// with the moving statistics and touch nothing else.
+// with the moving statistics and touch nothing else.  residual (optional, like x): y = act(bn(x) + residual).
 B2C_API void b2c_bn_fwd(const float* x, const float* gamma, const float* beta, float* y, float* saved,
                         float* moving_mean, float* moving_var, float* g_mean, float* g_var, int64_t M, int C,
-                        float eps, float momentum, float inv_lr, int relu, int inference) {
+                        float eps, float momentum, float inv_lr, int relu, int inference, const float* residual) {
   std::vector<double> sum(C, 0.0), sq(C, 0.0);
   std::vector<float> sc(C), sh(C);
   if (!inference) {
@@ -52,7 +52,7 @@ B2C_API void b2c_bn_fwd(const float* x, const float* gamma, const float* beta, f
   }
   for (int64_t r = 0; r < M; ++r)
     for (int c = 0; c < C; ++c) {
-      const float v = x[r * C + c] * sc[c] + sh[c];
+      const float v = x[r * C + c] * sc[c] + sh[c] + (residual ? residual[r * C + c] : 0.f);
       y[r * C + c] = relu ? std::max(v, 0.f) : v;
     }
 }

@@ -66,6 +66,7 @@ struct GemmArgs {
   void* D;
   const float* bias;
   const void* mask;
+  const void* addend;  // optional: D = epilogue(acc + addend), same dtype / row pitch as D (gradient sums)
   float* ws;
   uint32_t* counters;
   long long ldd;
@@ -103,6 +104,16 @@ __device__ __forceinline__ void epilogue_store4(const GemmArgs& a, int row, int 
   }
   if (a.flags & kFlagRelu) {
     v0 = fmaxf(v0, 0.f), v1 = fmaxf(v1, 0.f), v2 = fmaxf(v2, 0.f), v3 = fmaxf(v3, 0.f);
+  }
+  if (a.addend != nullptr) {
+    if (a.flags & kFlagOutBf16) {
+      const uint2 t = *reinterpret_cast<const uint2*>(static_cast<const uint16_t*>(a.addend) + (long long)row * a.ldd + col);
+      v0 += __uint_as_float(t.x << 16), v1 += __uint_as_float(t.x & 0xffff0000u);
+      v2 += __uint_as_float(t.y << 16), v3 += __uint_as_float(t.y & 0xffff0000u);
+    } else {
+      const float4 t = *reinterpret_cast<const float4*>(static_cast<const float*>(a.addend) + (long long)row * a.ldd + col);
+      v0 += t.x, v1 += t.y, v2 += t.z, v3 += t.w;
+    }
   }
   if (a.mask != nullptr) {
     float4 m;
@@ -142,6 +153,12 @@ __device__ __forceinline__ void epilogue_store8_bf16(const GemmArgs& a, int row,
   if (a.flags & kFlagRelu) {
 #pragma unroll
     for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
+  }
+  if (a.addend != nullptr) {
+    const uint4 t = *reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(a.addend) + (long long)row * a.ldd + col);
+    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v[2 * k] += __uint_as_float(w[k] << 16), v[2 * k + 1] += __uint_as_float(w[k] & 0xffff0000u);
   }
   if (a.mask != nullptr) {
     float m[8];
@@ -777,6 +794,7 @@ static int conv_plan_create(const b2d_conv_desc& d, bool dgrad, b2d_gemm_plan** 
   }
   GemmArgs& a = p->args;
   a.D = out_ptr, a.bias = dgrad ? nullptr : d.bias, a.mask = d.mask, a.ws = nullptr, a.counters = nullptr;
+  a.addend = dgrad ? d.addend : nullptr;
   a.ldd = n_ch, a.ldmask = n_ch, a.ldws = 0;
   a.M = gd.M, a.N = gd.N, a.K = gd.K;
   a.kb_total = g.k_blocks, a.kb_per_split = g.k_blocks, a.splits = 1;

@@ -63,6 +63,14 @@ __device__ __forceinline__ void store_scalar(__nv_bfloat16* p, float v) { *p = _
 __device__ __forceinline__ float load_scalar(const float* p) { return *p; }
 __device__ __forceinline__ float load_scalar(const __nv_bfloat16* p) { return __bfloat162float(*p); }
 
+// One 16-byte reduction per four channels: narrow tensors (C = 64) funnel every CTA's partial sums
+// into a handful of L2 lines, so the number of atomic operations is what bounds the tail.
+__device__ __forceinline__ void red_add_v4(float* p, const float* v) {
+  asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]),
+               "f"(v[3])
+               : "memory");
+}
+
 struct ChanMap {
   int cl, rg, nrg, col;
   bool ok;
@@ -132,7 +140,7 @@ __global__ void __launch_bounds__(256) col_stats_kernel(const T* __restrict__ x,
 #pragma unroll
   for (int k = 0; k < V; ++k) s[k] = 0.f, q[k] = 0.f;
   if (m.ok) {
-#pragma unroll 4
+#pragma unroll 8
     for (int r = r0 + m.rg; r < r1; r += m.nrg) {
       float v[V];
       VecIO<T>::load(x + (size_t)r * C + m.col, v);
@@ -146,9 +154,9 @@ __global__ void __launch_bounds__(256) col_stats_kernel(const T* __restrict__ x,
   cta_channel_reduce<V, SQ>(s, q, lanes_c);
   if (threadIdx.x < lanes_c && m.ok) {
 #pragma unroll
-    for (int k = 0; k < V; ++k) {
-      atomicAdd(&out[m.col + k], s[k]);
-      if (SQ) atomicAdd(&out[C + m.col + k], q[k]);
+    for (int k = 0; k < V; k += 4) {
+      red_add_v4(out + m.col + k, s + k);
+      if (SQ) red_add_v4(out + C + m.col + k, q + k);
     }
   }
 }
@@ -158,6 +166,7 @@ struct BnArgs {
   void* y;             // forward output; backward: the ReLU mask source when relu != 0
   const void* dy;
   void* dx;
+  const void* residual;  // forward: y = act(bn(x) + residual); backward then applies no ReLU mask
   const float *gamma, *beta;
   float *moving_mean, *moving_var;            // read in inference mode; updated in place when no *_grad
   float *moving_mean_grad, *moving_var_grad;  // training: pseudo-gradients (see b200dist.h)
@@ -210,16 +219,25 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const BnArgs a) {
     }
   }
   const T* x = static_cast<const T*>(a.x);
+  const T* res = static_cast<const T*>(a.residual);
   T* y = static_cast<T*>(a.y);
   const int r0 = blockIdx.y * a.rows_per_cta, r1 = min(M, r0 + a.rows_per_cta);
 #pragma unroll 4
   for (int r = r0 + m.rg; r < r1; r += m.nrg) {
     float v[V];
     VecIO<T>::load(x + (size_t)r * C + m.col, v);
+    if (res != nullptr) {
+      float rv[V];
+      VecIO<T>::load(res + (size_t)r * C + m.col, rv);
 #pragma unroll
-    for (int k = 0; k < V; ++k) {
-      v[k] = fmaf(v[k], sc[k], sh[k]);
-      if (a.relu) v[k] = fmaxf(v[k], 0.f);
+      for (int k = 0; k < V; ++k) v[k] = fmaf(v[k], sc[k], sh[k]) + rv[k];
+    } else {
+#pragma unroll
+      for (int k = 0; k < V; ++k) v[k] = fmaf(v[k], sc[k], sh[k]);
+    }
+    if (a.relu) {
+#pragma unroll
+      for (int k = 0; k < V; ++k) v[k] = fmaxf(v[k], 0.f);
     }
     VecIO<T>::store(y + (size_t)r * C + m.col, v);
   }
@@ -244,7 +262,7 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnArgs a) {
     float mean[V], rstd[V];
 #pragma unroll
     for (int k = 0; k < V; ++k) mean[k] = a.saved[m.col + k], rstd[k] = a.saved[C + m.col + k];
-#pragma unroll 2
+#pragma unroll 4
     for (int r = r0 + m.rg; r < r1; r += m.nrg) {
       const size_t o = (size_t)r * C + m.col;
       float g[V], xv[V];
@@ -266,9 +284,9 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnArgs a) {
   cta_channel_reduce<V, true>(s, q, a.lanes_c);
   if (threadIdx.x < a.lanes_c && m.ok) {
 #pragma unroll
-    for (int k = 0; k < V; ++k) {
-      atomicAdd(&a.red[m.col + k], s[k]);
-      atomicAdd(&a.red[C + m.col + k], q[k]);
+    for (int k = 0; k < V; k += 4) {
+      red_add_v4(a.red + m.col + k, s + k);
+      red_add_v4(a.red + C + m.col + k, q + k);
     }
   }
 }
@@ -604,7 +622,9 @@ struct ChanGrid {
   int lanes_c, rows_per_cta;
   dim3 grid;
 };
-static inline ChanGrid chan_grid(int M, int C, int V) {
+// ctas: how many CTAs to aim for — streaming kernels want many (8 per SM), the reduction kernels few
+// and fat ones (2 per SM): every CTA ends in atomics on the same 2C floats.
+static inline ChanGrid chan_grid(int M, int C, int V, int ctas = 148 * 8) {
   const int cvec = C / V;
   int lanes = 1;
   while (lanes < 32 && lanes < cvec) lanes <<= 1;
@@ -612,7 +632,7 @@ static inline ChanGrid chan_grid(int M, int C, int V) {
   g.lanes_c = lanes;
   const int gx = ceil_div(cvec, lanes);
   const int nrg = 256 / lanes;
-  const int target_y = max(1, (148 * 8) / gx);
+  const int target_y = max(1, ctas / gx);
   g.rows_per_cta = max(nrg * 4, ceil_div(M, target_y));
   g.grid = dim3(gx, ceil_div(M, g.rows_per_cta));
   return g;
@@ -626,12 +646,13 @@ typedef __nv_bfloat16 bf16_t;
 #define B2D_DTYPE_OK(dt) B2D_REQUIRE((dt) == B2D_F32 || (dt) == B2D_BF16, "unknown dtype %d", (int)(dt))
 
 static inline int vec_of(int dtype) { return dtype == B2D_F32 ? 4 : 8; }
+constexpr int kReduceCtas = 148 * 2;
 
 static int fill_bn_args(const b2d_bn_desc& d, BnArgs* a) {
   B2D_DTYPE_OK(d.dtype);
   const int V = vec_of(d.dtype);
   B2D_REQUIRE(d.M > 0 && d.C > 0 && d.C % V == 0, "batchnorm: C (%d) must be a multiple of %d", d.C, V);
-  a->x = d.x, a->y = d.y, a->dy = d.dy, a->dx = d.dx;
+  a->x = d.x, a->y = d.y, a->dy = d.dy, a->dx = d.dx, a->residual = d.residual;
   a->gamma = d.gamma, a->beta = d.beta;
   a->moving_mean = d.moving_mean, a->moving_var = d.moving_var;
   a->moving_mean_grad = d.moving_mean_grad, a->moving_var_grad = d.moving_var_grad;
@@ -656,17 +677,18 @@ extern "C" int b2d_bn_forward(const b2d_bn_desc* dp, void* stream) {
                   (d.moving_mean_grad == nullptr || (d.moving_mean && d.moving_var)),
               "bn_forward: inconsistent moving-statistics pointers");
   const ChanGrid g = chan_grid(d.M, d.C, vec_of(d.dtype));
+  const ChanGrid gr = chan_grid(d.M, d.C, vec_of(d.dtype), kReduceCtas);
   a.rows_per_cta = g.rows_per_cta, a.lanes_c = g.lanes_c;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (d.dtype == B2D_F32) {
     if (!d.inference)
-      B2D_CUDA_CHECK(launch_pdl(col_stats_kernel<float, true>, g.grid, dim3(256), 0, st, static_cast<const float*>(d.x),
-                                d.stats, d.M, d.C, g.rows_per_cta, g.lanes_c));
+      B2D_CUDA_CHECK(launch_pdl(col_stats_kernel<float, true>, gr.grid, dim3(256), 0, st, static_cast<const float*>(d.x),
+                                d.stats, d.M, d.C, gr.rows_per_cta, gr.lanes_c));
     B2D_CUDA_CHECK(launch_pdl(bn_apply_kernel<float>, g.grid, dim3(256), 0, st, a));
   } else {
     if (!d.inference)
-      B2D_CUDA_CHECK(launch_pdl(col_stats_kernel<bf16_t, true>, g.grid, dim3(256), 0, st,
-                                static_cast<const bf16_t*>(d.x), d.stats, d.M, d.C, g.rows_per_cta, g.lanes_c));
+      B2D_CUDA_CHECK(launch_pdl(col_stats_kernel<bf16_t, true>, gr.grid, dim3(256), 0, st,
+                                static_cast<const bf16_t*>(d.x), d.stats, d.M, d.C, gr.rows_per_cta, gr.lanes_c));
     B2D_CUDA_CHECK(launch_pdl(bn_apply_kernel<bf16_t>, g.grid, dim3(256), 0, st, a));
   }
   return B2D_OK;
@@ -680,15 +702,19 @@ extern "C" int b2d_bn_backward(const b2d_bn_desc* dp, void* stream) {
   if (rc != B2D_OK) return rc;
   B2D_REQUIRE(d.x && d.dy && d.gamma && d.saved && d.red && d.stats && d.dgamma && d.dbeta,
               "bn_backward: null tensor");
-  B2D_REQUIRE(!d.relu || d.y, "bn_backward: the ReLU mask needs the forward output");
-  ChanGrid g = chan_grid(d.M, d.C, vec_of(d.dtype));
+  if (d.residual != nullptr) a.relu = 0;   // dy is already the gradient of the pre-activation sum
+  B2D_REQUIRE(!a.relu || d.y, "bn_backward: the ReLU mask needs the forward output");
+  const ChanGrid g = chan_grid(d.M, d.C, vec_of(d.dtype));
+  const ChanGrid gr = chan_grid(d.M, d.C, vec_of(d.dtype), kReduceCtas);
   a.rows_per_cta = g.rows_per_cta, a.lanes_c = g.lanes_c;
+  BnArgs ar = a;
+  ar.rows_per_cta = gr.rows_per_cta;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (d.dtype == B2D_F32) {
-    B2D_CUDA_CHECK(launch_pdl(bn_bwd_reduce_kernel<float>, g.grid, dim3(256), 0, st, a));
+    B2D_CUDA_CHECK(launch_pdl(bn_bwd_reduce_kernel<float>, gr.grid, dim3(256), 0, st, ar));
     B2D_CUDA_CHECK(launch_pdl(bn_bwd_apply_kernel<float>, d.dx ? g.grid : dim3(g.grid.x, 1), dim3(256), 0, st, a));
   } else {
-    B2D_CUDA_CHECK(launch_pdl(bn_bwd_reduce_kernel<bf16_t>, g.grid, dim3(256), 0, st, a));
+    B2D_CUDA_CHECK(launch_pdl(bn_bwd_reduce_kernel<bf16_t>, gr.grid, dim3(256), 0, st, ar));
     B2D_CUDA_CHECK(launch_pdl(bn_bwd_apply_kernel<bf16_t>, d.dx ? g.grid : dim3(g.grid.x, 1), dim3(256), 0, st, a));
   }
   return B2D_OK;
@@ -829,7 +855,7 @@ extern "C" int b2d_colsum_t(int dtype, const void* dy, float* db, int M, int C, 
   B2D_DTYPE_OK(dtype);
   const int V = vec_of(dtype);
   B2D_REQUIRE(C % V == 0, "colsum: C (%d) must be a multiple of %d", C, V);
-  const ChanGrid g = chan_grid(M, C, V);
+  const ChanGrid g = chan_grid(M, C, V, kReduceCtas);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (dtype == B2D_F32)
     B2D_CUDA_CHECK(launch_pdl(col_stats_kernel<float, false>, g.grid, dim3(256), 0, st, static_cast<const float*>(dy), db,

@@ -28,7 +28,7 @@ def lib():
         l.b2c_relu_bwd.argtypes = [vp, vp, vp, i64]
         l.b2c_colsum.argtypes = [vp, vp, i, i]
         l.b2c_sgd_apply.argtypes = [vp, vp, i64, i64, f]
-        l.b2c_bn_fwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i, f, f, f, i, i]
+        l.b2c_bn_fwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i, f, f, f, i, i, vp]
         l.b2c_bn_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, i64, i, i]
         l.b2c_add_act.argtypes = [vp, vp, vp, vp, i64, i]
         l.b2c_maxpool_fwd.argtypes = [vp, vp, vp, i, i, i, i, i, i, i, i, i]

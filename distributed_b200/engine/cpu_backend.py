@@ -10,6 +10,7 @@ class CpuBackend:
     name = "cpu"
     device = torch.device("cpu")
     supports_conv_c1_pool = False
+    supports_bn_residual = True
     act_dtype = torch.float32
 
     def alloc(self, shape, dtype=torch.float32):
@@ -31,10 +32,15 @@ class CpuBackend:
     def conv2d_wgrad(self, x, dy, dw, db, strides, pad):
         return lambda: cpu.conv2d_wgrad(x, dy, dw, db, strides, pad)
 
-    def conv2d_dgrad(self, dy, w, dx, strides, pad, mask=None):
+    def dgrad_addend_ok(self, dx_shape, w_shape, strides, pad, out_hw, dtype):
+        return tuple(strides) == (1, 1)         # mirrors the CUDA backend's fused residual gradient sum
+
+    def conv2d_dgrad(self, dy, w, dx, strides, pad, mask=None, addend=None):
         def run():
             cpu.conv2d_dgrad(dy, w, dx, strides, pad)
-            if mask is not None:
+            if addend is not None:
+                cpu.add_act(dx, addend, dx, 2 if mask is not None else 0, mask)
+            elif mask is not None:
                 cpu.relu_bwd(dx, mask, dx)
         return run
 
@@ -70,12 +76,13 @@ class CpuBackend:
     # ---- ResNet-family layers (fp32; the dtype policy only affects the CUDA backend) --------------
     def batchnorm(self, x2d, y2d, gamma, beta, *, eps, momentum, relu, stats=None, saved=None, red=None,
                   moving=None, moving_grads=None, inv_lr=0.0, inference=False, dy2d=None, dx2d=None,
-                  dgamma=None, dbeta=None):
+                  dgamma=None, dbeta=None, residual=None):
         def fwd():
-            cpu.bn_fwd(x2d, gamma, beta, y2d, saved, moving, moving_grads, eps, momentum, inv_lr, relu, inference)
+            cpu.bn_fwd(x2d, gamma, beta, y2d, saved, moving, moving_grads, eps, momentum, inv_lr, relu, inference,
+                       residual)
 
-        def bwd():
-            cpu.bn_bwd(x2d, y2d, dy2d, gamma, saved, dx2d, dgamma, dbeta, relu)
+        def bwd():      # with a residual input the block's output gradient arrives already masked
+            cpu.bn_bwd(x2d, y2d, dy2d, gamma, saved, dx2d, dgamma, dbeta, relu and residual is None)
         return fwd, bwd
 
     def add_act(self, a, b, out, mode, mask=None):

@@ -24,6 +24,7 @@ _HEAD_SMEM = 200 * 1024
 class CudaBackend:
     name = "cuda"
     supports_conv_c1_pool = True
+    supports_bn_residual = True
 
     def __init__(self, device, act_dtype=torch.float32):
         self.device = torch.device(device)
@@ -77,7 +78,8 @@ class CudaBackend:
         if self._conv_tc_ok(x_shape, w_shape, layer.strides, layer.pad_amounts(), out_hw=layer.output_shape[:2],
                             dtype=self.act_dtype):
             return f"tcgen05 {kind} implicit GEMM (4-D TMA taps)"
-        if self.act_dtype == torch.bfloat16 or (ci * 4) % 128 != 0:
+        direct = os.environ.get("B200DIST_CONV", "") == "direct"
+        if not direct and (self.act_dtype == torch.bfloat16 or (ci * 4) % 128 != 0):
             return f"im2col + tcgen05 {kind} GEMM"
         return "direct conv (CUDA cores)"
 
@@ -188,10 +190,20 @@ class CudaBackend:
                     nn.colsum_t(dy2, db)
         return run
 
-    def conv2d_dgrad(self, dy, w, dx, strides, pad, mask=None):
+    def dgrad_addend_ok(self, dx_shape, w_shape, strides, pad, out_hw, dtype):
+        """True when the data gradient of this convolution can add another tensor in its epilogue."""
+        return (tuple(strides) == (1, 1) and os.environ.get("B200DIST_FUSE_SUM", "1") != "0"
+                and self._conv_tc_ok(dx_shape, w_shape, strides, pad, dgrad=True, out_hw=out_hw, dtype=dtype))
+
+    def conv2d_dgrad(self, dy, w, dx, strides, pad, mask=None, addend=None):
         from ..ops import conv as tc
         dt = dx.dtype
         wk = self._w_for(w, dt)
+        if addend is not None:
+            assert self.dgrad_addend_ok(dx.shape, w.shape, strides, pad, dy.shape[1:3], dt)
+            plan = tc.ConvDgradPlan(dy, wk, dx, pad, mask=mask, addend=addend)
+            self.plans.append(plan)
+            return plan.run
         if (strides[0] == strides[1] and strides[0] > 1 and os.environ.get("B200DIST_CONV", "") != "direct"
                 and tc.dgrad_strided_supported(dx.shape, w.shape, strides[0], dt)):
             plan = tc.ConvDgradStridedPlan(dy, wk, dx, pad, strides[0], mask=mask)

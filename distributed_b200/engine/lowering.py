@@ -60,6 +60,7 @@ class _State:
     cur: torch.Tensor                 # activation
     d_cur: torch.Tensor | None        # where the gradient w.r.t. `cur` must be written (None: not needed)
     post_relu: bool = False           # True: that gradient must be masked by cur > 0 by whoever writes it
+    addend: torch.Tensor | None = None  # the writer must ADD this tensor to the gradient (residual sum)
 
 
 class _Lowerer:
@@ -74,6 +75,7 @@ class _Lowerer:
         self.stages: list[list[Callable]] = []      # backward stages in forward order
         self.pending_bias_grad = None
         self.head_done = False
+        self.fused_tail = False
 
     # -- helpers ---------------------------------------------------------------------
     def pview(self, flat, layer):
@@ -113,9 +115,11 @@ class _Lowerer:
         return self.be.relu_bwd(d_buf, act, d_buf)
 
     # -- a list of layers --------------------------------------------------------------
-    def sequence(self, layers, st: _State, top_level: bool, final_dy=None) -> _State:
+    def sequence(self, layers, st: _State, top_level: bool, final_dy=None, final_fuse=None) -> _State:
         """Lower ``layers`` starting from state ``st``.  ``final_dy``: gradient buffer the LAST layer
-        must use for its output (a residual branch reads the block's output gradient directly)."""
+        must use for its output (a residual branch reads the block's output gradient directly).
+        ``final_fuse`` = (residual, relu, out): if the last layer is a BatchNormalization it computes
+        out = act(bn(x) + residual) itself (the tail of a residual block); sets ``self.fused_tail``."""
         be, batch, prog, training = self.be, self.batch, self.prog, self.training
         i, n = 0, len(layers)
         while i < n:
@@ -165,8 +169,9 @@ class _Lowerer:
                 if training:
                     stage = [be.conv2d_wgrad(st.cur, dy, dw, db, layer.strides, pad)]
                     if st.d_cur is not None:
+                        extra = {"addend": st.addend} if st.addend is not None else {}
                         stage.append(be.conv2d_dgrad(dy, w, st.d_cur, layer.strides, pad,
-                                                     mask=st.cur if st.post_relu else None))
+                                                     mask=st.cur if st.post_relu else None, **extra))
                     self.stages.append(stage)
                 prog.description.append(
                     f"conv2d{layer.kernel_size}{'/s' + str(layer.strides[0]) if layer.strides != (1, 1) else ''}"
@@ -202,7 +207,7 @@ class _Lowerer:
                 continue
 
             if isinstance(layer, L.BatchNormalization):
-                st = self.batchnorm(layer, st, fdy)
+                st = self.batchnorm(layer, st, fdy, final_fuse if i == n - 1 else None)
                 i += 1
                 continue
 
@@ -289,14 +294,20 @@ class _Lowerer:
         return _State(y, dy, False)
 
     # -- BatchNormalization (+ReLU) ----------------------------------------------------------
-    def batchnorm(self, layer, st: _State, fdy) -> _State:
+    def batchnorm(self, layer, st: _State, fdy, fuse=None) -> _State:
         be, prog, training = self.be, self.prog, self.training
         gamma, beta, mmean, mvar = self.pview(self.params, layer)
         dgamma, dbeta, g_mmean, g_mvar = self.pview(self.grads, layer)
         c = layer.input_shape[-1]
         relu = layer.activation == "relu"
         shape = tuple(st.cur.shape)
-        y = be.alloc(shape, st.cur.dtype)
+        extra = {}
+        if fuse is not None and not relu and getattr(be, "supports_bn_residual", False):
+            res, relu, y = fuse                       # y = act(bn(x) + residual), written to the block output
+            extra = {"residual": res.view(-1, c)}
+            self.fused_tail = True
+        else:
+            y = be.alloc(shape, st.cur.dtype)
         dy = (fdy if fdy is not None else be.alloc(shape, st.cur.dtype)) if training else None
         x2d, y2d = st.cur.view(-1, c), y.view(-1, c)
         if training:
@@ -305,18 +316,20 @@ class _Lowerer:
             fwd, bwd = be.batchnorm(x2d, y2d, gamma, beta, eps=layer.epsilon, momentum=layer.momentum, relu=relu,
                                     stats=stats, saved=saved, red=red, moving=(mmean, mvar),
                                     moving_grads=(g_mmean, g_mvar), inv_lr=self.inv_lr, inference=False,
-                                    dy2d=dy.view(-1, c), dx2d=dx2d, dgamma=dgamma, dbeta=dbeta)
+                                    dy2d=dy.view(-1, c), dx2d=dx2d, dgamma=dgamma, dbeta=dbeta, **extra)
             stage = [bwd]
             if st.d_cur is not None and st.post_relu:
                 stage.append(self.relu_mask(st.d_cur, st.cur))
             self.stages.append(stage)
         else:
             fwd, _ = be.batchnorm(x2d, y2d, gamma, beta, eps=layer.epsilon, momentum=layer.momentum, relu=relu,
-                                  moving=(mmean, mvar), inference=True)
+                                  moving=(mmean, mvar), inference=True, **extra)
         prog.forward.append(fwd)
-        prog.description.append(f"batchnorm{'+relu' if relu else ''} [C={c}]"
+        prog.description.append(f"batchnorm{'+residual' if extra else ''}{'+relu' if relu else ''} [C={c}]"
                                 f"{'' if training else ' (moving statistics)'}")
-        return _State(y, dy, False)          # owns its ReLU mask
+        # own ReLU: masks internally from its output.  Fused block tail: the block's ReLU is the CONSUMER's
+        # business (post_relu), exactly as for an unfused residual block.
+        return _State(y, dy, relu if extra else False)
 
     # -- relu(main(x) + shortcut(x)) ----------------------------------------------------
     def residual(self, layer, st: _State, fdy=None) -> _State:
@@ -328,7 +341,6 @@ class _Lowerer:
         x, shape = st.cur, tuple(st.cur.shape)
         need_dx = training and st.d_cur is not None
         relu = layer.activation == "relu"
-        d_main_in = be.alloc(shape, x.dtype) if need_dx else None
         d_sc_in = be.alloc(shape, x.dtype) if (need_dx and layer.shortcut) else None
         out_shape = (self.batch, *layer.output_shape)
         y = be.alloc(out_shape, x.dtype)
@@ -336,22 +348,49 @@ class _Lowerer:
         sum_stage: list[Callable] = []
         self.stages.append(sum_stage)               # runs LAST in backward: d_x = d_main_in + d_shortcut_in
         prog.description.append(f"residual block {layer.name}:")
-        m = self.sequence(layer.main, _State(x, d_main_in, False), top_level=False, final_dy=dy)
+        # d_x = d_main + d_shortcut (masked by x > 0 when x is a ReLU output).  When the main branch
+        # starts with a convolution whose data gradient runs on the tensor cores, that kernel adds the
+        # shortcut's gradient (and masks) in its epilogue and writes d_x itself; otherwise one add kernel.
+        other = (d_sc_in if layer.shortcut else dy) if need_dx else None
+        first = layer.main[0] if layer.main else None
+        fuse_sum = (need_dx and isinstance(first, L.Conv2D) and hasattr(be, "dgrad_addend_ok")
+                    and be.dgrad_addend_ok(shape, (*first.kernel_size, shape[3], first.filters), first.strides,
+                                           first.pad_amounts(), first.output_shape[:2], x.dtype))
+        if fuse_sum:
+            main_in = _State(x, st.d_cur, st.post_relu, addend=other)
+        else:
+            d_main_in = be.alloc(shape, x.dtype) if need_dx else None
+            main_in = _State(x, d_main_in, False)
+        # Forward order: shortcut, then main — so that a BatchNorm ending the main branch can add the
+        # shortcut and apply the block's ReLU itself.  Backward order is the reverse of the order of
+        # self.stages, and must be: shortcut, then main (whose first convolution may consume the shortcut's
+        # input gradient), then the sum — hence the stage lists are swapped after lowering.
+        i0 = len(self.stages)
         s = (self.sequence(layer.shortcut, _State(x, d_sc_in, False), top_level=False, final_dy=dy)
              if layer.shortcut else None)
-        if m.post_relu or (s is not None and s.post_relu):
+        i1 = len(self.stages)
+        if s is not None and s.post_relu:
             raise ValueError("the last layer of a residual branch must not carry an activation")
+        sc_out = s.cur if s is not None else x
+        self.fused_tail = False
+        m = self.sequence(layer.main, main_in, top_level=False, final_dy=dy, final_fuse=(sc_out, relu, y))
+        fused_tail, self.fused_tail = self.fused_tail, False
+        self.stages[i0:] = self.stages[i1:] + self.stages[i0:i1]
         if tuple(m.cur.shape) != out_shape or (s is not None and tuple(s.cur.shape) != out_shape):
             raise ValueError(f"residual block {layer.name}: branch output shapes differ")
-        sc_out = s.cur if s is not None else x
-        prog.forward.append(be.add_act(m.cur, sc_out, y, 1 if relu else 0))
-        if need_dx:
-            other = d_sc_in if s is not None else dy
+        if not fused_tail:
+            if m.post_relu:
+                raise ValueError("the last layer of a residual branch must not carry an activation")
+            prog.forward.append(be.add_act(m.cur, sc_out, y, 1 if relu else 0))
+        if need_dx and not fuse_sum:
             if st.post_relu:
                 sum_stage.append(be.add_act(d_main_in, other, st.d_cur, 2, mask=x))
             else:
                 sum_stage.append(be.add_act(d_main_in, other, st.d_cur, 0))
-        prog.description.append(f"  add{'+relu' if relu else ''} -> {out_shape}")
+        if fuse_sum:
+            prog.description.append("  gradient sum fused into the first convolution's data-gradient epilogue")
+        prog.description.append(f"  add{'+relu' if relu else ''} -> {out_shape}"
+                                f"{' (inside the last batchnorm)' if fused_tail else ''}")
         return _State(y, dy, relu)
 
 

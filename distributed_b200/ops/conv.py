@@ -21,7 +21,8 @@ class ConvDesc(C.Structure):
                 ("KH", C.c_int), ("KW", C.c_int), ("pad_h", C.c_int), ("pad_w", C.c_int),
                 ("x", C.c_void_p), ("w", C.c_void_p), ("y", C.c_void_p),
                 ("bias", C.c_void_p), ("mask", C.c_void_p), ("relu", C.c_int),
-                ("stride", C.c_int), ("OH", C.c_int), ("OW", C.c_int), ("mask_dtype", C.c_int)]
+                ("stride", C.c_int), ("OH", C.c_int), ("OW", C.c_int), ("mask_dtype", C.c_int),
+                ("addend", C.c_void_p)]
 
 
 _declared = False
@@ -44,7 +45,7 @@ def _lib():
     return lib
 
 
-def _desc(x, w, y, padding, bias=None, mask=None, relu=False, stride=1):
+def _desc(x, w, y, padding, bias=None, mask=None, relu=False, stride=1, addend=None):
     N, H, W, Ci = x.shape
     KH, KW, Ci2, Co = w.shape
     assert Ci == Ci2
@@ -57,6 +58,7 @@ def _desc(x, w, y, padding, bias=None, mask=None, relu=False, stride=1):
     d.mask = mask.data_ptr() if mask is not None else None
     d.mask_dtype = _DT[mask.dtype] if mask is not None else 0
     d.relu = int(relu)
+    d.addend = addend.data_ptr() if addend is not None else None
     d.stride, d.OH, d.OW = int(stride), y.shape[1], y.shape[2]
     return d
 
@@ -102,11 +104,14 @@ class ConvFwdPlan(_Plan):
 
 
 class ConvDgradPlan(_Plan):
-    """dx = conv2d_transpose(dy, w) (zeroed where mask <= 0), dx [N,H,W,Ci], dy [N,OH,OW,Co]."""
+    """dx = conv2d_transpose(dy, w) [+ addend] (zeroed where mask <= 0), dx [N,H,W,Ci], dy [N,OH,OW,Co].
+    ``addend`` (same shape / dtype as dx) is summed in the epilogue: the other branch's gradient of a
+    residual block, so that the block's gradient sum costs no extra pass."""
 
-    def __init__(self, dy, w, dx, padding=(0, 0), mask=None):
-        super().__init__(_lib().b2d_conv_dgrad_plan_create, _desc(dx, w, dy, padding, None, mask, False),
-                         [dy, w, dx, mask])
+    def __init__(self, dy, w, dx, padding=(0, 0), mask=None, addend=None):
+        assert addend is None or (addend.shape == dx.shape and addend.dtype == dx.dtype)
+        super().__init__(_lib().b2d_conv_dgrad_plan_create,
+                         _desc(dx, w, dy, padding, None, mask, False, addend=addend), [dy, w, dx, mask, addend])
 
 
 class ConvDgradStridedPlan:

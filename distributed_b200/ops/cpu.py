@@ -70,12 +70,13 @@ def sgd_apply(w, g, n_params, lr):
 
 
 # ---- ResNet-family layers (csrc/cpu/resnet_ops.cpp) -------------------------------------------
-def bn_fwd(x2d, gamma, beta, y2d, saved, moving, moving_grads, eps, momentum, inv_lr, relu, inference):
+def bn_fwd(x2d, gamma, beta, y2d, saved, moving, moving_grads, eps, momentum, inv_lr, relu, inference,
+           residual=None):
     M, C = x2d.shape
     mm, mv = moving if moving is not None else (None, None)
     gm, gv = moving_grads if moving_grads is not None else (None, None)
     cpu_lib.lib().b2c_bn_fwd(_p(x2d), _p(gamma), _p(beta), _p(y2d), _p(saved), _p(mm), _p(mv), _p(gm), _p(gv),
-                             M, C, float(eps), float(momentum), float(inv_lr), int(relu), int(inference))
+                             M, C, float(eps), float(momentum), float(inv_lr), int(relu), int(inference), _p(residual))
 
 
 def bn_bwd(x2d, y2d, dy2d, gamma, saved, dx2d, dgamma, dbeta, relu):

@@ -25,7 +25,7 @@ class BnDesc(C.Structure):
                 ("moving_mean", C.c_void_p), ("moving_var", C.c_void_p),
                 ("moving_mean_grad", C.c_void_p), ("moving_var_grad", C.c_void_p),
                 ("stats", C.c_void_p), ("saved", C.c_void_p), ("red", C.c_void_p),
-                ("dgamma", C.c_void_p), ("dbeta", C.c_void_p)]
+                ("dgamma", C.c_void_p), ("dbeta", C.c_void_p), ("residual", C.c_void_p)]
 
 
 def _lib():
@@ -179,7 +179,7 @@ class BatchNorm:
 
     def __init__(self, x2d, y2d, gamma, beta, *, eps, momentum, relu, stats=None, saved=None, red=None,
                  moving=None, moving_grads=None, inv_lr=0.0, inference=False,
-                 dy2d=None, dx2d=None, dgamma=None, dbeta=None):
+                 dy2d=None, dx2d=None, dgamma=None, dbeta=None, residual=None):
         M, Cc = x2d.shape
         d = BnDesc()
         d.dtype, d.M, d.C, d.relu, d.inference = _DT[x2d.dtype], M, Cc, int(relu), int(inference)
@@ -191,8 +191,9 @@ class BatchNorm:
         if moving_grads is not None:
             d.moving_mean_grad, d.moving_var_grad = _p(moving_grads[0]), _p(moving_grads[1])
         d.stats, d.saved, d.red, d.dgamma, d.dbeta = _p(stats), _p(saved), _p(red), _p(dgamma), _p(dbeta)
+        d.residual = _p(residual)
         self.desc = d
-        self._keep = [x2d, y2d, gamma, beta, stats, saved, red, moving, moving_grads, dy2d, dx2d, dgamma, dbeta]
+        self._keep = [x2d, y2d, gamma, beta, stats, saved, red, moving, moving_grads, dy2d, dx2d, dgamma, dbeta, residual]
         self._lib = _lib()
 
     def forward(self):

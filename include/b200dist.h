@@ -126,6 +126,7 @@ typedef struct b2d_conv_desc {
   int OH, OW;   /* output size; 0 = derive from symmetric padding (TF 'same' may be asymmetric:  */
                 /* pad_h / pad_w are the top / left amounts, the output size fixes the rest)    */
   int mask_dtype;
+  const void* addend; /* unit-stride dgrad only: dx = mask(conv_transpose(dy, w) + addend), addend like dx */
 } b2d_conv_desc;
 typedef struct b2d_conv_wgrad_plan b2d_conv_wgrad_plan;
 int b2d_conv_tc_supported(const b2d_conv_desc* desc, int dgrad);
@@ -217,6 +218,10 @@ typedef struct b2d_bn_desc {
   float* red;
   float* dgamma;             /* += */
   float* dbeta;              /* += */
+  /* Optional residual input (like x): forward computes y = act(bn(x) + residual) — the tail of a
+   * residual block in one pass; backward then applies NO ReLU mask (the producer of dy, which is the
+   * gradient of the block output, has already masked it). */
+  const void* residual;
 } b2d_bn_desc;
 int b2d_bn_forward(const b2d_bn_desc* d, void* stream);    /* 2 launches (1 in inference mode)       */
 int b2d_bn_backward(const b2d_bn_desc* d, void* stream);   /* 2 launches                             */
@@ -337,7 +342,7 @@ void b2c_sgd_apply(float* w, float* g, int64_t n_params, int64_t n_total, float 
 /* ResNet-family layers on the CPU (csrc/cpu/resnet_ops.cpp): same semantics as the b2d_* kernels above. */
 void b2c_bn_fwd(const float* x, const float* gamma, const float* beta, float* y, float* saved, float* moving_mean,
                 float* moving_var, float* g_mean, float* g_var, int64_t M, int C, float eps, float momentum,
-                float inv_lr, int relu, int inference);
+                float inv_lr, int relu, int inference, const float* residual);
 void b2c_bn_bwd(const float* x, const float* y, const float* dy, const float* gamma, const float* saved, float* dx,
                 float* dgamma, float* dbeta, int64_t M, int C, int relu);
 void b2c_add_act(const float* a, const float* b, const float* mask, float* out, int64_t n, int mode);

@@ -176,3 +176,25 @@ def test_stem_conv_bf16_via_im2col():
     assert (y.float() - ref).abs().max().item() < 1e-2 * ref.abs().max().item()
     pre.backward(dy.float())
     assert (dw - wq.grad).abs().max().item() < 5e-3 * wq.grad.abs().max().item()
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_dgrad_epilogue_adds_the_other_branch_gradient(dtype):
+    """Residual blocks: dx = (conv_transpose(dy, w) + addend) * (mask > 0) in one kernel."""
+    from distributed_b200.ops.conv import ConvDgradPlan
+    g = torch.Generator(device="cuda").manual_seed(17)
+    N, H, W, Ci, Co = 4, 28, 28, 256, 64
+    q = (lambda t: t.to(dtype).float())
+    x = torch.zeros((N, H, W, Ci), device="cuda", requires_grad=True)
+    w = q(torch.randn((1, 1, Ci, Co), device="cuda", generator=g) * 0.1)
+    dy = q(torch.randn((N, H, W, Co), device="cuda", generator=g))
+    addend = q(torch.randn((N, H, W, Ci), device="cuda", generator=g))
+    mask = q(torch.randn((N, H, W, Ci), device="cuda", generator=g))
+    _ref(x, w, None, 0).backward(dy)
+    ref = (x.grad + addend) * (mask > 0)
+    dx = torch.full(x.shape, float("nan"), device="cuda", dtype=dtype)
+    ConvDgradPlan(dy.to(dtype), w.to(dtype), dx, (0, 0), mask=mask.to(dtype), addend=addend.to(dtype)).run()
+    tol = (3e-3 if dtype == torch.float32 else 1e-2) * ref.abs().max().item()
+    assert (dx.float() - ref).abs().max().item() < tol
+    ConvDgradPlan(dy.to(dtype), w.to(dtype), dx, (0, 0), addend=addend.to(dtype)).run()
+    assert (dx.float() - (x.grad + addend)).abs().max().item() < tol

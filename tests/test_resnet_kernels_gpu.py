@@ -164,3 +164,32 @@ def test_im2col_bf16_matches_unfold():
     ref = ref.view(2, 3, 49, 100).permute(0, 3, 2, 1).reshape(200, 147)      # -> (kh, kw, ci) order
     assert torch.equal(col[:, :147], ref.to(torch.bfloat16))
     assert col[:, 147:].abs().max().item() == 0
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_batchnorm_with_residual_tail(dtype):
+    """y = relu(bn(x) + residual) in one kernel; its backward must not mask (dy arrives masked)."""
+    from distributed_b200.ops import nn
+    g = _g(21)
+    M, C, eps, mom = 3136, 256, 1e-3, 0.9
+    x = _q(torch.randn((M, C), device="cuda", generator=g) * 2 + 1, dtype).requires_grad_()
+    res = _q(torch.randn((M, C), device="cuda", generator=g), dtype)
+    gamma = (torch.rand(C, device="cuda", generator=g) + 0.5).requires_grad_()
+    beta = torch.randn(C, device="cuda", generator=g).requires_grad_()
+    pre = F.batch_norm(x, None, None, gamma, beta, training=True, eps=eps)
+    ref = torch.relu(pre + res)
+    stats, saved, red = (torch.zeros(2 * C, device="cuda") for _ in range(3))
+    xs = x.detach().to(dtype)
+    y, dx, dy_buf = torch.empty_like(xs), torch.empty_like(xs), torch.empty_like(xs)
+    dgamma, dbeta = torch.zeros(C, device="cuda"), torch.zeros(C, device="cuda")
+    bn = nn.BatchNorm(xs, y, gamma.detach(), beta.detach(), eps=eps, momentum=mom, relu=True, stats=stats, saved=saved,
+                      red=red, residual=res.to(dtype), dy2d=dy_buf, dx2d=dx, dgamma=dgamma, dbeta=dbeta)
+    bn.forward()
+    assert (y.float() - ref).abs().max().item() < 2 * _tol(dtype, ref)
+    dz = _q(torch.randn((M, C), device="cuda", generator=g), dtype)       # gradient of the pre-activation sum
+    dy_buf.copy_(dz)
+    pre.backward(dz)
+    bn.backward()
+    gtol = 1e-4 if dtype == torch.float32 else 2e-2
+    assert (dx.float() - x.grad).abs().max().item() < gtol * max(1.0, x.grad.abs().max().item())
+    assert torch.allclose(dgamma, gamma.grad, atol=(1e-3 if dtype == torch.float32 else 2e-2) * gamma.grad.abs().max().item())
