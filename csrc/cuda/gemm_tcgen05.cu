@@ -484,13 +484,28 @@ int encode_tmap_2d(CUtensorMap* tm, int dtype, const void* base, uint64_t inner,
   return B2D_OK;
 }
 
+// Latency-bound regime (convolution-sized GEMMs: a handful of k-blocks per tile, several waves of
+// tiles): what hides a CTA's serial prologue / epilogue is ANOTHER CTA on the same SM, not a deeper
+// ring, so the ring is cut until 2-3 CTAs fit in shared memory together.  B2D_GEMM_CORESIDENT=0 keeps
+// the one-CTA-per-SM deep-ring configuration everywhere (A/B switch).
+static bool coresident_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("B2D_GEMM_CORESIDENT");
+    return e == nullptr || e[0] != '0';
+  }();
+  return on;
+}
+constexpr int kShallowKBlocks = 64;   // K loops up to this many k-blocks count as latency-bound
+
 static int pick_block_n(const b2d_gemm_desc& d) {
   // A bf16 MN-major B tile is built from 64-element (128 B) atoms, so its minimum width is 64.
   if (d.N <= 32 && !(d.dtype == B2D_BF16 && d.b_mn_major)) return 32;
   if (d.N <= 64) return 64;
   const int mt = ceil_div(d.M, kBlockM);
   // Prefer the widest tile that still yields at least one full wave of CTAs (never wider than N).
-  if (d.N > 128 && mt * ceil_div(d.N, 256) >= 148) return 256;
+  const int kb = ceil_div(d.K, d.dtype == B2D_F32 ? 32 : 64);
+  const bool shallow = coresident_enabled() && kb <= kShallowKBlocks;
+  if (d.N > 128 && mt * ceil_div(d.N, 256) >= 148 && !shallow) return 256;
   if (mt * ceil_div(d.N, 128) >= 120) return 128;
   // Few tiles: narrower tiles double the CTA count and halve each CTA's epilogue.
   if (mt * ceil_div(d.N, 128) < 74) return 64;
@@ -528,6 +543,12 @@ static int resolve(const b2d_gemm_desc& d, b2d_gemm_geometry* g) {
   // shared-memory footprint small), never deeper than fits.
   const int per_cta = ceil_div(g->k_blocks, g->splits);
   g->stages = max(2, min(min(kMaxStages, kSmemBudget / stage_bytes), per_cta));
+  const int ctas = g->m_tiles * g->n_tiles * g->splits;
+  if (coresident_enabled() && ctas > 148 && g->k_blocks <= kShallowKBlocks && g->block_n <= 128) {
+    const int together = g->block_n <= 64 ? 3 : 2;
+    const int budget = (227 * 1024) / together - 1024 /*per-CTA reserve*/ - 1024 - 256;
+    g->stages = max(2, min(g->stages, budget / stage_bytes));
+  }
   g->smem_bytes = g->stages * stage_bytes + 1024 + 256;
   return B2D_OK;
 }
@@ -1096,19 +1117,29 @@ extern "C" int b2d_conv_wgrad_plan_create(const b2d_conv_desc* dp, b2d_conv_wgra
   WgradArgs& a = p->args;
   // Box height: smallest h making OW*h a multiple of the MMA K, scaled up towards ~96 pixels.
   const int h_unit = umma_k / gcd_int(OW, umma_k);
-  int ho_t = h_unit;
-  while (OW * (ho_t + h_unit) <= 96 && (ho_t + h_unit) * stride <= 256 && ho_t < OH) ho_t += h_unit;
+  const int block_n = d.Ci <= 32 && atom <= 32 ? 32 : (d.Ci <= 64 ? 64 : 128);
+  a.m_tiles = ceil_div(d.Co, kBlockM), a.n_tiles = ceil_div(d.Ci, block_n);
+  const int a_atoms = kBlockM / atom, b_atoms = block_n / atom;
+  // Pixel box per pipeline stage: ~96 pixels and a ring as deep as fits for one CTA per SM; ~64 pixels and a
+  // ring cut to half the shared memory when two CTAs are meant to share an SM (the grid below always aims at
+  // two CTAs per SM), provided that still leaves a ring of at least two stages.
+  int ho_t = 0, stage_bytes = 0;
+  for (int together = coresident_enabled() ? 1 : 0; together >= 0; --together) {
+    const int max_rows = together ? 64 : 96;
+    ho_t = h_unit;
+    while (OW * (ho_t + h_unit) <= max_rows && (ho_t + h_unit) * stride <= 256 && ho_t < OH) ho_t += h_unit;
+    stage_bytes = (a_atoms + b_atoms) * OW * ho_t * 128;
+    a.stages = max(1, min(4, kSmemBudget / stage_bytes));
+    if (together) a.stages = min(a.stages, (227 * 1024 / 2 - 1024 - 1024 - 256) / stage_bytes);
+    if (a.stages >= 2) break;
+  }
+  a.stages = max(1, a.stages);
   B2D_REQUIRE(ho_t * stride <= 256, "conv_wgrad: pixel box too tall for a strided TMA box");
   a.ho_t = ho_t, a.rows = OW * ho_t;
   a.tiles_h = ceil_div(OH, ho_t);
   a.tiles_total = d.N * a.tiles_h;
   a.Ci = d.Ci, a.Co = d.Co, a.KW = d.KW, a.pad_h = d.pad_h, a.pad_w = d.pad_w, a.stride = stride;
   a.dw = static_cast<float*>(const_cast<void*>(d.w));
-  const int block_n = d.Ci <= 32 && atom <= 32 ? 32 : (d.Ci <= 64 ? 64 : 128);
-  a.m_tiles = ceil_div(d.Co, kBlockM), a.n_tiles = ceil_div(d.Ci, block_n);
-  const int a_atoms = kBlockM / atom, b_atoms = block_n / atom;
-  const int stage_bytes = (a_atoms + b_atoms) * a.rows * 128;
-  a.stages = max(1, min(4, kSmemBudget / stage_bytes));
   if (stage_bytes > kSmemBudget) {
     set_error("conv_wgrad: pixel box of %d rows does not fit shared memory", a.rows);
     delete p;

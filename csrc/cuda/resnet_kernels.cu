@@ -546,7 +546,7 @@ __global__ void __launch_bounds__(256) gap_bwd_kernel(const float* __restrict__ 
 // path (a pixel is less than one 128-byte TMA row, e.g. the 3-channel stem of ResNet): the patch
 // matrix col[pixel][tap*Ci + ci] (row pitch kpad, padding columns zero) is materialised once per
 // step and feeds the tcgen05 GEMM core for the forward product (col . W) and the filter
-// gradient (col^T . dy).  One warp per output pixel.
+// gradient (col^T . dy).
 // ---------------------------------------------------------------------------------------
 struct PatchShape {
   int N, H, W, Ci, KH, KW, OH, OW, sh, sw, ph, pw;
@@ -555,30 +555,37 @@ struct PatchShape {
 template <typename TI, typename TO>
 __global__ void __launch_bounds__(256) im2col_kernel(const TI* __restrict__ x, TO* __restrict__ col, PatchShape s,
                                                       int kpad) {
+  // One thread = one 16-byte vector of one patch row: VO consecutive k = (kh, kw, ci) entries, walked with
+  // carries instead of a division per element; the loads of a vector are independent.
+  constexpr int VO = VecIO<TO>::N;
   pdl_wait();
   pdl_trigger();
   const int K = s.KH * s.KW * s.Ci;
-  const size_t npix = (size_t)s.N * s.OH * s.OW;
-  const int lane = threadIdx.x & 31;
-  const size_t warp0 = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5;
-  const size_t nwarps = ((size_t)gridDim.x * blockDim.x) >> 5;
-  for (size_t p = warp0; p < npix; p += nwarps) {
+  const int kv = kpad / VO;
+  const size_t total = (size_t)s.N * s.OH * s.OW * kv;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int k0 = (int)(i % kv) * VO;
+    const size_t p = i / kv;
     const int ow = p % s.OW;
     const int oh = (p / s.OW) % s.OH;
     const int n = (int)(p / ((size_t)s.OW * s.OH));
-    TO* row = col + p * kpad;
-    for (int k = lane; k < kpad; k += 32) {
-      float v = 0.f;
-      if (k < K) {
-        const int ci = k % s.Ci;
-        const int kw = (k / s.Ci) % s.KW;
-        const int kh = k / (s.Ci * s.KW);
-        const int ih = oh * s.sh - s.ph + kh, iw = ow * s.sw - s.pw + kw;
-        if (ih >= 0 && ih < s.H && iw >= 0 && iw < s.W)
-          v = load_scalar(x + (((size_t)n * s.H + ih) * s.W + iw) * s.Ci + ci);
+    const int ih0 = oh * s.sh - s.ph, iw0 = ow * s.sw - s.pw;
+    int ci = k0 % s.Ci;
+    int kw = (k0 / s.Ci) % s.KW;
+    int kh = k0 / (s.Ci * s.KW);
+    float v[VO];
+#pragma unroll
+    for (int j = 0; j < VO; ++j) {
+      const int ih = ih0 + kh, iw = iw0 + kw;
+      v[j] = 0.f;
+      if (k0 + j < K && ih >= 0 && ih < s.H && iw >= 0 && iw < s.W)
+        v[j] = load_scalar(x + (((size_t)n * s.H + ih) * s.W + iw) * s.Ci + ci);
+      if (++ci == s.Ci) {
+        ci = 0;
+        if (++kw == s.KW) kw = 0, ++kh;
       }
-      store_scalar(row + k, v);
     }
+    VecIO<TO>::store(col + p * kpad + k0, v);
   }
 }
 
@@ -820,7 +827,7 @@ extern "C" int b2d_im2col(int in_dtype, int out_dtype, const void* x, void* col,
               "im2col: kpad must be >= KH*KW*Ci and keep rows 16-byte aligned");
   const size_t npix = (size_t)N * s.OH * s.OW;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const dim3 grid(grid_1d(npix * 32));
+  const dim3 grid(grid_1d(npix * (kpad / vec_of(out_dtype))));
   if (in_dtype == B2D_F32 && out_dtype == B2D_F32)
     B2D_CUDA_CHECK(launch_pdl(im2col_kernel<float, float>, grid, dim3(256), 0, st, static_cast<const float*>(x),
                               static_cast<float*>(col), s, kpad));
