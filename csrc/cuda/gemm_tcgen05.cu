@@ -99,7 +99,7 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 __device__ __forceinline__ void epilogue_store4(const GemmArgs& a, int row, int col, float v0,
                                                 float v1, float v2, float v3) {
   if (a.bias != nullptr) {
-    const float4 b = *reinterpret_cast<const float4*>(a.bias + col);
+    const float4 b = __ldg(reinterpret_cast<const float4*>(a.bias + col));
     v0 += b.x, v1 += b.y, v2 += b.z, v3 += b.w;
   }
   if (a.flags & kFlagRelu) {
@@ -111,7 +111,7 @@ __device__ __forceinline__ void epilogue_store4(const GemmArgs& a, int row, int 
       v0 += __uint_as_float(t.x << 16), v1 += __uint_as_float(t.x & 0xffff0000u);
       v2 += __uint_as_float(t.y << 16), v3 += __uint_as_float(t.y & 0xffff0000u);
     } else {
-      const float4 t = *reinterpret_cast<const float4*>(static_cast<const float*>(a.addend) + (long long)row * a.ldd + col);
+      const float4 t = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(a.addend) + (long long)row * a.ldd + col));
       v0 += t.x, v1 += t.y, v2 += t.z, v3 += t.w;
     }
   }
@@ -123,7 +123,7 @@ __device__ __forceinline__ void epilogue_store4(const GemmArgs& a, int row, int 
       m = make_float4(__uint_as_float(t.x << 16), __uint_as_float(t.x & 0xffff0000u),
                       __uint_as_float(t.y << 16), __uint_as_float(t.y & 0xffff0000u));
     } else {
-      m = *reinterpret_cast<const float4*>(static_cast<const float*>(a.mask) + (long long)row * a.ldmask + col);
+      m = __ldg(reinterpret_cast<const float4*>(static_cast<const float*>(a.mask) + (long long)row * a.ldmask + col));
     }
     v0 = m.x > 0.f ? v0 : 0.f, v1 = m.y > 0.f ? v1 : 0.f;
     v2 = m.z > 0.f ? v2 : 0.f, v3 = m.w > 0.f ? v3 : 0.f;
@@ -204,7 +204,7 @@ struct GemmCfg {
 };
 
 template <MmaKind KIND, bool A_MN, bool B_MN, int BLOCK_N>
-__global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const __grid_constant__ GemmArgs args) {
+__global__ void __launch_bounds__(256, 2) gemm_tc_kernel(const __grid_constant__ GemmArgs args) {
   using Cfg = GemmCfg<KIND, A_MN, B_MN, BLOCK_N>;
   const int STAGES = args.stages;  // ring depth chosen on the host (<= Cfg::STAGES): short K loops
                                    // ask for little shared memory
@@ -353,13 +353,37 @@ __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const __grid_constant__
       row_ok = m < cv.rows_used && oh < cv.OH && n < cv.N_img;
       row = (n * cv.OH_full + oh * cv.out_step + cv.out_off_h) * cv.OW_full + w_i * cv.out_step + cv.out_off_w;
     }
-    mbar_wait(tmem_full_bar, 0);
-    tc_fence_after();
-    if (dbg != nullptr && threadIdx.x == 128) dbg[5] = gtime_ns();   // accumulator visible to the epilogue
     const bool finalize = (args.flags & kFlagFinalize) != 0;
     // bf16 output written directly (no split-K meeting, no accumulation): 16-byte stores
     const bool wide_bf16 = (args.flags & (kFlagOutBf16 | kFlagFinalize | kFlagAccumulate)) == kFlagOutBf16 &&
                            (args.ldd & 7) == 0 && (args.mask == nullptr || (args.ldmask & 7) == 0);
+    // Fast path of the bf16 networks: the epilogue operands that do NOT depend on the accumulator (the
+    // other branch's gradient, the ReLU mask) are fetched one 32-column chunk ahead — the first chunk
+    // while the main loop is still running — as read-only loads the compiler cannot serialise behind the
+    // stores to D.
+    const bool fast = wide_bf16 && row_ok && (args.mask == nullptr || (args.flags & kFlagMaskBf16));
+    const uint16_t* add_row =
+        args.addend == nullptr ? nullptr : static_cast<const uint16_t*>(args.addend) + (long long)row * args.ldd;
+    const uint16_t* mask_row =
+        args.mask == nullptr ? nullptr : static_cast<const uint16_t*>(args.mask) + (long long)row * args.ldmask;
+    uint4 pa[4], pm[4];
+    auto prefetch = [&](int c) {
+      const int col0 = n0 + c * 32;
+      if (fast && col0 + 32 <= args.N) {
+        if (add_row != nullptr) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) pa[g] = __ldg(reinterpret_cast<const uint4*>(add_row + col0) + g);
+        }
+        if (mask_row != nullptr) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) pm[g] = __ldg(reinterpret_cast<const uint4*>(mask_row + col0) + g);
+        }
+      }
+    };
+    prefetch(0);
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    if (dbg != nullptr && threadIdx.x == 128) dbg[5] = gtime_ns();   // accumulator visible to the epilogue
     // Each thread owns one accumulator row (TMEM lane) and stores 32 consecutive columns per chunk.
     // (A shared-memory transposed, fully coalesced variant measured the same latency on the small
     // GEMMs and 9% lower throughput at 8192^3, so the direct form stays.)
@@ -370,7 +394,46 @@ __global__ void __launch_bounds__(256, 1) gemm_tc_kernel(const __grid_constant__
       tmem_ld_wait();
       const int col0 = n0 + c * 32;
       if (row_ok) {
-        if (wide_bf16 && col0 + 32 <= args.N) {
+        if (fast && col0 + 32 <= args.N) {
+          uint4 o[4];
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            float f[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) f[k] = __uint_as_float(v[g * 8 + k]);
+            if (args.bias != nullptr) {
+              const float4 b0 = __ldg(reinterpret_cast<const float4*>(args.bias + col0 + g * 8));
+              const float4 b1 = __ldg(reinterpret_cast<const float4*>(args.bias + col0 + g * 8 + 4));
+              f[0] += b0.x, f[1] += b0.y, f[2] += b0.z, f[3] += b0.w;
+              f[4] += b1.x, f[5] += b1.y, f[6] += b1.z, f[7] += b1.w;
+            }
+            if (args.flags & kFlagRelu) {
+#pragma unroll
+              for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
+            }
+            if (add_row != nullptr) {
+              const uint32_t w[4] = {pa[g].x, pa[g].y, pa[g].z, pa[g].w};
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                f[2 * k] += __uint_as_float(w[k] << 16), f[2 * k + 1] += __uint_as_float(w[k] & 0xffff0000u);
+            }
+            if (mask_row != nullptr) {
+              const uint32_t w[4] = {pm[g].x, pm[g].y, pm[g].z, pm[g].w};
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                f[2 * k] = __uint_as_float(w[k] << 16) > 0.f ? f[2 * k] : 0.f;
+                f[2 * k + 1] = __uint_as_float(w[k] & 0xffff0000u) > 0.f ? f[2 * k + 1] : 0.f;
+              }
+            }
+            o[g].x = pack_bf16x2(f[0], f[1]), o[g].y = pack_bf16x2(f[2], f[3]);
+            o[g].z = pack_bf16x2(f[4], f[5]), o[g].w = pack_bf16x2(f[6], f[7]);
+          }
+          // operands of the next chunk: issued before this chunk's stores, in flight across the next TMEM load
+          if (c + 1 < BLOCK_N / 32) prefetch(c + 1);
+          uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(args.D) + (long long)row * args.ldd + col0);
+#pragma unroll
+          for (int g = 0; g < 4; ++g) dst[g] = o[g];
+        } else if (wide_bf16 && col0 + 32 <= args.N) {
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             float f[8];
@@ -545,7 +608,7 @@ static int resolve(const b2d_gemm_desc& d, b2d_gemm_geometry* g) {
   g->stages = max(2, min(min(kMaxStages, kSmemBudget / stage_bytes), per_cta));
   const int ctas = g->m_tiles * g->n_tiles * g->splits;
   if (coresident_enabled() && ctas > 148 && g->k_blocks <= kShallowKBlocks && g->block_n <= 128) {
-    const int together = g->block_n <= 64 ? 3 : 2;
+    const int together = 2;   // registers (<= 128 per thread) allow two CTAs per SM
     const int budget = (227 * 1024) / together - 1024 /*per-CTA reserve*/ - 1024 - 256;
     g->stages = max(2, min(g->stages, budget / stage_bytes));
   }
