@@ -74,6 +74,7 @@ struct GemmArgs {
   long long ldws;
   int M, N, K;
   int kb_total, kb_per_split, splits;
+  int m_tiles, n_tiles;   // tile grid (persistent CTAs walk m_tiles * n_tiles * splits tiles)
   int flags;
 };
 
@@ -96,6 +97,7 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 }
 
 // Applies bias / ReLU / mask to four consecutive columns of one row and stores them.
+template <bool OUT_BF16>
 __device__ __forceinline__ void epilogue_store4(const GemmArgs& a, int row, int col, float v0,
                                                 float v1, float v2, float v3) {
   if (a.bias != nullptr) {
@@ -106,7 +108,7 @@ __device__ __forceinline__ void epilogue_store4(const GemmArgs& a, int row, int 
     v0 = fmaxf(v0, 0.f), v1 = fmaxf(v1, 0.f), v2 = fmaxf(v2, 0.f), v3 = fmaxf(v3, 0.f);
   }
   if (a.addend != nullptr) {
-    if (a.flags & kFlagOutBf16) {
+    if (OUT_BF16 && (a.flags & kFlagOutBf16)) {
       const uint2 t = *reinterpret_cast<const uint2*>(static_cast<const uint16_t*>(a.addend) + (long long)row * a.ldd + col);
       v0 += __uint_as_float(t.x << 16), v1 += __uint_as_float(t.x & 0xffff0000u);
       v2 += __uint_as_float(t.y << 16), v3 += __uint_as_float(t.y & 0xffff0000u);
@@ -130,7 +132,7 @@ __device__ __forceinline__ void epilogue_store4(const GemmArgs& a, int row, int 
   }
   if (a.flags & kFlagAccumulate) {
     red_add_f4(reinterpret_cast<float*>(a.D) + (long long)row * a.ldd + col, v0, v1, v2, v3);
-  } else if (a.flags & kFlagOutBf16) {
+  } else if (OUT_BF16 && (a.flags & kFlagOutBf16)) {
     uint2 p;
     p.x = pack_bf16x2(v0, v1);
     p.y = pack_bf16x2(v2, v3);
@@ -203,45 +205,36 @@ struct GemmCfg {
       umma_idesc(KIND == MmaKind::TF32 ? 2u : 1u, A_MN ? 1u : 0u, B_MN ? 1u : 0u, kBlockM, BLOCK_N);
 };
 
-template <MmaKind KIND, bool A_MN, bool B_MN, int BLOCK_N>
+template <MmaKind KIND, bool A_MN, bool B_MN, int BLOCK_N, bool OUT_BF16>
 __global__ void __launch_bounds__(256, 2) gemm_tc_kernel(const __grid_constant__ GemmArgs args) {
+  // Persistent CTA: tiles (m, n, k-split) are walked with stride gridDim.x.  The accumulator is
+  // double-buffered in tensor memory, so the epilogue warps drain tile t while the MMA thread is already
+  // filling tile t+1, and the TMA producer runs ahead across tile boundaries: the per-CTA prologue is paid
+  // once per SM and the epilogue of every tile but the last is hidden.
   using Cfg = GemmCfg<KIND, A_MN, B_MN, BLOCK_N>;
-  const int STAGES = args.stages;  // ring depth chosen on the host (<= Cfg::STAGES): short K loops
-                                   // ask for little shared memory
+  const int STAGES = args.stages;  // ring depth chosen on the host (<= Cfg::STAGES)
   constexpr int STAGE_BYTES = Cfg::STAGE_BYTES;
   constexpr int BLOCK_K = Cfg::BLOCK_K;
+  constexpr uint32_t ACC_COLS = Cfg::TMEM_COLS;      // one accumulator
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
   uint64_t* empty_bar = full_bar + STAGES;
-  uint64_t* tmem_full_bar = empty_bar + STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+  uint64_t* tmem_full_bar = empty_bar + STAGES;      // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;      // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
   int* last_flag = reinterpret_cast<int*>(tmem_slot + 1);
 
   const int warp = threadIdx.x >> 5;  // warp-uniform
   const int lane = threadIdx.x & 31;
-  long long* dbg = args.dbg == nullptr
-                       ? nullptr
-                       : args.dbg + 16 * (blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z));
+  long long* dbg = args.dbg == nullptr ? nullptr : args.dbg + 16 * blockIdx.x;
   if (dbg != nullptr && threadIdx.x == 0) dbg[0] = gtime_ns();
-  const int m0 = blockIdx.x * kBlockM;
-  const int n0 = blockIdx.y * BLOCK_N;
-  const int kb_begin = blockIdx.z * args.kb_per_split;
-  const int kb_end = min(args.kb_total, kb_begin + args.kb_per_split);
-  const int num_kb = kb_end - kb_begin;  // >= 1 by construction on the host
-  // convolution view: first image / first output row of this M tile
   const ConvGeom& cv = args.cv;
-  int cv_n0 = 0, cv_oh0 = 0;
-  if (cv.enabled) {
-    if (cv.n_t == 1) {
-      cv_n0 = blockIdx.x / cv.tiles_h;
-      cv_oh0 = (blockIdx.x % cv.tiles_h) * cv.ho_t;
-    } else {
-      cv_n0 = blockIdx.x * cv.n_t;
-    }
-  }
+  const int total_tiles = args.m_tiles * args.n_tiles * args.splits;
+  // two accumulators only when this CTA walks more than one tile (a one-tile CTA has nothing to overlap)
+  const uint32_t tmem_cols = total_tiles > static_cast<int>(gridDim.x) ? 2 * ACC_COLS : ACC_COLS;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&args.tmA);
@@ -252,10 +245,13 @@ __global__ void __launch_bounds__(256, 2) gemm_tc_kernel(const __grid_constant__
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
     }
-    mbar_init(tmem_full_bar, 1);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tmem_full_bar[b], 1);
+      mbar_init(&tmem_empty_bar[b], 4);   // one arrival per epilogue warp
+    }
     fence_mbar_init();
   }
-  if (warp == 2) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
+  if (warp == 2) tmem_alloc_dyn(tmem_slot, tmem_cols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -267,232 +263,290 @@ __global__ void __launch_bounds__(256, 2) gemm_tc_kernel(const __grid_constant__
   pdl_trigger();
   if (dbg != nullptr && threadIdx.x == 0) dbg[2] = gtime_ns();   // upstream kernel complete
 
+  // tile id -> (m tile, n tile, k split): n fastest, so that neighbouring CTAs share the A tile in L2
+  auto decode = [&](int tile, int& mt, int& nt, int& kb_begin, int& num_kb) {
+    nt = tile % args.n_tiles;
+    const int r = tile / args.n_tiles;
+    mt = r % args.m_tiles;
+    const int z = r / args.m_tiles;
+    kb_begin = z * args.kb_per_split;
+    num_kb = min(args.kb_total, kb_begin + args.kb_per_split) - kb_begin;   // >= 1 by construction
+  };
+  // convolution view: first image / first output row of an M tile
+  auto conv_origin = [&](int mt, int& cv_n0, int& cv_oh0) {
+    cv_n0 = 0, cv_oh0 = 0;
+    if (cv.enabled) {
+      if (cv.n_t == 1) {
+        cv_n0 = mt / cv.tiles_h;
+        cv_oh0 = (mt % cv.tiles_h) * cv.ho_t;
+      } else {
+        cv_n0 = mt * cv.n_t;
+      }
+    }
+  };
+
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0) {
-      for (int i = 0; i < num_kb; ++i) {
-        const int stage = i % STAGES;
-        const uint32_t phase = (i / STAGES) & 1;
-        mbar_wait(&empty_bar[stage], phase ^ 1);
-        uint8_t* sa = smem + stage * STAGE_BYTES;
-        uint8_t* sb = sa + kABytes;
-        const int kb = kb_begin + i;
-        const int k0 = kb * BLOCK_K;
-        int tap = 0, cc = 0;
-        if (cv.enabled) tap = kb / cv.c_chunks, cc = kb - tap * cv.c_chunks;
-        mbar_expect_tx(&full_bar[stage], cv.enabled ? cv.rows_used * 128 + Cfg::B_BYTES : STAGE_BYTES);
-        if constexpr (!A_MN) {
-          if (cv.enabled) {
-            const int r = tap / cv.kw, sx = tap - r * cv.kw;
-            tma_load_4d(sa, &args.tmA, &full_bar[stage], cc * BLOCK_K, cv.w_base + cv.tap_sign * sx,
-                        cv_oh0 * cv.stride + cv.h_base + cv.tap_sign * r, cv_n0);
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        int mt, nt, kb_begin, num_kb, cv_n0, cv_oh0;
+        decode(tile, mt, nt, kb_begin, num_kb);
+        conv_origin(mt, cv_n0, cv_oh0);
+        const int m0 = mt * kBlockM, n0 = nt * BLOCK_N;
+        for (int i = 0; i < num_kb; ++i, ++it) {
+          const int stage = it % STAGES;
+          const uint32_t phase = (it / STAGES) & 1;
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * STAGE_BYTES;
+          uint8_t* sb = sa + kABytes;
+          const int kb = kb_begin + i;
+          const int k0 = kb * BLOCK_K;
+          int tap = 0, cc = 0;
+          if (cv.enabled) tap = kb / cv.c_chunks, cc = kb - tap * cv.c_chunks;
+          mbar_expect_tx(&full_bar[stage], cv.enabled ? cv.rows_used * 128 + Cfg::B_BYTES : STAGE_BYTES);
+          if constexpr (!A_MN) {
+            if (cv.enabled) {
+              const int r = tap / cv.kw, sx = tap - r * cv.kw;
+              tma_load_4d(sa, &args.tmA, &full_bar[stage], cc * BLOCK_K, cv.w_base + cv.tap_sign * sx,
+                          cv_oh0 * cv.stride + cv.h_base + cv.tap_sign * r, cv_n0);
+            } else {
+              tma_load_2d(sa, &args.tmA, &full_bar[stage], k0, m0);
+            }
           } else {
-            tma_load_2d(sa, &args.tmA, &full_bar[stage], k0, m0);
-          }
-        } else {
 #pragma unroll
-          for (int a = 0; a < kBlockM / Cfg::ATOM_E; ++a)
-            tma_load_2d(sa + a * (BLOCK_K * 128), &args.tmA, &full_bar[stage], m0 + a * Cfg::ATOM_E,
-                        k0);
-        }
-        if constexpr (!B_MN) {
-          if (cv.enabled) {  // dgrad: weights [taps * C_in rows][C_out], K = C_out chunk of this tap
-            const int tr = tap / cv.kw, ts = tap - tr * cv.kw;
-            const int tap_full = (cv.tap_r0 + cv.tap_step * tr) * cv.kw_full + cv.tap_s0 + cv.tap_step * ts;
-            tma_load_2d(sb, &args.tmB, &full_bar[stage], cc * BLOCK_K, tap_full * cv.b_rows_per_tap + n0);
+            for (int a = 0; a < kBlockM / Cfg::ATOM_E; ++a)
+              tma_load_2d(sa + a * (BLOCK_K * 128), &args.tmA, &full_bar[stage], m0 + a * Cfg::ATOM_E, k0);
           }
-          else
-            tma_load_2d(sb, &args.tmB, &full_bar[stage], k0, n0);
-        } else {
+          if constexpr (!B_MN) {
+            if (cv.enabled) {  // dgrad: weights [taps * C_in rows][C_out], K = C_out chunk of this tap
+              const int tr = tap / cv.kw, ts = tap - tr * cv.kw;
+              const int tap_full = (cv.tap_r0 + cv.tap_step * tr) * cv.kw_full + cv.tap_s0 + cv.tap_step * ts;
+              tma_load_2d(sb, &args.tmB, &full_bar[stage], cc * BLOCK_K, tap_full * cv.b_rows_per_tap + n0);
+            } else {
+              tma_load_2d(sb, &args.tmB, &full_bar[stage], k0, n0);
+            }
+          } else {
 #pragma unroll
-          for (int a = 0; a < (BLOCK_N + Cfg::ATOM_E - 1) / Cfg::ATOM_E; ++a)
-            tma_load_2d(sb + a * (BLOCK_K * 128), &args.tmB, &full_bar[stage], n0 + a * Cfg::ATOM_E,
-                        k0);
+            for (int a = 0; a < (BLOCK_N + Cfg::ATOM_E - 1) / Cfg::ATOM_E; ++a)
+              tma_load_2d(sb + a * (BLOCK_K * 128), &args.tmB, &full_bar[stage], n0 + a * Cfg::ATOM_E, k0);
+          }
         }
       }
     }
   } else if (warp == 1) {
     // ===== MMA issuer (single thread) =====
     if (lane == 0) {
-      for (int i = 0; i < num_kb; ++i) {
-        const int stage = i % STAGES;
-        const uint32_t phase = (i / STAGES) & 1;
-        mbar_wait(&full_bar[stage], phase);
+      uint32_t it = 0, t = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++t) {
+        int mt, nt, kb_begin, num_kb;
+        decode(tile, mt, nt, kb_begin, num_kb);
+        const uint32_t buf = t & 1;
+        mbar_wait(&tmem_empty_bar[buf], ((t >> 1) & 1) ^ 1);   // epilogue has drained this accumulator
         tc_fence_after();
-        if (dbg != nullptr && i == 0) dbg[3] = gtime_ns();           // first tiles landed
-        const uint32_t a_base = smem_u32(smem + stage * STAGE_BYTES);
-        const uint32_t b_base = a_base + kABytes;
+        const uint32_t acc = tmem_base + buf * ACC_COLS;
+        for (int i = 0; i < num_kb; ++i, ++it) {
+          const int stage = it % STAGES;
+          const uint32_t phase = (it / STAGES) & 1;
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          if (dbg != nullptr && it == 0) dbg[3] = gtime_ns();           // first tiles landed
+          const uint32_t a_base = smem_u32(smem + stage * STAGE_BYTES);
+          const uint32_t b_base = a_base + kABytes;
 #pragma unroll
-        for (int j = 0; j < BLOCK_K / Cfg::UMMA_K; ++j) {
-          // K-major: step 32 B inside the 128 B swizzled row; 8-row groups are 1024 B apart.
-          // MN-major: step UMMA_K rows (whole swizzle atoms); LBO = distance between the
-          // 128 B-wide MN atoms (one TMA box each), SBO = one atom of K rows (8, or 4 for tf32).
-          const uint64_t da = A_MN ? umma_smem_desc_sw128(a_base + j * Cfg::UMMA_K * 128,
-                                                          BLOCK_K * 128, Cfg::MN_SBO, Cfg::MN_LAYOUT)
-                                   : umma_smem_desc_sw128(a_base + j * 32, 16, 1024);
-          const uint64_t db = B_MN ? umma_smem_desc_sw128(b_base + j * Cfg::UMMA_K * 128,
-                                                          BLOCK_K * 128, Cfg::MN_SBO, Cfg::MN_LAYOUT)
-                                   : umma_smem_desc_sw128(b_base + j * 32, 16, 1024);
-          tc_mma<KIND>(tmem_base, da, db, Cfg::IDESC, (i | j) != 0 ? 1u : 0u);
+          for (int j = 0; j < BLOCK_K / Cfg::UMMA_K; ++j) {
+            // K-major: step 32 B inside the 128 B swizzled row; 8-row groups are 1024 B apart.
+            // MN-major: step UMMA_K rows (whole swizzle atoms); LBO = distance between the
+            // 128 B-wide MN atoms (one TMA box each), SBO = one atom of K rows (8, or 4 for tf32).
+            const uint64_t da = A_MN ? umma_smem_desc_sw128(a_base + j * Cfg::UMMA_K * 128,
+                                                            BLOCK_K * 128, Cfg::MN_SBO, Cfg::MN_LAYOUT)
+                                     : umma_smem_desc_sw128(a_base + j * 32, 16, 1024);
+            const uint64_t db = B_MN ? umma_smem_desc_sw128(b_base + j * Cfg::UMMA_K * 128,
+                                                            BLOCK_K * 128, Cfg::MN_SBO, Cfg::MN_LAYOUT)
+                                     : umma_smem_desc_sw128(b_base + j * 32, 16, 1024);
+            tc_mma<KIND>(acc, da, db, Cfg::IDESC, (i | j) != 0 ? 1u : 0u);
+          }
+          tc_commit(&empty_bar[stage]);  // frees this ring slot once the MMAs above retire
         }
-        tc_commit(&empty_bar[stage]);  // frees this ring slot once the MMAs above retire
+        tc_commit(&tmem_full_bar[buf]);  // accumulator complete
+        if (dbg != nullptr && t == 0) dbg[4] = gtime_ns();             // all MMAs of the first tile issued
       }
-      tc_commit(tmem_full_bar);  // accumulator complete
-      if (dbg != nullptr) dbg[4] = gtime_ns();                       // all MMAs issued
     }
   } else if (warp >= 4) {
     // ===== epilogue: 4 warps, warp q owns TMEM lanes [32q, 32q+32) =====
     const int q = warp - 4;
-    int row = m0 + q * 32 + lane;
-    bool row_ok = row < args.M;
-    if (cv.enabled) {  // tile-local pixel index -> (image, out row, out column) -> output matrix row
-      const int m = q * 32 + lane;
-      const int w_i = m % cv.wo_t, t = m / cv.wo_t;
-      const int h_i = t % cv.ho_t, n_i = t / cv.ho_t;
-      const int oh = cv_oh0 + h_i, n = cv_n0 + n_i;
-      row_ok = m < cv.rows_used && oh < cv.OH && n < cv.N_img;
-      row = (n * cv.OH_full + oh * cv.out_step + cv.out_off_h) * cv.OW_full + w_i * cv.out_step + cv.out_off_w;
-    }
     const bool finalize = (args.flags & kFlagFinalize) != 0;
     // bf16 output written directly (no split-K meeting, no accumulation): 16-byte stores
-    const bool wide_bf16 = (args.flags & (kFlagOutBf16 | kFlagFinalize | kFlagAccumulate)) == kFlagOutBf16 &&
+    const bool wide_bf16 = OUT_BF16 &&
+                           (args.flags & (kFlagOutBf16 | kFlagFinalize | kFlagAccumulate)) == kFlagOutBf16 &&
                            (args.ldd & 7) == 0 && (args.mask == nullptr || (args.ldmask & 7) == 0);
-    // Fast path of the bf16 networks: the epilogue operands that do NOT depend on the accumulator (the
-    // other branch's gradient, the ReLU mask) are fetched one 32-column chunk ahead — the first chunk
-    // while the main loop is still running — as read-only loads the compiler cannot serialise behind the
-    // stores to D.
-    const bool fast = wide_bf16 && row_ok && (args.mask == nullptr || (args.flags & kFlagMaskBf16));
-    const uint16_t* add_row =
-        args.addend == nullptr ? nullptr : static_cast<const uint16_t*>(args.addend) + (long long)row * args.ldd;
-    const uint16_t* mask_row =
-        args.mask == nullptr ? nullptr : static_cast<const uint16_t*>(args.mask) + (long long)row * args.ldmask;
-    uint4 pa[4], pm[4];
-    auto prefetch = [&](int c) {
-      const int col0 = n0 + c * 32;
-      if (fast && col0 + 32 <= args.N) {
-        if (add_row != nullptr) {
-#pragma unroll
-          for (int g = 0; g < 4; ++g) pa[g] = __ldg(reinterpret_cast<const uint4*>(add_row + col0) + g);
-        }
-        if (mask_row != nullptr) {
-#pragma unroll
-          for (int g = 0; g < 4; ++g) pm[g] = __ldg(reinterpret_cast<const uint4*>(mask_row + col0) + g);
-        }
+    uint32_t t = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++t) {
+      int mt, nt, kb_begin, num_kb, cv_n0, cv_oh0;
+      decode(tile, mt, nt, kb_begin, num_kb);
+      conv_origin(mt, cv_n0, cv_oh0);
+      const int m0 = mt * kBlockM, n0 = nt * BLOCK_N;
+      const uint32_t buf = t & 1;
+      int row = m0 + q * 32 + lane;
+      bool row_ok = row < args.M;
+      if (cv.enabled) {  // tile-local pixel index -> (image, out row, out column) -> output matrix row
+        const int m = q * 32 + lane;
+        const int w_i = m % cv.wo_t, tt = m / cv.wo_t;
+        const int h_i = tt % cv.ho_t, n_i = tt / cv.ho_t;
+        const int oh = cv_oh0 + h_i, n = cv_n0 + n_i;
+        row_ok = m < cv.rows_used && oh < cv.OH && n < cv.N_img;
+        row = (n * cv.OH_full + oh * cv.out_step + cv.out_off_h) * cv.OW_full + w_i * cv.out_step + cv.out_off_w;
       }
-    };
-    prefetch(0);
-    mbar_wait(tmem_full_bar, 0);
-    tc_fence_after();
-    if (dbg != nullptr && threadIdx.x == 128) dbg[5] = gtime_ns();   // accumulator visible to the epilogue
-    // Each thread owns one accumulator row (TMEM lane) and stores 32 consecutive columns per chunk.
-    // (A shared-memory transposed, fully coalesced variant measured the same latency on the small
-    // GEMMs and 9% lower throughput at 8192^3, so the direct form stays.)
-#pragma unroll 1
-    for (int c = 0; c < BLOCK_N / 32; ++c) {
-      uint32_t v[32];
-      tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c * 32, v);
-      tmem_ld_wait();
-      const int col0 = n0 + c * 32;
-      if (row_ok) {
+      // Fast path of the bf16 networks: the epilogue operands that do NOT depend on the accumulator (the
+      // other branch's gradient, the ReLU mask) are fetched one 32-column chunk ahead — the first chunk
+      // while the main loop is still running — as read-only loads the compiler cannot serialise behind the
+      // stores to D.
+      const bool fast = wide_bf16 && row_ok && (args.mask == nullptr || (args.flags & kFlagMaskBf16));
+      const uint16_t* add_row =
+          args.addend == nullptr ? nullptr : static_cast<const uint16_t*>(args.addend) + (long long)row * args.ldd;
+      const uint16_t* mask_row =
+          args.mask == nullptr ? nullptr : static_cast<const uint16_t*>(args.mask) + (long long)row * args.ldmask;
+      uint4 pa[4], pm[4];
+      auto prefetch = [&](int c) {
+        const int col0 = n0 + c * 32;
         if (fast && col0 + 32 <= args.N) {
-          uint4 o[4];
+          if (add_row != nullptr) {
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            float f[8];
+            for (int g = 0; g < 4; ++g) pa[g] = __ldg(reinterpret_cast<const uint4*>(add_row + col0) + g);
+          }
+          if (mask_row != nullptr) {
 #pragma unroll
-            for (int k = 0; k < 8; ++k) f[k] = __uint_as_float(v[g * 8 + k]);
-            if (args.bias != nullptr) {
-              const float4 b0 = __ldg(reinterpret_cast<const float4*>(args.bias + col0 + g * 8));
-              const float4 b1 = __ldg(reinterpret_cast<const float4*>(args.bias + col0 + g * 8 + 4));
-              f[0] += b0.x, f[1] += b0.y, f[2] += b0.z, f[3] += b0.w;
-              f[4] += b1.x, f[5] += b1.y, f[6] += b1.z, f[7] += b1.w;
-            }
-            if (args.flags & kFlagRelu) {
+            for (int g = 0; g < 4; ++g) pm[g] = __ldg(reinterpret_cast<const uint4*>(mask_row + col0) + g);
+          }
+        }
+      };
+      if constexpr (OUT_BF16) prefetch(0);
+      mbar_wait(&tmem_full_bar[buf], (t >> 1) & 1);
+      tc_fence_after();
+      if (dbg != nullptr && threadIdx.x == 128 && t == 0) dbg[5] = gtime_ns();   // accumulator visible
+      const uint32_t acc = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * ACC_COLS;
+      // Each thread owns one accumulator row (TMEM lane) and stores 32 consecutive columns per chunk.
+      // (A shared-memory transposed, fully coalesced variant measured the same latency on the small
+      // GEMMs and 9% lower throughput at 8192^3, so the direct form stays.)
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(acc + c * 32, v);
+        tmem_ld_wait();
+        if (c == BLOCK_N / 32 - 1) {
+          // the accumulator now lives in registers: hand the TMEM buffer back to the MMA thread
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);
+        }
+        const int col0 = n0 + c * 32;
+        if (row_ok) {
+          bool done = false;
+          if constexpr (OUT_BF16) {
+            if (fast && col0 + 32 <= args.N) {
+              done = true;
+              uint4 o[4];
 #pragma unroll
-              for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
-            }
-            if (add_row != nullptr) {
-              const uint32_t w[4] = {pa[g].x, pa[g].y, pa[g].z, pa[g].w};
+              for (int g = 0; g < 4; ++g) {
+                float f[8];
 #pragma unroll
-              for (int k = 0; k < 4; ++k)
-                f[2 * k] += __uint_as_float(w[k] << 16), f[2 * k + 1] += __uint_as_float(w[k] & 0xffff0000u);
-            }
-            if (mask_row != nullptr) {
-              const uint32_t w[4] = {pm[g].x, pm[g].y, pm[g].z, pm[g].w};
+                for (int k = 0; k < 8; ++k) f[k] = __uint_as_float(v[g * 8 + k]);
+                if (args.bias != nullptr) {
+                  const float4 b0 = __ldg(reinterpret_cast<const float4*>(args.bias + col0 + g * 8));
+                  const float4 b1 = __ldg(reinterpret_cast<const float4*>(args.bias + col0 + g * 8 + 4));
+                  f[0] += b0.x, f[1] += b0.y, f[2] += b0.z, f[3] += b0.w;
+                  f[4] += b1.x, f[5] += b1.y, f[6] += b1.z, f[7] += b1.w;
+                }
+                if (args.flags & kFlagRelu) {
 #pragma unroll
-              for (int k = 0; k < 4; ++k) {
-                f[2 * k] = __uint_as_float(w[k] << 16) > 0.f ? f[2 * k] : 0.f;
-                f[2 * k + 1] = __uint_as_float(w[k] & 0xffff0000u) > 0.f ? f[2 * k + 1] : 0.f;
+                  for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
+                }
+                if (add_row != nullptr) {
+                  const uint32_t w[4] = {pa[g].x, pa[g].y, pa[g].z, pa[g].w};
+#pragma unroll
+                  for (int k = 0; k < 4; ++k)
+                    f[2 * k] += __uint_as_float(w[k] << 16), f[2 * k + 1] += __uint_as_float(w[k] & 0xffff0000u);
+                }
+                if (mask_row != nullptr) {
+                  const uint32_t w[4] = {pm[g].x, pm[g].y, pm[g].z, pm[g].w};
+#pragma unroll
+                  for (int k = 0; k < 4; ++k) {
+                    f[2 * k] = __uint_as_float(w[k] << 16) > 0.f ? f[2 * k] : 0.f;
+                    f[2 * k + 1] = __uint_as_float(w[k] & 0xffff0000u) > 0.f ? f[2 * k + 1] : 0.f;
+                  }
+                }
+                o[g].x = pack_bf16x2(f[0], f[1]), o[g].y = pack_bf16x2(f[2], f[3]);
+                o[g].z = pack_bf16x2(f[4], f[5]), o[g].w = pack_bf16x2(f[6], f[7]);
+              }
+              // operands of the next chunk: issued before this chunk's stores, in flight across the next TMEM load
+              if (c + 1 < BLOCK_N / 32) prefetch(c + 1);
+              uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(args.D) + (long long)row * args.ldd + col0);
+#pragma unroll
+              for (int g = 0; g < 4; ++g) dst[g] = o[g];
+            } else if (wide_bf16 && col0 + 32 <= args.N) {
+              done = true;
+#pragma unroll
+              for (int g = 0; g < 4; ++g) {
+                float f[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) f[k] = __uint_as_float(v[g * 8 + k]);
+                epilogue_store8_bf16(args, row, col0 + g * 8, f);
               }
             }
-            o[g].x = pack_bf16x2(f[0], f[1]), o[g].y = pack_bf16x2(f[2], f[3]);
-            o[g].z = pack_bf16x2(f[4], f[5]), o[g].w = pack_bf16x2(f[6], f[7]);
           }
-          // operands of the next chunk: issued before this chunk's stores, in flight across the next TMEM load
-          if (c + 1 < BLOCK_N / 32) prefetch(c + 1);
-          uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(args.D) + (long long)row * args.ldd + col0);
+          if (!done) {
 #pragma unroll
-          for (int g = 0; g < 4; ++g) dst[g] = o[g];
-        } else if (wide_bf16 && col0 + 32 <= args.N) {
-#pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            float f[8];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) f[k] = __uint_as_float(v[g * 8 + k]);
-            epilogue_store8_bf16(args, row, col0 + g * 8, f);
-          }
-        } else {
-#pragma unroll
-          for (int g = 0; g < 8; ++g) {
-            const int col = col0 + g * 4;
-            if (col < args.N) {
-              const float f0 = __uint_as_float(v[g * 4 + 0]), f1 = __uint_as_float(v[g * 4 + 1]);
-              const float f2 = __uint_as_float(v[g * 4 + 2]), f3 = __uint_as_float(v[g * 4 + 3]);
-              if (finalize)
-                red_add_f4(args.ws + (long long)row * args.ldws + col, f0, f1, f2, f3);
-              else
-                epilogue_store4(args, row, col, f0, f1, f2, f3);
+            for (int g = 0; g < 8; ++g) {
+              const int col = col0 + g * 4;
+              if (col < args.N) {
+                const float f0 = __uint_as_float(v[g * 4 + 0]), f1 = __uint_as_float(v[g * 4 + 1]);
+                const float f2 = __uint_as_float(v[g * 4 + 2]), f3 = __uint_as_float(v[g * 4 + 3]);
+                if (finalize)
+                  red_add_f4(args.ws + (long long)row * args.ldws + col, f0, f1, f2, f3);
+                else
+                  epilogue_store4<OUT_BF16>(args, row, col, f0, f1, f2, f3);
+              }
             }
           }
         }
       }
-    }
-    if (finalize) {
-      // Split-K rendezvous: the CTA that bumps the tile counter last owns the epilogue.
-      const int et = threadIdx.x - 128;
-      __threadfence();
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (et == 0) {
-        const uint32_t tile = blockIdx.y * gridDim.x + blockIdx.x;
-        const uint32_t old = atomicAdd(&args.counters[tile], 1u);
-        *last_flag = (old == static_cast<uint32_t>(args.splits) - 1u) ? 1 : 0;
-        if (*last_flag) args.counters[tile] = 0;  // self-cleaning for the next launch
-      }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (*last_flag) {
+      if (finalize) {
+        // Split-K rendezvous: the CTA that bumps the tile counter last owns the epilogue.
+        const int et = threadIdx.x - 128;
         __threadfence();
-        // Only rows < M exist; batch the L2 reads (4 independent float4 per thread in flight)
-        // instead of a load -> store -> load chain.
-        constexpr int C4 = BLOCK_N / 4;
-        const int rows = min(kBlockM, args.M - m0);
-        const int total = rows * C4;
-        for (int base = et; base < total; base += 128 * 4) {
-          float4 v[4];
-          int rr[4], cc[4];
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (et == 0) {
+          const uint32_t ctr = nt * args.m_tiles + mt;
+          const uint32_t old = atomicAdd(&args.counters[ctr], 1u);
+          *last_flag = (old == static_cast<uint32_t>(args.splits) - 1u) ? 1 : 0;
+          if (*last_flag) args.counters[ctr] = 0;  // self-cleaning for the next launch
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (*last_flag) {
+          __threadfence();
+          // Only rows < M exist; batch the L2 reads (4 independent float4 per thread in flight)
+          // instead of a load -> store -> load chain.
+          constexpr int C4 = BLOCK_N / 4;
+          const int rows = min(kBlockM, args.M - m0);
+          const int total = rows * C4;
+          for (int base = et; base < total; base += 128 * 4) {
+            float4 v[4];
+            int rr[4], cc[4];
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            const int idx = base + u * 128;
-            rr[u] = m0 + idx / C4, cc[u] = n0 + (idx % C4) * 4;
-            if (idx < total && cc[u] < args.N)
-              v[u] = __ldcg(reinterpret_cast<const float4*>(args.ws + (long long)rr[u] * args.ldws + cc[u]));
-          }
+            for (int u = 0; u < 4; ++u) {
+              const int idx = base + u * 128;
+              rr[u] = m0 + idx / C4, cc[u] = n0 + (idx % C4) * 4;
+              if (idx < total && cc[u] < args.N)
+                v[u] = __ldcg(reinterpret_cast<const float4*>(args.ws + (long long)rr[u] * args.ldws + cc[u]));
+            }
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            const int idx = base + u * 128;
-            if (idx < total && cc[u] < args.N) {
-              __stcg(reinterpret_cast<float4*>(args.ws + (long long)rr[u] * args.ldws + cc[u]),
-                     make_float4(0.f, 0.f, 0.f, 0.f));
-              epilogue_store4(args, rr[u], cc[u], v[u].x, v[u].y, v[u].z, v[u].w);
+            for (int u = 0; u < 4; ++u) {
+              const int idx = base + u * 128;
+              if (idx < total && cc[u] < args.N) {
+                __stcg(reinterpret_cast<float4*>(args.ws + (long long)rr[u] * args.ldws + cc[u]),
+                       make_float4(0.f, 0.f, 0.f, 0.f));
+                epilogue_store4<OUT_BF16>(args, rr[u], cc[u], v[u].x, v[u].y, v[u].z, v[u].w);
+              }
             }
           }
         }
@@ -503,7 +557,7 @@ __global__ void __launch_bounds__(256, 2) gemm_tc_kernel(const __grid_constant__
   if (dbg != nullptr && threadIdx.x == 128) dbg[6] = gtime_ns();     // epilogue done
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+  if (warp == 2) tmem_dealloc_dyn(tmem_base, tmem_cols);
   if (dbg != nullptr && threadIdx.x == 0) dbg[7] = gtime_ns();
 }
 
@@ -626,36 +680,56 @@ struct b2d_gemm_plan {
   void (*kernel)(const GemmArgs);
   int smem_bytes;     // maximum the kernel instantiation may ask for (function attribute)
   int launch_smem;    // what this plan actually launches with (ring depth of this problem)
+  int grid;           // persistent CTAs: min(tiles, SMs x CTAs that fit an SM together)
 };
 
-template <MmaKind KIND, bool A_MN, bool B_MN>
+// Last step of every plan constructor: publish the tile grid to the kernel and size the launch.
+static void finish_plan(b2d_gemm_plan* p) {
+  GemmArgs& a = p->args;
+  a.m_tiles = p->geo.m_tiles, a.n_tiles = p->geo.n_tiles;
+  const int total = a.m_tiles * a.n_tiles * a.splits;
+  const int acc_cols = p->geo.block_n < 32 ? 32 : p->geo.block_n;
+  // two CTAs share an SM when both their shared memory and their (double-buffered) accumulators fit
+  const bool two = p->launch_smem + 1024 <= (227 * 1024) / 2 && 2 * (2 * acc_cols) <= 512;
+  p->grid = min(total, 148 * (two ? 2 : 1));
+}
+
+template <MmaKind KIND, bool A_MN, bool B_MN, bool OUT_BF16>
 static void select_n(int block_n, void (**k)(const GemmArgs), int* smem) {
   switch (block_n) {
     case 32:
-      *k = gemm_tc_kernel<KIND, A_MN, B_MN, 32>;
+      *k = gemm_tc_kernel<KIND, A_MN, B_MN, 32, OUT_BF16>;
       *smem = GemmCfg<KIND, A_MN, B_MN, 32>::SMEM_BYTES;
       break;
     case 64:
-      *k = gemm_tc_kernel<KIND, A_MN, B_MN, 64>;
+      *k = gemm_tc_kernel<KIND, A_MN, B_MN, 64, OUT_BF16>;
       *smem = GemmCfg<KIND, A_MN, B_MN, 64>::SMEM_BYTES;
       break;
     case 128:
-      *k = gemm_tc_kernel<KIND, A_MN, B_MN, 128>;
+      *k = gemm_tc_kernel<KIND, A_MN, B_MN, 128, OUT_BF16>;
       *smem = GemmCfg<KIND, A_MN, B_MN, 128>::SMEM_BYTES;
       break;
     default:
-      *k = gemm_tc_kernel<KIND, A_MN, B_MN, 256>;
+      *k = gemm_tc_kernel<KIND, A_MN, B_MN, 256, OUT_BF16>;
       *smem = GemmCfg<KIND, A_MN, B_MN, 256>::SMEM_BYTES;
       break;
   }
 }
 
+// The epilogue is compiled per output type: fp32-output kernels (every GEMM of the tf32 models) do not carry
+// the bf16 store paths, which keeps their instruction footprint — what a run-once kernel pays for — small.
 template <MmaKind KIND>
-static void select_major(bool a_mn, bool b_mn, int block_n, void (**k)(const GemmArgs), int* smem) {
-  if (a_mn && b_mn) return select_n<KIND, true, true>(block_n, k, smem);
-  if (a_mn) return select_n<KIND, true, false>(block_n, k, smem);
-  if (b_mn) return select_n<KIND, false, true>(block_n, k, smem);
-  return select_n<KIND, false, false>(block_n, k, smem);
+static void select_major(bool a_mn, bool b_mn, int block_n, int out_dtype, void (**k)(const GemmArgs), int* smem) {
+  if (out_dtype == B2D_BF16) {
+    if (a_mn && b_mn) return select_n<KIND, true, true, true>(block_n, k, smem);
+    if (a_mn) return select_n<KIND, true, false, true>(block_n, k, smem);
+    if (b_mn) return select_n<KIND, false, true, true>(block_n, k, smem);
+    return select_n<KIND, false, false, true>(block_n, k, smem);
+  }
+  if (a_mn && b_mn) return select_n<KIND, true, true, false>(block_n, k, smem);
+  if (a_mn) return select_n<KIND, true, false, false>(block_n, k, smem);
+  if (b_mn) return select_n<KIND, false, true, false>(block_n, k, smem);
+  return select_n<KIND, false, false, false>(block_n, k, smem);
 }
 
 extern "C" int b2d_gemm_query(const b2d_gemm_desc* desc, b2d_gemm_geometry* out) {
@@ -723,9 +797,9 @@ extern "C" int b2d_gemm_plan_create(const b2d_gemm_desc* desc, b2d_gemm_plan** o
   p->launch_smem = g.smem_bytes;
   p->geo = g;
   if (d.dtype == B2D_F32)
-    select_major<MmaKind::TF32>(d.a_mn_major, d.b_mn_major, g.block_n, &p->kernel, &p->smem_bytes);
+    select_major<MmaKind::TF32>(d.a_mn_major, d.b_mn_major, g.block_n, d.out_dtype, &p->kernel, &p->smem_bytes);
   else
-    select_major<MmaKind::F16>(d.a_mn_major, d.b_mn_major, g.block_n, &p->kernel, &p->smem_bytes);
+    select_major<MmaKind::F16>(d.a_mn_major, d.b_mn_major, g.block_n, d.out_dtype, &p->kernel, &p->smem_bytes);
   cudaError_t e = cudaFuncSetAttribute(reinterpret_cast<const void*>(p->kernel),
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem_bytes);
   if (e != cudaSuccess) {
@@ -733,14 +807,15 @@ extern "C" int b2d_gemm_plan_create(const b2d_gemm_desc* desc, b2d_gemm_plan** o
     delete p;
     return B2D_ERR_CUDA;
   }
+  finish_plan(p);
   *out = p;
   return B2D_OK;
 }
 
 extern "C" int b2d_gemm_plan_run(const b2d_gemm_plan* p, void* stream) {
   B2D_REQUIRE(p != nullptr, "gemm_plan_run: null plan");
-  const dim3 grid(p->geo.m_tiles, p->geo.n_tiles, p->geo.splits);
-  B2D_CUDA_CHECK(launch_pdl(p->kernel, grid, dim3(256), p->launch_smem, static_cast<cudaStream_t>(stream), p->args));
+  B2D_CUDA_CHECK(launch_pdl(p->kernel, dim3(p->grid), dim3(256), p->launch_smem, static_cast<cudaStream_t>(stream),
+                            p->args));
   return B2D_OK;
 }
 
@@ -888,9 +963,9 @@ static int conv_plan_create(const b2d_conv_desc& d, bool dgrad, b2d_gemm_plan** 
   p->launch_smem = g.smem_bytes;
   p->geo = g;
   if (d.dtype == B2D_F32)
-    select_major<MmaKind::TF32>(false, !dgrad, g.block_n, &p->kernel, &p->smem_bytes);
+    select_major<MmaKind::TF32>(false, !dgrad, g.block_n, d.out_dtype, &p->kernel, &p->smem_bytes);
   else
-    select_major<MmaKind::F16>(false, !dgrad, g.block_n, &p->kernel, &p->smem_bytes);
+    select_major<MmaKind::F16>(false, !dgrad, g.block_n, d.out_dtype, &p->kernel, &p->smem_bytes);
   cudaError_t e = cudaFuncSetAttribute(reinterpret_cast<const void*>(p->kernel),
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem_bytes);
   if (e != cudaSuccess) {
@@ -898,6 +973,7 @@ static int conv_plan_create(const b2d_conv_desc& d, bool dgrad, b2d_gemm_plan** 
     delete p;
     return B2D_ERR_CUDA;
   }
+  finish_plan(p);
   *out = p;
   return B2D_OK;
 }
@@ -973,9 +1049,9 @@ extern "C" int b2d_conv_dgrad_class_plan_create(const b2d_conv_desc* dp, int a, 
   p->launch_smem = g.smem_bytes;
   p->geo = g;
   if (d.dtype == B2D_F32)
-    select_major<MmaKind::TF32>(false, false, g.block_n, &p->kernel, &p->smem_bytes);
+    select_major<MmaKind::TF32>(false, false, g.block_n, d.out_dtype, &p->kernel, &p->smem_bytes);
   else
-    select_major<MmaKind::F16>(false, false, g.block_n, &p->kernel, &p->smem_bytes);
+    select_major<MmaKind::F16>(false, false, g.block_n, d.out_dtype, &p->kernel, &p->smem_bytes);
   cudaError_t e = cudaFuncSetAttribute(reinterpret_cast<const void*>(p->kernel),
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem_bytes);
   if (e != cudaSuccess) {
@@ -983,6 +1059,7 @@ extern "C" int b2d_conv_dgrad_class_plan_create(const b2d_conv_desc* dp, int a, 
     delete p;
     return B2D_ERR_CUDA;
   }
+  finish_plan(p);
   *out = p;
   return B2D_OK;
 }
@@ -1357,9 +1434,9 @@ extern "C" int b2d_gemm_noalloc(const b2d_gemm_desc* desc, void* stream) {
             (d.mask != nullptr && d.mask_dtype == B2D_BF16 ? kFlagMaskBf16 : 0);
   a.stages = g.stages;
   if (d.dtype == B2D_F32)
-    select_major<MmaKind::TF32>(d.a_mn_major, d.b_mn_major, g.block_n, &plan.kernel, &plan.smem_bytes);
+    select_major<MmaKind::TF32>(d.a_mn_major, d.b_mn_major, g.block_n, d.out_dtype, &plan.kernel, &plan.smem_bytes);
   else
-    select_major<MmaKind::F16>(d.a_mn_major, d.b_mn_major, g.block_n, &plan.kernel, &plan.smem_bytes);
+    select_major<MmaKind::F16>(d.a_mn_major, d.b_mn_major, g.block_n, d.out_dtype, &plan.kernel, &plan.smem_bytes);
   B2D_CUDA_CHECK(cudaFuncSetAttribute(reinterpret_cast<const void*>(plan.kernel),
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, plan.smem_bytes));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -1369,7 +1446,8 @@ extern "C" int b2d_gemm_noalloc(const b2d_gemm_desc* desc, void* stream) {
     B2D_CUDA_CHECK(cudaMemsetAsync(counters, 0, tiles * sizeof(uint32_t), st));
     B2D_CUDA_CHECK(cudaMemsetAsync(workspace, 0, ws_floats * sizeof(float), st));
   }
-  const dim3 grid(g.m_tiles, g.n_tiles, g.splits);
-  B2D_CUDA_CHECK(launch_pdl(plan.kernel, grid, dim3(256), g.smem_bytes, st, plan.args));
+  plan.geo = g, plan.launch_smem = g.smem_bytes;
+  finish_plan(&plan);
+  B2D_CUDA_CHECK(launch_pdl(plan.kernel, dim3(plan.grid), dim3(256), g.smem_bytes, st, plan.args));
   return B2D_OK;
 }
