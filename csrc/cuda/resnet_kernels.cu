@@ -252,16 +252,21 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnArgs a) {
   const int C = a.C, M = a.M;
   const ChanMap m = chan_map<V>(C, a.lanes_c);
   const T* x = static_cast<const T*>(a.x);
-  const T* y = static_cast<const T*>(a.y);
   const T* dy = static_cast<const T*>(a.dy);
   const int r0 = blockIdx.y * a.rows_per_cta, r1 = min(M, r0 + a.rows_per_cta);
   float s[V], q[V];
 #pragma unroll
   for (int k = 0; k < V; ++k) s[k] = 0.f, q[k] = 0.f;
   if (m.ok) {
-    float mean[V], rstd[V];
+    // The ReLU mask (y > 0) is recomputed from x with the forward pass' own scale / shift instead of
+    // reading y back: same fp32 expression, and rounding y to bf16 cannot change its sign.
+    float mean[V], rstd[V], sc[V], sh[V];
 #pragma unroll
-    for (int k = 0; k < V; ++k) mean[k] = a.saved[m.col + k], rstd[k] = a.saved[C + m.col + k];
+    for (int k = 0; k < V; ++k) {
+      mean[k] = a.saved[m.col + k], rstd[k] = a.saved[C + m.col + k];
+      sc[k] = a.gamma[m.col + k] * rstd[k];
+      sh[k] = a.beta[m.col + k] - mean[k] * sc[k];
+    }
 #pragma unroll 4
     for (int r = r0 + m.rg; r < r1; r += m.nrg) {
       const size_t o = (size_t)r * C + m.col;
@@ -269,10 +274,8 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const BnArgs a) {
       VecIO<T>::load(dy + o, g);
       VecIO<T>::load(x + o, xv);
       if (a.relu) {
-        float yv[V];
-        VecIO<T>::load(y + o, yv);
 #pragma unroll
-        for (int k = 0; k < V; ++k) g[k] = yv[k] > 0.f ? g[k] : 0.f;
+        for (int k = 0; k < V; ++k) g[k] = fmaf(xv[k], sc[k], sh[k]) > 0.f ? g[k] : 0.f;
       }
 #pragma unroll
       for (int k = 0; k < V; ++k) {
@@ -302,13 +305,14 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnArgs a) {
   const ChanMap m = chan_map<V>(C, a.lanes_c);
   if (!m.ok) return;
   const float inv_m = 1.f / (float)M;
-  float mean[V], rstd[V], ga[V], sb[V], sq[V];
+  float mean[V], rstd[V], ga[V], sb[V], sq[V], sh[V];
 #pragma unroll
   for (int k = 0; k < V; ++k) {
     const int c = m.col + k;
     mean[k] = a.saved[c], rstd[k] = a.saved[C + c];
     const float rs = a.red[c], rq = a.red[C + c];
     ga[k] = a.gamma[c] * rstd[k];
+    sh[k] = a.beta[c] - mean[k] * ga[k];          // forward: y = x * ga + sh
     sb[k] = rs * inv_m, sq[k] = rq * inv_m;
     if (blockIdx.y == 0 && m.rg == 0) {
       a.dbeta[c] += rs, a.dgamma[c] += rq;
@@ -317,21 +321,18 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnArgs a) {
   }
   if (a.dx == nullptr) return;
   const T* x = static_cast<const T*>(a.x);
-  const T* y = static_cast<const T*>(a.y);
   const T* dy = static_cast<const T*>(a.dy);
   T* dx = static_cast<T*>(a.dx);
   const int r0 = blockIdx.y * a.rows_per_cta, r1 = min(M, r0 + a.rows_per_cta);
-#pragma unroll 2
+#pragma unroll 4
   for (int r = r0 + m.rg; r < r1; r += m.nrg) {
     const size_t o = (size_t)r * C + m.col;
     float g[V], xv[V];
     VecIO<T>::load(dy + o, g);
     VecIO<T>::load(x + o, xv);
-    if (a.relu) {
-      float yv[V];
-      VecIO<T>::load(y + o, yv);
+    if (a.relu) {     // mask recomputed from x (see bn_bwd_reduce_kernel)
 #pragma unroll
-      for (int k = 0; k < V; ++k) g[k] = yv[k] > 0.f ? g[k] : 0.f;
+      for (int k = 0; k < V; ++k) g[k] = fmaf(xv[k], ga[k], sh[k]) > 0.f ? g[k] : 0.f;
     }
 #pragma unroll
     for (int k = 0; k < V; ++k) {
@@ -710,7 +711,7 @@ extern "C" int b2d_bn_backward(const b2d_bn_desc* dp, void* stream) {
   B2D_REQUIRE(d.x && d.dy && d.gamma && d.saved && d.red && d.stats && d.dgamma && d.dbeta,
               "bn_backward: null tensor");
   if (d.residual != nullptr) a.relu = 0;   // dy is already the gradient of the pre-activation sum
-  B2D_REQUIRE(!a.relu || d.y, "bn_backward: the ReLU mask needs the forward output");
+  B2D_REQUIRE(!a.relu || d.beta, "bn_backward: the ReLU mask is recomputed from x and needs beta");
   const ChanGrid g = chan_grid(d.M, d.C, vec_of(d.dtype));
   const ChanGrid gr = chan_grid(d.M, d.C, vec_of(d.dtype), kReduceCtas);
   a.rows_per_cta = g.rows_per_cta, a.lanes_c = g.lanes_c;

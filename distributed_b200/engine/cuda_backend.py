@@ -164,7 +164,16 @@ class CudaBackend:
         dt = dy.dtype
         vec = 4 if dt == torch.float32 else 8
         dy2 = dy.view(-1, dy.shape[-1])
-        if (x.dtype == dt and self._conv_tc_ok(x.shape, dw.shape, strides, pad, out_hw=dy.shape[1:3], dtype=dt)
+        pointwise = (tuple(dw.shape[:2]) == (1, 1) and tuple(strides) == (1, 1) and tuple(pad) == (0, 0)
+                     and x.dtype == dt and x.shape[3] % vec == 0 and dw.shape[3] % vec == 0
+                     and os.environ.get("B200DIST_CONV", "") != "direct"
+                     and os.environ.get("B200DIST_WGRAD_1X1", "gemm") == "gemm")
+        if pointwise:
+            # a 1x1 / stride-1 filter gradient is a plain GEMM over the pixels: dW[ci, co] += x^T . dy,
+            # split along the pixels, partial tiles added with 16-byte vector reductions
+            wgrad = self._plan(x.view(-1, x.shape[3]), dy2, dw.view(dw.shape[2], dw.shape[3]), a_mn_major=True,
+                               b_mn_major=True, accumulate=True)
+        elif (x.dtype == dt and self._conv_tc_ok(x.shape, dw.shape, strides, pad, out_hw=dy.shape[1:3], dtype=dt)
                 and x.shape[3] % vec == 0 and dw.shape[3] % vec == 0):
             plan = tc.ConvWgradPlan(x, dy, dw, pad, stride=strides[0])
             self.plans.append(plan)
