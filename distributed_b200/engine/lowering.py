@@ -55,6 +55,16 @@ class StepProgram:
             f()
 
 
+def _side(f):
+    """Tag a backward launch as independent of the rest of the backward chain (a weight gradient: it
+    reads an activation and a gradient that are final, and writes only the gradient arena), so the
+    trainer may put it on a concurrent branch of the step graph."""
+    def run():
+        f()
+    run.side_ok = True
+    return run
+
+
 @dataclass
 class _State:
     cur: torch.Tensor                 # activation
@@ -167,7 +177,7 @@ class _Lowerer:
                 relu = layer.activation == "relu"
                 prog.forward.append(be.conv2d_fwd(st.cur, w, b, y, layer.strides, pad, relu))
                 if training:
-                    stage = [be.conv2d_wgrad(st.cur, dy, dw, db, layer.strides, pad)]
+                    stage = [_side(be.conv2d_wgrad(st.cur, dy, dw, db, layer.strides, pad))]
                     if st.d_cur is not None:
                         extra = {"addend": st.addend} if st.addend is not None else {}
                         stage.append(be.conv2d_dgrad(dy, w, st.d_cur, layer.strides, pad,
@@ -260,7 +270,7 @@ class _Lowerer:
                                        and self.fuses_head(nxt, True, units, nxt.units))
                     if head_takes_bias:
                         self.pending_bias_grad = db
-                    stage = [be.dense_wgrad(st.cur, dy, dw, None if head_takes_bias else db)]
+                    stage = [_side(be.dense_wgrad(st.cur, dy, dw, None if head_takes_bias else db))]
                     if st.d_cur is not None:
                         stage.append(be.dense_dgrad(dy, w, st.d_cur, mask=st.cur if st.post_relu else None))
                     self.stages.append(stage)

@@ -168,13 +168,35 @@ class Trainer:
                             f()
                         pipe["small"]()                    # the only communication on the critical path
                     else:
-                        prog.run()
+                        self._run_step_branches(prog)
                         self.updates[slot]()
                     nl.check(lib.b2d_exec_end_capture(h, slot), "b2d_exec_end_capture")
                 self.kernels_per_step = int(lib.b2d_exec_graph_nodes(h, 0))
             else:
                 self.kernels_per_step = None
         self.stream.synchronize()
+
+    def _run_step_branches(self, prog):
+        """Issue one step for capture.  Weight-gradient launches (tagged ``side_ok`` by the lowering) go to
+        the executor's side stream, forked right where they sit in the backward list and joined before the
+        update: in the graph they become a branch that runs concurrently with the data-gradient chain
+        (B200DIST_SIDE_WGRAD=0 keeps the step a single chain)."""
+        import os
+        from .._native import cuda_lib as nl
+        for f in prog.forward:
+            f()
+        side = os.environ.get("B200DIST_SIDE_WGRAD", "1") != "0"
+        forked = False
+        for f in prog.backward:
+            if side and getattr(f, "side_ok", False):
+                nl.check(self._lib.b2d_exec_fork(self._exec), "b2d_exec_fork")
+                with torch.cuda.stream(self.side_stream):
+                    f()
+                forked = True
+            else:
+                f()
+        if forked:
+            nl.check(self._lib.b2d_exec_join(self._exec), "b2d_exec_join")
 
     def _deferred_begin(self, prog):
         """Arena offset where the deferred bucket starts (end of the first parametrised layer), or
