@@ -44,6 +44,8 @@ class StepProgram:
     backward: list[Callable[[], None]] = field(default_factory=list)
     logits: torch.Tensor | None = None
     early_forward: int = 0            # forward launches that need only the FIRST parametrised layer
+    early_backward: int = -1          # backward launches before the first parametrised layer's own backward stage
+                                      # (everything after that layer is final there: bucket boundary); -1 = unknown
     first_param_layer: int = -1       # leaf index of that layer (bucket boundary for overlapped all-reduce)
     description: list[str] = field(default_factory=list)
     keep: list = field(default_factory=list)        # buffers / plans kept alive
@@ -86,6 +88,7 @@ class _Lowerer:
         self.pending_bias_grad = None
         self.head_done = False
         self.fused_tail = False
+        self.first_param_stage = -1
 
     # -- helpers ---------------------------------------------------------------------
     def pview(self, flat, layer):
@@ -99,10 +102,11 @@ class _Lowerer:
         return (self.training and is_last and layer.activation is None and layer.use_bias
                 and getattr(self.be, "supports_conv_c1_pool", False) and self.be.supports_fused_head(k_in, units))
 
-    def note_param_layer(self, layer):
+    def note_param_layer(self, layer, top_level=True):
         prog = self.prog
         if prog.first_param_layer < 0:
             prog.first_param_layer = self.layout.leaf_index(layer)
+            self.first_param_stage = len(self.stages) if top_level else -1
         elif prog.early_forward == 0:
             prog.early_forward = len(prog.forward)     # everything so far needs only the first layer's weights
 
@@ -145,7 +149,7 @@ class _Lowerer:
                 i += 1
                 continue
             if isinstance(layer, (L.Conv2D, L.Dense, L.BatchNormalization)):
-                self.note_param_layer(layer)
+                self.note_param_layer(layer, top_level)
 
             if isinstance(layer, L.Conv2D):
                 w, b = self.kernel_bias(self.params, layer)
@@ -425,6 +429,9 @@ def lower(layers, batch: int, be, layout: ArenaLayout, params, grads, x_in, labe
             prog.description.append("softmax_xent (+grad, +accuracy count)")
     for stage in reversed(lw.stages):
         prog.backward.extend(stage)
+    if training and lw.first_param_stage >= 0:
+        # stages after the first parametrised layer's run first in backward
+        prog.early_backward = sum(len(stage) for stage in lw.stages[lw.first_param_stage + 1:])
     if begin is not None:
         prog.early_forward = 0       # the step starts by re-reading every weight: nothing to overlap
     return prog

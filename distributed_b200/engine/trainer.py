@@ -117,6 +117,7 @@ class Trainer:
                                           self.ring_len), "b2d_exec_set_metrics")
         self.side_stream = torch.cuda.ExternalStream(lib.b2d_exec_side_stream(h), device=self.be.device)
         self.pipelined = []          # per slot: {"small", "deferred", "flush"} or empty
+        self.bucketed = []           # per slot: {"early", "late"} or empty (intra-step overlap, default)
         torch.cuda.synchronize(self.be.device)
         import os
         with torch.cuda.stream(self.stream):
@@ -133,6 +134,16 @@ class Trainer:
                     # step's first kernels run.  Measured SLOWER for the README model (the overlap
                     # window — one 5 us kernel — is shorter than the bucket's barrier + transfer), so
                     # it is off by default; it pays once the first layer's forward is long.
+                    # Default for N > 1: two buckets inside the step.  Everything after the first parametrised
+                    # layer is final once that layer's own backward starts, so its fused all-reduce+SGD runs on
+                    # the side branch UNDER the first layer's backward; only the first layer's (small) bucket and
+                    # the metric sums remain on the critical path.  B200DIST_BUCKETS=0: one update per step.
+                    bucket_begin = self._bucket_begin(prog)
+                    if (self.use_graph and bucket_begin is not None and hasattr(self.comm, "make_bucketed_updates")
+                            and os.environ.get("B200DIST_BUCKETS", "1") != "0"
+                            and os.environ.get("B200DIST_PIPELINE", "0") != "1"):
+                        self.bucketed.append(self.comm.make_bucketed_updates(
+                            be, self.params, g_slot, g_other, lay.n_params, self.lr, bucket_begin))
                     deferred_begin = self._deferred_begin(prog)
                     if (self.use_graph and deferred_begin is not None
                             and hasattr(self.comm, "make_pipelined_updates")
@@ -167,6 +178,9 @@ class Trainer:
                         for f in prog.backward:
                             f()
                         pipe["small"]()                    # the only communication on the critical path
+                    elif len(self.bucketed) == n_slots:
+                        self._run_step_branches(prog, early=self.bucketed[slot]["early"])
+                        self.bucketed[slot]["late"]()
                     else:
                         self._run_step_branches(prog)
                         self.updates[slot]()
@@ -176,18 +190,26 @@ class Trainer:
                 self.kernels_per_step = None
         self.stream.synchronize()
 
-    def _run_step_branches(self, prog):
+    def _run_step_branches(self, prog, early=None):
         """Issue one step for capture.  Weight-gradient launches (tagged ``side_ok`` by the lowering) go to
         the executor's side stream, forked right where they sit in the backward list and joined before the
         update: in the graph they become a branch that runs concurrently with the data-gradient chain
-        (B200DIST_SIDE_WGRAD=0 keeps the step a single chain)."""
+        (B200DIST_SIDE_WGRAD=0 keeps the step a single chain).  ``early``: the fused all-reduce+SGD of every
+        layer after the first parametrised one; it is queued on the side stream — behind the weight gradients
+        that feed it and after the main stream's data gradients that still read those weights — at the point
+        where only the first layer's backward remains."""
         import os
         from .._native import cuda_lib as nl
         for f in prog.forward:
             f()
         side = os.environ.get("B200DIST_SIDE_WGRAD", "1") != "0"
         forked = False
-        for f in prog.backward:
+        for i, f in enumerate(prog.backward):
+            if early is not None and i == prog.early_backward:
+                nl.check(self._lib.b2d_exec_fork(self._exec), "b2d_exec_fork")
+                with torch.cuda.stream(self.side_stream):
+                    early()
+                forked, side = True, False      # later weight gradients stay on the main stream
             if side and getattr(f, "side_ok", False):
                 nl.check(self._lib.b2d_exec_fork(self._exec), "b2d_exec_fork")
                 with torch.cuda.stream(self.side_stream):
@@ -197,6 +219,16 @@ class Trainer:
                 f()
         if forked:
             nl.check(self._lib.b2d_exec_join(self._exec), "b2d_exec_join")
+
+    def _bucket_begin(self, prog):
+        """Arena offset where the early bucket starts (end of the first parametrised layer), or None."""
+        if prog.first_param_layer < 0 or not 0 <= prog.early_backward < len(prog.backward):
+            return None
+        later = [s for s in self.layout.slots if s.layer_index > prog.first_param_layer]
+        if not later:
+            return None
+        begin = min(s.offset for s in later)
+        return begin if 0 < begin < self.layout.n_params else None
 
     def _deferred_begin(self, prog):
         """Arena offset where the deferred bucket starts (end of the first parametrised layer), or

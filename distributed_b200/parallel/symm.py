@@ -191,6 +191,22 @@ class SymmComm:
                      "b2d_allreduce_sgd")
         return run
 
+    def make_bucketed_updates(self, be, params, g_slot, g_other, n_params, lr, early_begin):
+        """Two fused all-reduce+SGD launches per step (engine/trainer.py):
+
+        * ``early`` — [early_begin, n_params): every layer after the first parametrised one, on its own
+                       signal channel, launched on the side branch as soon as those gradients are final;
+        * ``late``  — [0, early_begin) + the metric tail: the first layer's (small) bucket, one-shot, the
+                       only communication left on the critical path.
+        Each zeroes its own ranges of the other ping-pong gradient buffer."""
+        n_total = params.numel()
+        return {
+            "early": self.make_update(be, params, g_slot, n_params, lr, grads_other=g_other,
+                                      segments=[(early_begin, n_params)], channel=1),
+            "late": self.make_update(be, params, g_slot, n_params, lr, grads_other=g_other,
+                                     segments=[(0, early_begin), (n_params, n_total)], channel=0, algo=0),
+        }
+
     def make_pipelined_updates(self, be, params, g_slot, g_other, n_params, lr, deferred_begin):
         """Bucketed update that hides the big bucket behind compute (see engine/trainer.py).
 
