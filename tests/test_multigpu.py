@@ -8,8 +8,9 @@ import pytest
 pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
 
 
-def _worker(ctx, n, algo, steps=5, epochs=2):
+def _worker(ctx, n, algo, steps=5, epochs=2, env=None):
     import os
+    os.environ.update(env or {})
     os.environ["B200DIST_ALLREDUCE"] = algo
     os.environ["TF_CONFIG"] = json.dumps(ctx.tf_config(base_port=int(ctx.address[0].split(":")[1]) % 20000 + 30000))
     import numpy as np
@@ -75,3 +76,20 @@ def test_n_gpus_match_one_gpu_with_the_global_batch():
     single = [float(np.abs(a).astype(np.float64).sum()) for a in m.get_weights()]
     for a, b in zip(single, multi["digest"]):
         assert abs(a - b) <= 2e-3 * max(abs(a), 1.0)
+
+
+@pytest.mark.parametrize("env", [{"B200DIST_BUCKETS": "1"}, {"B200DIST_PIPELINE": "1"}, {"B200DIST_SIDE_WGRAD": "0"}])
+def test_optional_update_schedules_keep_replicas_identical_and_match_the_default(env):
+    """Bucketed (intra-step), pipelined (cross-step) and single-chain schedules are different graphs over the
+    same kernels: replicas must stay bit-identical and the training trajectory must match the default one."""
+    from distributed_b200.launch import barrier_apply
+    n = min(_ngpu(), 8)
+    base = json.loads(barrier_apply(lambda ctx: _worker(ctx, n, "auto", steps=4, epochs=1), n, timeout=600)[0])
+    res = [json.loads(s) if s.startswith("{") else s for s in
+           barrier_apply(lambda ctx: _worker(ctx, n, "auto", steps=4, epochs=1, env=env), n, timeout=600)]
+    assert all(isinstance(r, dict) for r in res), res
+    for r in res[1:]:
+        assert r["loss"] == res[0]["loss"] and r["digest"] == res[0]["digest"]
+    assert abs(res[0]["loss"][0] - base["loss"][0]) < 1e-3
+    for a, b in zip(res[0]["digest"], base["digest"]):
+        assert abs(a - b) <= 1e-3 * max(abs(a), 1.0)
