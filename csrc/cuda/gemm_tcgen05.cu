@@ -629,6 +629,15 @@ static int pick_block_n(const b2d_gemm_desc& d) {
   return d.N % 128 == 0 || d.N > 512 ? 128 : 64;
 }
 
+// Persistent CTAs to launch for a resolved geometry: one per tile up to what the GPU holds at once — two per
+// SM when both their shared memory and their (double-buffered) accumulators fit together, else one.
+static int persistent_ctas(const b2d_gemm_geometry& g) {
+  const int total = g.m_tiles * g.n_tiles * g.splits;
+  const int acc_cols = g.block_n < 32 ? 32 : g.block_n;
+  const bool two = g.smem_bytes + 1024 <= (227 * 1024) / 2 && 2 * (2 * acc_cols) <= 512;
+  return min(total, 148 * (two ? 2 : 1));
+}
+
 static int resolve(const b2d_gemm_desc& d, b2d_gemm_geometry* g) {
   B2D_REQUIRE(d.M > 0 && d.N > 0 && d.K > 0, "gemm: M, N, K must be positive");
   B2D_REQUIRE(d.dtype == B2D_F32 || d.dtype == B2D_BF16, "gemm: dtype must be F32 or BF16");
@@ -667,6 +676,7 @@ static int resolve(const b2d_gemm_desc& d, b2d_gemm_geometry* g) {
     g->stages = max(2, min(g->stages, budget / stage_bytes));
   }
   g->smem_bytes = g->stages * stage_bytes + 1024 + 256;
+  g->ctas = persistent_ctas(*g);
   return B2D_OK;
 }
 
@@ -687,11 +697,8 @@ struct b2d_gemm_plan {
 static void finish_plan(b2d_gemm_plan* p) {
   GemmArgs& a = p->args;
   a.m_tiles = p->geo.m_tiles, a.n_tiles = p->geo.n_tiles;
-  const int total = a.m_tiles * a.n_tiles * a.splits;
-  const int acc_cols = p->geo.block_n < 32 ? 32 : p->geo.block_n;
-  // two CTAs share an SM when both their shared memory and their (double-buffered) accumulators fit
-  const bool two = p->launch_smem + 1024 <= (227 * 1024) / 2 && 2 * (2 * acc_cols) <= 512;
-  p->grid = min(total, 148 * (two ? 2 : 1));
+  p->geo.ctas = persistent_ctas(p->geo);      // the convolution plans changed m_tiles after resolve()
+  p->grid = p->geo.ctas;
 }
 
 template <MmaKind KIND, bool A_MN, bool B_MN, bool OUT_BF16>

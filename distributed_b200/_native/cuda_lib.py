@@ -33,7 +33,7 @@ class GemmDesc(C.Structure):
 
 class GemmGeometry(C.Structure):
     _fields_ = [(n, C.c_int) for n in
-                ("block_n", "m_tiles", "n_tiles", "splits", "k_blocks", "stages", "smem_bytes")]
+                ("block_n", "m_tiles", "n_tiles", "splits", "k_blocks", "stages", "smem_bytes", "ctas")]
 
 
 def _declare(lib) -> None:

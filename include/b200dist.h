@@ -78,6 +78,7 @@ typedef struct b2d_gemm_plan b2d_gemm_plan;
 /* Resolved launch geometry for a descriptor (splits after clamping etc.). */
 typedef struct b2d_gemm_geometry {
   int block_n, m_tiles, n_tiles, splits, k_blocks, stages, smem_bytes;
+  int ctas; /* persistent CTAs launched: min(m_tiles * n_tiles * splits, SMs x CTAs that fit an SM together) */
 } b2d_gemm_geometry;
 
 int b2d_gemm_query(const b2d_gemm_desc* desc, b2d_gemm_geometry* out);
@@ -87,6 +88,10 @@ size_t b2d_gemm_counter_count(const b2d_gemm_desc* desc);
 int b2d_gemm_plan_create(const b2d_gemm_desc* desc, b2d_gemm_plan** out);
 int b2d_gemm_plan_run(const b2d_gemm_plan* plan, void* stream);
 void b2d_gemm_plan_destroy(b2d_gemm_plan* plan);
+/* Latency analysis (tools/gemm_timeline.py): attach a buffer of 16 x int64 per persistent CTA (geometry.ctas)
+ * that receives %globaltimer stamps — start, prologue done, upstream kernel complete, first tiles landed, first
+ * tile's MMAs issued, accumulator visible to the epilogue, epilogue done, end — or detach with NULL. */
+void b2d_gemm_plan_set_timeline(b2d_gemm_plan* plan, long long* buf);
 
 /* The same GEMM for callers that cannot allocate device memory (a host that has given the
  * whole GPU to its own pool, a plug-in inside another runtime's callback, a latency-critical

@@ -94,6 +94,7 @@ BF16_SHAPES = [
     (3, 14, 14, 256, 1024, 1, 0),
     (5, 7, 7, 512, 512, 3, 1),        # several images per M tile
     (2, 13, 13, 64, 128, 3, 0),
+    (32, 56, 56, 64, 256, 1, 0),      # 896 x 2 tiles on <= 296 persistent CTAs
 ]
 
 

@@ -33,6 +33,8 @@ CASES = [
     (300, 200, 1000, True, False),
     (1024, 1024, 3200, False, True),
     (260, 36, 72, True, True),
+    (8192, 2048, 256, False, True),   # 1024 tiles: persistent CTAs walk several tiles, double-buffered TMEM
+    (4096, 640, 8192, False, False),  # 160 tiles, long K loop (deep ring, one CTA per SM)
 ]
 
 

@@ -15,7 +15,7 @@ NAMES = ["start", "prologue", "pdl_wait", "tiles_landed", "mma_issued", "acc_rea
 def run(name, a, b, d, **kw):
     p = GemmPlan(a, b, d, **kw)
     g = p.geometry
-    n_cta = g.m_tiles * g.n_tiles * g.splits
+    n_cta = g.ctas          # persistent CTAs (<= tiles); stamps 3-5 describe each CTA's FIRST tile
     buf = torch.zeros(n_cta * 16, dtype=torch.int64, device="cuda")
     for _ in range(3):
         p.run()
