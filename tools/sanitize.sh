@@ -4,8 +4,8 @@
 # Runs the smallest test that exercises every kernel family.  The cross-GPU kernels are covered by
 # the emulated (single cooperative launch) tests; the C++ CPU backend can be built with
 # CXXFLAGS="-fsanitize=thread,address" via `CXX_EXTRA=... python -m distributed_b200._native.build`.
-# NOTE (round 1): on the shared B200 pool `compute-sanitizer` is refused ("closed on this pool"); the last run
-# that was accepted is recorded in profiles/.  Until it is available again the kernels are guarded by their own
+# NOTE (round 1): on the shared B200 pool `compute-sanitizer` is refused ("closed on this pool"), so no
+# sanitizer log exists for this round.  Until it is available again the kernels are guarded by their own
 # argument checks (B2D_REQUIRE), small-shape tests and comparison with the C++ CPU reference.
 set -euo pipefail
 tool="${1:-memcheck}"
