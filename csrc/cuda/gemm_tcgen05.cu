@@ -658,8 +658,14 @@ static int resolve(const b2d_gemm_desc& d, b2d_gemm_geometry* g) {
   if (splits <= 0) {
     const int tiles = g->m_tiles * g->n_tiles;
     splits = 1;
-    // Few tiles and a long K: spread K over the idle SMs, keeping >= 2 k-blocks per CTA.
-    if (tiles < 74 && g->k_blocks >= 8) splits = min(g->k_blocks / 2, max(1, 148 / tiles));
+    // Few tiles and a long K: spread K over the idle SMs, keeping >= 2 k-blocks per CTA
+    // (B2D_SPLITK_MIN_KB overrides the 2: fewer, longer splits mean fewer partial tiles to meet).
+    static const int min_kb = [] {
+      const char* e = getenv("B2D_SPLITK_MIN_KB");
+      const int v = e != nullptr ? atoi(e) : 2;
+      return v >= 1 ? v : 2;
+    }();
+    if (tiles < 74 && g->k_blocks >= 8) splits = min(max(1, g->k_blocks / min_kb), max(1, 148 / tiles));
   }
   splits = max(1, min(splits, g->k_blocks));
   const int per = ceil_div(g->k_blocks, splits);
