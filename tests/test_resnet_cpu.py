@@ -90,3 +90,28 @@ def test_weights_roundtrip_keeps_moving_statistics(tmp_path):
     for a, b, n in zip(model.get_weights(), other.get_weights(), model.weight_names()):
         assert np.array_equal(a, b), n
     assert np.allclose(model.predict(x, batch_size=8), other.predict(x, batch_size=8), atol=1e-6)
+
+
+def test_resnet_builder_lowers_with_fused_block_tails_and_gradient_sums():
+    """The ResNet builder (one bottleneck per stage) through fit() on the CPU backend: every block's tail is
+    the BatchNorm+add+ReLU fusion, every block's gradient sum rides in its first convolution's data gradient,
+    weights in Keras order include the moving statistics, and the loss starts near ln(classes)."""
+    import distributed_b200 as tf
+    m = tf.models.resnet(blocks=(1, 1, 1, 1), input_shape=(32, 32, 3), classes=10, width=8, learning_rate=0.01)
+    names = m.weight_names()
+    assert names[0] == "conv2d/kernel:0" and names[1:5] == [
+        "batch_normalization/gamma:0", "batch_normalization/beta:0", "batch_normalization/moving_mean:0",
+        "batch_normalization/moving_variance:0"]
+    rng = np.random.default_rng(3)
+    x = rng.standard_normal((8, 32, 32, 3)).astype(np.float32)
+    y = rng.integers(0, 10, 8)
+    h = m.fit(x, y, batch_size=4, epochs=1, steps_per_epoch=2, verbose=0)
+    assert np.isfinite(h.history["loss"][0]) and 1.5 < h.history["loss"][0] < 4.0
+    plan = m._trainer.describe()
+    assert sum("residual block" in p for p in plan) == 4
+    assert sum("inside the last batchnorm" in p for p in plan) == 4
+    assert sum("gradient sum fused" in p for p in plan) == 4
+    assert sum(p.startswith("batchnorm+residual+relu") for p in plan) == 4
+    trainable = sum(l.count_trainable_params() for l in m.layers)
+    assert 0 < m.count_params() - trainable == sum(
+        int(np.prod(a.shape)) for n, a in zip(names, m.get_weights()) if "/moving_" in n)
