@@ -151,7 +151,9 @@ class Sequential(Model):
             raise ValueError(f"input samples have shape {tuple(sample_shape)}, model expects "
                              f"{self.layers[0].input_shape}")
         t = self._trainer
-        if t is None or t.batch != batch_per_replica:
+        # the learning rate is baked into the captured step (update kernel, BatchNorm pseudo-gradients): a
+        # changed optimizer.learning_rate rebuilds the trainer around the current weights
+        if t is None or t.batch != batch_per_replica or t.lr != float(self.optimizer.learning_rate):
             weights = t.get_weights() if t is not None else self._pending_weights
             if t is not None:
                 t.close()

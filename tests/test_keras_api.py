@@ -108,3 +108,21 @@ def test_version_and_datasets():
     (xtr, ytr), (xte, yte) = tf.keras.datasets.mnist.load_data()
     assert xtr.shape == (60000, 28, 28) and ytr.shape == (60000,) and xte.shape == (10000, 28, 28)
     assert xtr.dtype == np.uint8 and int(ytr.max()) == 9
+
+
+def test_changing_the_learning_rate_between_fits_takes_effect():
+    """lr is baked into the captured step; a new value must rebuild the trainer around the same weights."""
+    import numpy as np
+    import distributed_b200 as tf
+    rng = np.random.default_rng(0)
+    x = rng.random((64, 28, 28, 1)).astype(np.float32)
+    y = rng.integers(0, 10, 64)
+    m = tf.models.mnist_cnn(learning_rate=0.01)
+    m.fit(x, y, batch_size=64, epochs=1, steps_per_epoch=1, verbose=0)
+    w1 = m.get_weights()
+    m.optimizer.learning_rate = 0.0
+    m.fit(x, y, batch_size=64, epochs=1, steps_per_epoch=1, verbose=0)
+    assert all(np.array_equal(a, b) for a, b in zip(w1, m.get_weights()))       # lr = 0: nothing moves
+    m.optimizer.learning_rate = 0.05
+    m.fit(x, y, batch_size=64, epochs=1, steps_per_epoch=1, verbose=0)
+    assert any(not np.array_equal(a, b) for a, b in zip(w1, m.get_weights()))
