@@ -29,5 +29,21 @@ class ModelCheckpoint(Callback):
         self.model.save_weights(path)
 
 
+class LearningRateScheduler(Callback):
+    """``schedule(epoch, lr) -> lr`` evaluated at the start of every epoch (Keras signature).  The learning
+    rate is a constant of the captured step graph, so a changed value re-captures the step (a few
+    milliseconds) around the current weights; every replica evaluates the same schedule."""
+
+    def __init__(self, schedule, verbose=0):
+        self.schedule, self.verbose = schedule, verbose
+
+    def on_epoch_begin(self, epoch, logs=None):
+        opt = self.model.optimizer
+        lr = float(self.schedule(epoch, float(opt.learning_rate)))
+        if self.verbose:
+            print(f"Epoch {epoch + 1}: LearningRateScheduler setting learning rate to {lr}.")
+        opt.learning_rate = lr
+
+
 class History(Callback):
     pass

@@ -225,6 +225,7 @@ class Sequential(Model):
                 print(f"Epoch {epoch + 1}/{epochs}", file=out)
             for cb in callbacks:
                 cb.on_epoch_begin(epoch)
+            trainer = self._ensure_trainer(per_replica, sample_shape)     # a callback may have changed the lr
             trainer.reset_metrics()
             t0 = time.perf_counter()
             trainer.run_steps(xt, yt, self._global_step, steps_in_src, steps, global_batch)

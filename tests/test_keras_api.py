@@ -126,3 +126,25 @@ def test_changing_the_learning_rate_between_fits_takes_effect():
     m.optimizer.learning_rate = 0.05
     m.fit(x, y, batch_size=64, epochs=1, steps_per_epoch=1, verbose=0)
     assert any(not np.array_equal(a, b) for a, b in zip(w1, m.get_weights()))
+
+
+def test_learning_rate_scheduler_and_model_checkpoint(tmp_path):
+    import numpy as np
+    import distributed_b200 as tf
+    rng = np.random.default_rng(1)
+    x = rng.random((128, 28, 28, 1)).astype(np.float32)
+    y = rng.integers(0, 10, 128)
+    seen = []
+
+    def schedule(epoch, lr):
+        seen.append((epoch, lr))
+        return 0.02 if epoch == 0 else 0.0            # second epoch must not move the weights
+
+    m = tf.models.mnist_cnn(learning_rate=0.5)
+    ck = tf.keras.callbacks.ModelCheckpoint(str(tmp_path / "w-{epoch}.npz"))
+    m.fit(x, y, batch_size=64, epochs=2, steps_per_epoch=1, verbose=0,
+          callbacks=[tf.keras.callbacks.LearningRateScheduler(schedule), ck])
+    assert seen == [(0, 0.5), (1, 0.02)]
+    a, b = np.load(tmp_path / "w-1.npz"), np.load(tmp_path / "w-2.npz")
+    keys = [k for k in a.files if k.endswith("--0")]          # "conv2d/kernel:0" is stored as "conv2d__kernel--0"
+    assert keys and all(np.array_equal(a[k], b[k]) for k in keys)
