@@ -45,5 +45,31 @@ class LearningRateScheduler(Callback):
         opt.learning_rate = lr
 
 
+class EarlyStopping(Callback):
+    """Stops ``fit`` when ``monitor`` has not improved by ``min_delta`` for ``patience`` epochs.  The metric is
+    the cross-replica value, identical on every worker, so all replicas stop on the same epoch."""
+
+    def __init__(self, monitor="loss", min_delta=0.0, patience=0, mode="auto"):
+        self.monitor, self.min_delta, self.patience = monitor, abs(float(min_delta)), int(patience)
+        self.maximise = mode == "max" or (mode == "auto" and "acc" in monitor)
+
+    def on_train_begin(self, logs=None):
+        self.best, self.wait, self.stopped_epoch = None, 0, None
+
+    def on_epoch_end(self, epoch, logs=None):
+        v = (logs or {}).get(self.monitor)
+        if v is None:
+            return
+        better = self.best is None or (v > self.best + self.min_delta if self.maximise
+                                       else v < self.best - self.min_delta)
+        if better:
+            self.best, self.wait = v, 0
+            return
+        self.wait += 1
+        if self.wait > self.patience:
+            self.stopped_epoch = epoch
+            self.model.stop_training = True
+
+
 class History(Callback):
     pass

@@ -212,6 +212,7 @@ class Sequential(Model):
             from ..parallel.strategy import log
             log.warning("ModelCheckpoint callback is not provided. Workers will need to restart "
                         "training if any fails.")
+        self.stop_training = False
         history = History()
         history.params = {"epochs": epochs, "steps": steps, "batch_size": global_batch, "samples": n_samples}
         out = sys.stdout

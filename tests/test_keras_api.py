@@ -148,3 +148,15 @@ def test_learning_rate_scheduler_and_model_checkpoint(tmp_path):
     a, b = np.load(tmp_path / "w-1.npz"), np.load(tmp_path / "w-2.npz")
     keys = [k for k in a.files if k.endswith("--0")]          # "conv2d/kernel:0" is stored as "conv2d__kernel--0"
     assert keys and all(np.array_equal(a[k], b[k]) for k in keys)
+
+
+def test_early_stopping_stops_fit():
+    import numpy as np
+    import distributed_b200 as tf
+    rng = np.random.default_rng(2)
+    x = rng.random((64, 28, 28, 1)).astype(np.float32)
+    y = rng.integers(0, 10, 64)
+    m = tf.models.mnist_cnn(learning_rate=0.0)                 # the loss cannot improve
+    es = tf.keras.callbacks.EarlyStopping(monitor="loss", patience=1)
+    h = m.fit(x, y, batch_size=64, epochs=10, steps_per_epoch=1, verbose=0, callbacks=[es])
+    assert len(h.history["loss"]) == 3 and es.stopped_epoch == 2
