@@ -67,6 +67,21 @@ def _side(f):
     return run
 
 
+def _tag(f, **attrs):
+    """Wrap a launch and attach scheduling hints for the trainer's graph capture, keeping earlier ones:
+    ``branch=True`` — the launch belongs to a residual block's shortcut branch, which depends only on the
+    block's input (forward) / output gradient (backward) and may run on its own stream next to the main branch;
+    ``join_branch=True`` — the launch is the first consumer of that branch's results."""
+    def run():
+        f()
+    for k in ("side_ok", "branch", "join_branch"):
+        if getattr(f, k, False):
+            setattr(run, k, True)
+    for k, v in attrs.items():
+        setattr(run, k, v)
+    return run
+
+
 @dataclass
 class _State:
     cur: torch.Tensor                 # activation
@@ -379,28 +394,40 @@ class _Lowerer:
         # shortcut and apply the block's ReLU itself.  Backward order is the reverse of the order of
         # self.stages, and must be: shortcut, then main (whose first convolution may consume the shortcut's
         # input gradient), then the sum — hence the stage lists are swapped after lowering.
-        i0 = len(self.stages)
+        i0, f0 = len(self.stages), len(prog.forward)
         s = (self.sequence(layer.shortcut, _State(x, d_sc_in, False), top_level=False, final_dy=dy)
              if layer.shortcut else None)
-        i1 = len(self.stages)
+        i1, f1 = len(self.stages), len(prog.forward)
+        # the shortcut branch is independent of the main branch: let the trainer run it on its own stream
+        prog.forward[f0:f1] = [_tag(f, branch=True) for f in prog.forward[f0:f1]]
+        for k in range(i0, i1):
+            self.stages[k][:] = [_tag(f, branch=True) for f in self.stages[k]]
         if s is not None and s.post_relu:
             raise ValueError("the last layer of a residual branch must not carry an activation")
         sc_out = s.cur if s is not None else x
         self.fused_tail = False
         m = self.sequence(layer.main, main_in, top_level=False, final_dy=dy, final_fuse=(sc_out, relu, y))
         fused_tail, self.fused_tail = self.fused_tail, False
+        if f1 > f0:
+            # first consumers of the shortcut: forward, the launch that adds it (last of the main branch when the
+            # BatchNorm tail is fused, else the add below); backward, whichever launch folds its input gradient in
+            # (the last launch of the main branch's first stage = its first convolution's dgrad, else the sum stage)
+            if fused_tail:
+                prog.forward[-1] = _tag(prog.forward[-1], join_branch=True)
+            if fuse_sum and i1 < len(self.stages) and self.stages[i1]:
+                self.stages[i1][-1] = _tag(self.stages[i1][-1], join_branch=True)
         self.stages[i0:] = self.stages[i1:] + self.stages[i0:i1]
         if tuple(m.cur.shape) != out_shape or (s is not None and tuple(s.cur.shape) != out_shape):
             raise ValueError(f"residual block {layer.name}: branch output shapes differ")
         if not fused_tail:
             if m.post_relu:
                 raise ValueError("the last layer of a residual branch must not carry an activation")
-            prog.forward.append(be.add_act(m.cur, sc_out, y, 1 if relu else 0))
+            prog.forward.append(_tag(be.add_act(m.cur, sc_out, y, 1 if relu else 0), join_branch=f1 > f0))
         if need_dx and not fuse_sum:
             if st.post_relu:
-                sum_stage.append(be.add_act(d_main_in, other, st.d_cur, 2, mask=x))
+                sum_stage.append(_tag(be.add_act(d_main_in, other, st.d_cur, 2, mask=x), join_branch=f1 > f0))
             else:
-                sum_stage.append(be.add_act(d_main_in, other, st.d_cur, 0))
+                sum_stage.append(_tag(be.add_act(d_main_in, other, st.d_cur, 0), join_branch=f1 > f0))
         if fuse_sum:
             prog.description.append("  gradient sum fused into the first convolution's data-gradient epilogue")
         prog.description.append(f"  add{'+relu' if relu else ''} -> {out_shape}"

@@ -116,6 +116,8 @@ class Trainer:
         nl.check(lib.b2d_exec_set_metrics(h, tail.data_ptr(), TAIL * 4, self.metrics_host.data_ptr(),
                                           self.ring_len), "b2d_exec_set_metrics")
         self.side_stream = torch.cuda.ExternalStream(lib.b2d_exec_side_stream(h), device=self.be.device)
+        self.branch_stream = torch.cuda.Stream(device=self.be.device)     # shortcut branches of residual blocks
+        self._capture_events = []                                        # fork / join events of the captures
         self.pipelined = []          # per slot: {"small", "deferred", "flush"} or empty
         self.bucketed = []           # per slot: {"early", "late"} or empty (intra-step overlap, default)
         torch.cuda.synchronize(self.be.device)
@@ -196,29 +198,65 @@ class Trainer:
         """Issue one step for capture.  Weight-gradient launches (tagged ``side_ok`` by the lowering) go to
         the executor's side stream, forked right where they sit in the backward list and joined before the
         update: in the graph they become a branch that runs concurrently with the data-gradient chain
-        (B200DIST_SIDE_WGRAD=0 keeps the step a single chain).  ``early``: the fused all-reduce+SGD of every
+        (B200DIST_SIDE_WGRAD=0 keeps the step a single chain).  Launches tagged ``branch`` (the shortcut of a
+        residual block, forward and backward) run on a third stream from their first launch to their first
+        consumer (``join_branch``); B200DIST_SIDE_SHORTCUT=0 keeps them on the main stream.  ``early``: the fused all-reduce+SGD of every
         layer after the first parametrised one; it is queued on the side stream — behind the weight gradients
         that feed it and after the main stream's data gradients that still read those weights — at the point
         where only the first layer's backward remains."""
         import os
         from .._native import cuda_lib as nl
-        for f in prog.forward:
-            f()
         side = os.environ.get("B200DIST_SIDE_WGRAD", "1") != "0"
+        use_branch = os.environ.get("B200DIST_SIDE_SHORTCUT", "1") != "0"
+        main = torch.cuda.current_stream()
+        state = {"open": False}
+
+        def join_branch():
+            if state["open"]:
+                ev = torch.cuda.Event()
+                ev.record(self.branch_stream)
+                main.wait_event(ev)
+                self._capture_events.append(ev)
+                state["open"] = False
+
+        def on_branch(f):
+            """Shortcut branch of a residual block: its own stream, forked where its first launch sits."""
+            if not state["open"]:
+                ev = torch.cuda.Event()
+                ev.record(main)
+                self.branch_stream.wait_event(ev)
+                self._capture_events.append(ev)
+                state["open"] = True
+            with torch.cuda.stream(self.branch_stream):
+                f()
+
+        for f in prog.forward:
+            if getattr(f, "join_branch", False):
+                join_branch()
+            if use_branch and getattr(f, "branch", False):
+                on_branch(f)
+            else:
+                f()
+        join_branch()
         forked = False
         for i, f in enumerate(prog.backward):
+            if getattr(f, "join_branch", False):
+                join_branch()
             if early is not None and i == prog.early_backward:
                 nl.check(self._lib.b2d_exec_fork(self._exec), "b2d_exec_fork")
                 with torch.cuda.stream(self.side_stream):
                     early()
                 forked, side = True, False      # later weight gradients stay on the main stream
-            if side and getattr(f, "side_ok", False):
+            if use_branch and getattr(f, "branch", False):
+                on_branch(f)                    # incl. the branch's own weight gradients: they read its dy
+            elif side and getattr(f, "side_ok", False):
                 nl.check(self._lib.b2d_exec_fork(self._exec), "b2d_exec_fork")
                 with torch.cuda.stream(self.side_stream):
                     f()
                 forked = True
             else:
                 f()
+        join_branch()
         if forked:
             nl.check(self._lib.b2d_exec_join(self._exec), "b2d_exec_join")
 
