@@ -490,6 +490,59 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const T* __restrict__ 
   }
 }
 
+// Same gather with a compile-time window / stride: the (up to K*K) candidate windows of a pixel are enumerated
+// without divisions, and ALL their (code, dy) pairs are fetched before any is used — one memory round trip per
+// pixel instead of one per window (the run-time version above serialises them: 86 us for the ResNet stem pool).
+template <typename T, int K, int S>
+__global__ void __launch_bounds__(256) maxpool_bwd_fixed_kernel(const T* __restrict__ dy,
+                                                                 const uint8_t* __restrict__ code, T* __restrict__ dx,
+                                                                 int N, int H, int W, int C, int OH, int OW, int p) {
+  constexpr int V = VecIO<T>::N;
+  using CV = typename CodeVec<V>::type;
+  pdl_wait();
+  pdl_trigger();
+  const int cv = C / V;
+  const size_t total = (size_t)N * H * W * cv;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % cv) * V;
+    size_t t = i / cv;
+    const int iw = t % W;
+    t /= W;
+    const int ih = t % H;
+    const int n = (int)(t / H);
+    float v[K * K][V];
+    int cd[K * K][V];
+    bool ok[K * K];
+#pragma unroll
+    for (int kh = 0; kh < K; ++kh) {
+      const int th = ih + p - kh;
+      const bool okh = th >= 0 && th % S == 0 && th / S < OH;
+#pragma unroll
+      for (int kw = 0; kw < K; ++kw) {
+        const int tw = iw + p - kw;
+        const int tap = kh * K + kw;
+        ok[tap] = okh && tw >= 0 && tw % S == 0 && tw / S < OW;
+        if (ok[tap]) {
+          const size_t o = (((size_t)n * OH + th / S) * OW + tw / S) * C + c;
+          unpack_code(__ldg(reinterpret_cast<const CV*>(code + o)), cd[tap]);
+          VecIO<T>::load(dy + o, v[tap]);
+        }
+      }
+    }
+    float g[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) g[j] = 0.f;
+#pragma unroll
+    for (int tap = 0; tap < K * K; ++tap)
+      if (ok[tap]) {
+#pragma unroll
+        for (int j = 0; j < V; ++j)
+          if (cd[tap][j] == tap) g[j] += v[tap][j];
+      }
+    VecIO<T>::store(dx + i * V, g);
+  }
+}
+
 // Global average pooling: y[n,c] (fp32) = mean over H*W of x; backward: dx[n,h,w,c] = dy[n,c] / (H*W),
 // zeroed where msk <= 0 (msk = the pooled tensor itself when it is the output of a ReLU).
 template <typename T>
@@ -777,12 +830,29 @@ extern "C" int b2d_maxpool_bwd(int dtype, const void* dy, const uint8_t* code, v
   if (OW <= 0) OW = (W + 2 * p - k) / s + 1;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const dim3 grid(grid_1d((size_t)N * H * W * (C / V)));
-  if (dtype == B2D_F32)
-    B2D_CUDA_CHECK(launch_pdl(maxpool_bwd_kernel<float>, grid, dim3(256), 0, st, static_cast<const float*>(dy), code,
-                              static_cast<float*>(dx), N, H, W, C, OH, OW, k, s, p));
-  else
-    B2D_CUDA_CHECK(launch_pdl(maxpool_bwd_kernel<bf16_t>, grid, dim3(256), 0, st, static_cast<const bf16_t*>(dy), code,
-                              static_cast<bf16_t*>(dx), N, H, W, C, OH, OW, k, s, p));
+#define B2D_POOL_BWD_FIXED(T, K, S)                                                                              \
+  B2D_CUDA_CHECK(launch_pdl(maxpool_bwd_fixed_kernel<T, K, S>, grid, dim3(256), 0, st, static_cast<const T*>(dy), code, \
+                            static_cast<T*>(dx), N, H, W, C, OH, OW, p))
+  // B2D_POOL_BWD_FIXED=1 selects the compile-time-window kernels (off until measured on the GPU)
+  static const bool fixed = [] {
+    const char* e = getenv("B2D_POOL_BWD_FIXED");
+    return e != nullptr && e[0] == '1';
+  }();
+  if (!fixed) k = -k;      // no specialisation matches a negative window
+  if (dtype == B2D_F32) {
+    if (k == 3 && s == 2) B2D_POOL_BWD_FIXED(float, 3, 2);
+    else if (k == 2 && s == 2) B2D_POOL_BWD_FIXED(float, 2, 2);
+    else
+      B2D_CUDA_CHECK(launch_pdl(maxpool_bwd_kernel<float>, grid, dim3(256), 0, st, static_cast<const float*>(dy), code,
+                                static_cast<float*>(dx), N, H, W, C, OH, OW, k < 0 ? -k : k, s, p));
+  } else {
+    if (k == 3 && s == 2) B2D_POOL_BWD_FIXED(bf16_t, 3, 2);
+    else if (k == 2 && s == 2) B2D_POOL_BWD_FIXED(bf16_t, 2, 2);
+    else
+      B2D_CUDA_CHECK(launch_pdl(maxpool_bwd_kernel<bf16_t>, grid, dim3(256), 0, st, static_cast<const bf16_t*>(dy), code,
+                                static_cast<bf16_t*>(dx), N, H, W, C, OH, OW, k < 0 ? -k : k, s, p));
+  }
+#undef B2D_POOL_BWD_FIXED
   return B2D_OK;
 }
 
