@@ -8,6 +8,14 @@
 // small std::thread pool by output rows.
 #include <algorithm>
 #include <atomic>
+#include <chrono>
+#include <memory>
+#include <pthread.h>
+#include <sched.h>
+#include <unistd.h>
+#include <cstdlib>
+#include <condition_variable>
+#include <mutex>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -27,22 +35,135 @@ int num_threads() {
   return static_cast<int>(std::max(1u, std::min(hw, 8u)));
 }
 
-// Static-partition parallel for over [0, n); falls back to inline when the range is small.
+// Persistent worker pool: threads are created once and parked on a condition variable; a parallel_for posts
+// one job (a range cut into chunks handed out by an atomic counter), the caller works too, and returns when
+// every chunk is done.  (The first version spawned and joined std::threads per call: ~0.1 ms per op.)
+class Pool {
+ public:
+  static Pool& get() {
+    static Pool p;
+    return p;
+  }
+  // A job is finished when every CHUNK is done, not when every worker has checked in: a worker that wakes
+  // late finds no chunk left and goes back to sleep, so a short job never waits for the slowest wake-up.
+  struct Job {
+    const std::function<void(int64_t, int64_t)>* fn;
+    int64_t n, chunk, chunks;
+    std::atomic<int64_t> next{0}, done{0};
+  };
+  void run(int64_t n, int64_t chunk, int want, const std::function<void(int64_t, int64_t)>& fn) {
+    std::lock_guard<std::mutex> serial(run_mu_);          // one job at a time
+    ensure(want - 1);
+    auto job = std::make_shared<Job>();
+    job->fn = &fn, job->n = n, job->chunk = chunk, job->chunks = (n + chunk - 1) / chunk;
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      job_ = job;
+      active_ = std::min<int>(want - 1, (int)workers_.size());
+    }
+    generation_.fetch_add(1, std::memory_order_release);
+    cv_.notify_all();
+    work(*job);
+    for (int spin = 0; job->done.load(std::memory_order_acquire) < job->chunks; ++spin) {
+      if (spin < 4096) __builtin_ia32_pause();
+      else std::this_thread::yield();
+    }
+  }
+
+ private:
+  Pool() = default;
+  ~Pool() {
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      stop_ = true;
+    }
+    generation_.fetch_add(1, std::memory_order_release);
+    cv_.notify_all();
+    for (auto& t : workers_) t.join();
+  }
+  void ensure(int k) {
+    while ((int)workers_.size() < k) {
+      const int id = (int)workers_.size();
+      workers_.emplace_back([this, id] { loop(id); });
+      pin(workers_.back(), id);
+    }
+  }
+  // Workers are woken by one thread and, left to the scheduler's wake-affine placement, all land on the
+  // waker's CPU for bursts as short as these (measured: 8 threads on 1 CPU).  Each worker is therefore pinned
+  // to its own CPU of the process's affinity mask, starting at a per-process offset so that several worker
+  // processes on one host do not stack on the same cores.  B200DIST_CPU_PIN=0 leaves placement to the OS.
+  static void pin(std::thread& t, int id) {
+    const char* e = std::getenv("B200DIST_CPU_PIN");
+    if (e != nullptr && e[0] == '0') return;
+    cpu_set_t allowed;
+    CPU_ZERO(&allowed);
+    if (sched_getaffinity(0, sizeof(allowed), &allowed) != 0) return;
+    std::vector<int> cpus;
+    for (int c = 0; c < CPU_SETSIZE; ++c)
+      if (CPU_ISSET(c, &allowed)) cpus.push_back(c);
+    if (cpus.size() < 2) return;
+    const size_t off = static_cast<size_t>(getpid()) % cpus.size();
+    cpu_set_t one;
+    CPU_ZERO(&one);
+    CPU_SET(cpus[(off + id + 1) % cpus.size()], &one);
+    pthread_setaffinity_np(t.native_handle(), sizeof(one), &one);
+  }
+  static void work(Job& j) {
+    for (;;) {
+      const int64_t b = j.next.fetch_add(j.chunk, std::memory_order_relaxed);
+      if (b >= j.n) break;
+      (*j.fn)(b, std::min(j.n, b + j.chunk));      // the caller is still inside run(): fn is alive
+      j.done.fetch_add(1, std::memory_order_release);
+    }
+  }
+  void loop(int id) {
+    // After a job a worker keeps polling for the next one for a short while (the ops of a training step
+    // follow each other within tens of microseconds) before it parks on the condition variable.
+    static const int spin_us = [] {
+      const char* e = std::getenv("B200DIST_CPU_SPIN_US");
+      return e != nullptr ? std::max(0, atoi(e)) : 200;
+    }();
+    uint64_t seen = 0;
+    for (;;) {
+      const auto t0 = std::chrono::steady_clock::now();
+      while (generation_.load(std::memory_order_acquire) == seen) {
+        if (std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(spin_us)) {
+          std::unique_lock<std::mutex> lk(mu_);
+          cv_.wait(lk, [&] { return generation_.load(std::memory_order_acquire) != seen; });
+          break;
+        }
+        __builtin_ia32_pause();
+      }
+      std::shared_ptr<Job> job;
+      {
+        std::lock_guard<std::mutex> lk(mu_);
+        if (stop_) return;
+        seen = generation_.load(std::memory_order_acquire);
+        if (id < active_) job = job_;
+      }
+      if (job) work(*job);
+    }
+  }
+  std::mutex mu_, run_mu_;
+  std::condition_variable cv_;
+  std::vector<std::thread> workers_;
+  std::shared_ptr<Job> job_;
+  std::atomic<uint64_t> generation_{0};
+  int active_ = 0;
+  bool stop_ = false;
+};
+
+// Parallel for over [0, n) in chunks of >= grain; runs inline when the range is small.
 void parallel_for(int64_t n, int64_t grain, const std::function<void(int64_t, int64_t)>& fn) {
+  if (n <= 0) return;
   const int nt = static_cast<int>(std::min<int64_t>(num_threads(), (n + grain - 1) / grain));
   if (nt <= 1) {
     fn(0, n);
     return;
   }
-  std::vector<std::thread> th;
-  th.reserve(nt - 1);
-  const int64_t chunk = (n + nt - 1) / nt;
-  for (int t = 1; t < nt; ++t) {
-    const int64_t b = t * chunk, e = std::min(n, b + chunk);
-    if (b < e) th.emplace_back([=, &fn] { fn(b, e); });
-  }
-  fn(0, std::min(n, chunk));
-  for (auto& t : th) t.join();
+  // ~4 chunks per thread for balance, never smaller than the grain
+  const int64_t chunk = std::max<int64_t>(grain, (n + 4 * nt - 1) / (4 * nt));
+  Pool::get().run(n, chunk, nt, fn);
 }
 
 struct ConvShape {
@@ -99,8 +220,51 @@ B2C_API void b2c_conv2d_wgrad(const float* x, const float* dy, float* dw, float*
                               int W, int Ci, int Co, int KH, int KW, int sh, int sw, int ph, int pw,
                               int OH, int OW) {
   const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw, OH, OW);
+  const int64_t taps = (int64_t)KH * KW * Ci;
+  if (taps * Co <= 16384 && N >= 2) {
+    // Small filter (e.g. the README's 3x3x1x32): the reduction runs over many pixels and few taps, so the
+    // work is split over fixed groups of images, each into its own partial filter, and the partials are
+    // added in group order afterwards — the result does not depend on the number of threads.
+    constexpr int kGroup = 4;
+    const int groups = (N + kGroup - 1) / kGroup;
+    std::vector<float> part((size_t)groups * (taps * Co + Co), 0.f);
+    parallel_for(groups, 1, [&](int64_t g0, int64_t g1) {
+      for (int64_t g = g0; g < g1; ++g) {
+        float* __restrict__ pw_ = part.data() + g * (taps * Co + Co);
+        float* __restrict__ pb = pw_ + taps * Co;
+        for (int n = (int)g * kGroup; n < std::min(N, (int)(g + 1) * kGroup); ++n)
+          for (int oh = 0; oh < s.OH; ++oh)
+            for (int ow = 0; ow < s.OW; ++ow) {
+              const float* __restrict__ dp = dy + (((int64_t)n * s.OH + oh) * s.OW + ow) * Co;
+              if (db != nullptr)
+                for (int c = 0; c < Co; ++c) pb[c] += dp[c];
+              for (int kh = 0; kh < KH; ++kh) {
+                const int ih = oh * sh - ph + kh;
+                if (ih < 0 || ih >= H) continue;
+                for (int kw = 0; kw < KW; ++kw) {
+                  const int iw = ow * sw - pw + kw;
+                  if (iw < 0 || iw >= W) continue;
+                  const float* __restrict__ xp = x + (((int64_t)n * H + ih) * W + iw) * Ci;
+                  float* __restrict__ dwr = pw_ + (int64_t)(kh * KW + kw) * Ci * Co;
+                  for (int ci = 0; ci < Ci; ++ci) {
+                    const float xv = xp[ci];
+                    for (int c = 0; c < Co; ++c) dwr[ci * Co + c] += xv * dp[c];
+                  }
+                }
+              }
+            }
+      }
+    });
+    for (int g = 0; g < groups; ++g) {
+      const float* pg = part.data() + (int64_t)g * (taps * Co + Co);
+      for (int64_t i = 0; i < taps * Co; ++i) dw[i] += pg[i];
+      if (db != nullptr)
+        for (int c = 0; c < Co; ++c) db[c] += pg[taps * Co + c];
+    }
+    return;
+  }
   // Parallel over filter taps (kh, kw, ci): each owns a disjoint dW row, so no reduction.
-  parallel_for((int64_t)KH * KW * Ci, 1, [&](int64_t b, int64_t e) {
+  parallel_for(taps, 1, [&](int64_t b, int64_t e) {
     for (int64_t tap = b; tap < e; ++tap) {
       const int ci = tap % Ci, kw = (tap / Ci) % KW, kh = tap / ((int64_t)Ci * KW);
       float* dwr = dw + tap * Co;
@@ -161,23 +325,31 @@ B2C_API void b2c_conv2d_dgrad(const float* dy, const float* w, float* dx, int N,
 }
 
 // 2x2/stride-2 max pool with argmax code (0..3 = dy*2+dx; first maximum wins)        [K2]
+// Inner loops run over the contiguous channel dimension with select-style updates (no branches), which
+// the compiler vectorises.
 B2C_API void b2c_maxpool2_fwd(const float* x, float* y, uint8_t* code, int N, int H, int W, int C) {
   const int PH = H / 2, PW = W / 2;
-  parallel_for((int64_t)N * PH, 8, [&](int64_t b, int64_t e) {
+  parallel_for((int64_t)N * PH, 4, [&](int64_t b, int64_t e) {
     for (int64_t r = b; r < e; ++r) {
       const int n = r / PH, ph = r % PH;
-      for (int pw = 0; pw < PW; ++pw)
+      for (int pw = 0; pw < PW; ++pw) {
+        const float* __restrict__ p00 = x + (((int64_t)n * H + 2 * ph) * W + 2 * pw) * C;
+        const float* __restrict__ p01 = p00 + C;
+        const float* __restrict__ p10 = p00 + (int64_t)W * C;
+        const float* __restrict__ p11 = p10 + C;
+        float* __restrict__ yo = y + (((int64_t)n * PH + ph) * PW + pw) * C;
+        uint8_t* __restrict__ co = code + (((int64_t)n * PH + ph) * PW + pw) * C;
         for (int c = 0; c < C; ++c) {
-          const float* p = x + (((int64_t)n * H + 2 * ph) * W + 2 * pw) * C + c;
-          float best = p[0];
+          float best = p00[c];
           int arg = 0;
-          if (p[C] > best) best = p[C], arg = 1;
-          if (p[(int64_t)W * C] > best) best = p[(int64_t)W * C], arg = 2;
-          if (p[(int64_t)W * C + C] > best) best = p[(int64_t)W * C + C], arg = 3;
-          const int64_t o = (((int64_t)n * PH + ph) * PW + pw) * C + c;
-          y[o] = best;
-          code[o] = (uint8_t)arg;
+          const float v1 = p01[c], v2 = p10[c], v3 = p11[c];
+          arg = v1 > best ? 1 : arg, best = v1 > best ? v1 : best;
+          arg = v2 > best ? 2 : arg, best = v2 > best ? v2 : best;
+          arg = v3 > best ? 3 : arg, best = v3 > best ? v3 : best;
+          yo[c] = best;
+          co[c] = (uint8_t)arg;
         }
+      }
     }
   });
 }
@@ -186,50 +358,106 @@ B2C_API void b2c_maxpool2_fwd(const float* x, float* y, uint8_t* code, int N, in
 B2C_API void b2c_maxpool2_bwd(const float* dy, const uint8_t* code, const float* y_pooled, float* dx,
                               int N, int H, int W, int C, int act_relu) {
   const int PH = H / 2, PW = W / 2;
-  parallel_for((int64_t)N * H, 8, [&](int64_t b, int64_t e) {
+  parallel_for((int64_t)N * H, 4, [&](int64_t b, int64_t e) {
     for (int64_t r = b; r < e; ++r) {
       const int n = r / H, hh = r % H;
-      for (int w = 0; w < W; ++w)
-        for (int c = 0; c < C; ++c) {
-          const int ph = hh >> 1, pw = w >> 1;
-          float g = 0.f;
-          if (ph < PH && pw < PW) {
-            const int64_t o = (((int64_t)n * PH + ph) * PW + pw) * C + c;
-            if (code[o] == ((hh & 1) * 2 + (w & 1)) && !(act_relu && !(y_pooled[o] > 0.f))) g = dy[o];
-          }
-          dx[(((int64_t)n * H + hh) * W + w) * C + c] = g;
+      const int ph = hh >> 1;
+      for (int w = 0; w < W; ++w) {
+        float* __restrict__ dxo = dx + (((int64_t)n * H + hh) * W + w) * C;
+        const int pw = w >> 1;
+        if (ph >= PH || pw >= PW) {          // odd trailing row / column: outside every window
+          for (int c = 0; c < C; ++c) dxo[c] = 0.f;
+          continue;
         }
+        const int64_t o = (((int64_t)n * PH + ph) * PW + pw) * C;
+        const float* __restrict__ g = dy + o;
+        const uint8_t* __restrict__ cd = code + o;
+        const float* __restrict__ yp = y_pooled + o;
+        const int me = (hh & 1) * 2 + (w & 1);
+        if (act_relu) {
+          for (int c = 0; c < C; ++c) dxo[c] = (cd[c] == me && yp[c] > 0.f) ? g[c] : 0.f;
+        } else {
+          for (int c = 0; c < C; ++c) dxo[c] = cd[c] == me ? g[c] : 0.f;
+        }
+      }
     }
   });
 }
 
 // D[m,:] (+)= act(A[m,:] . B + bias), arbitrary strides so one routine serves forward
 // (x.W), dgrad (dy.W^T) and wgrad (x^T.dy).                                      [K3/K4/K6/K7]
+// B is first packed into zero-padded panels of kNR columns ([panel][k][kNR], contiguous), then a
+// kMR x kNR register tile walks K: two 8-float vectors of B and one broadcast of A per FMA row, which the
+// compiler turns into AVX2 FMAs without reassociating any sum (every output is accumulated in k order, so
+// the result does not depend on the thread count and is identical on every worker).
+namespace {
+constexpr int kMR = 4, kNR = 16;
+
+// GCC vector extension: 8 floats; the unaligned variant is for loads from the packed panels.
+typedef float v8 __attribute__((vector_size(32)));
+typedef float v8u __attribute__((vector_size(32), aligned(4)));
+
+inline void gemm_tile(const float* A, int64_t sam, int64_t sak, const float* panel, int K, int rows,
+                      float (&c)[kMR][kNR]) {
+  const float* a0 = A;
+  const float* a1 = A + (rows > 1 ? 1 : 0) * sam;
+  const float* a2 = A + (rows > 2 ? 2 : 0) * sam;
+  const float* a3 = A + (rows > 3 ? 3 : 0) * sam;
+  v8 c00 = *reinterpret_cast<const v8u*>(&c[0][0]), c01 = *reinterpret_cast<const v8u*>(&c[0][8]);
+  v8 c10 = *reinterpret_cast<const v8u*>(&c[1][0]), c11 = *reinterpret_cast<const v8u*>(&c[1][8]);
+  v8 c20 = *reinterpret_cast<const v8u*>(&c[2][0]), c21 = *reinterpret_cast<const v8u*>(&c[2][8]);
+  v8 c30 = *reinterpret_cast<const v8u*>(&c[3][0]), c31 = *reinterpret_cast<const v8u*>(&c[3][8]);
+  for (int k = 0; k < K; ++k) {
+    const v8 b0 = *reinterpret_cast<const v8u*>(panel + (int64_t)k * kNR);
+    const v8 b1 = *reinterpret_cast<const v8u*>(panel + (int64_t)k * kNR + 8);
+    const float s0 = a0[k * sak], s1 = a1[k * sak], s2 = a2[k * sak], s3 = a3[k * sak];
+    const v8 v0 = {s0, s0, s0, s0, s0, s0, s0, s0}, v1 = {s1, s1, s1, s1, s1, s1, s1, s1};
+    const v8 v2 = {s2, s2, s2, s2, s2, s2, s2, s2}, v3 = {s3, s3, s3, s3, s3, s3, s3, s3};
+    c00 += v0 * b0, c01 += v0 * b1;
+    c10 += v1 * b0, c11 += v1 * b1;
+    c20 += v2 * b0, c21 += v2 * b1;
+    c30 += v3 * b0, c31 += v3 * b1;
+  }
+  *reinterpret_cast<v8u*>(&c[0][0]) = c00, *reinterpret_cast<v8u*>(&c[0][8]) = c01;
+  *reinterpret_cast<v8u*>(&c[1][0]) = c10, *reinterpret_cast<v8u*>(&c[1][8]) = c11;
+  *reinterpret_cast<v8u*>(&c[2][0]) = c20, *reinterpret_cast<v8u*>(&c[2][8]) = c21;
+  *reinterpret_cast<v8u*>(&c[3][0]) = c30, *reinterpret_cast<v8u*>(&c[3][8]) = c31;
+}
+}  // namespace
+
 B2C_API void b2c_gemm(const float* A, int64_t sam, int64_t sak, const float* B, int64_t sbk,
                       int64_t sbn, float* D, int64_t ldd, const float* bias, int M, int N, int K,
                       int relu, int accumulate) {
-  parallel_for(M, 4, [&](int64_t b, int64_t e) {
-    std::vector<float> acc(N);
-    for (int64_t m = b; m < e; ++m) {
-      for (int n = 0; n < N; ++n) acc[n] = bias ? bias[n] : 0.f;
-      if (sbn == 1) {
-        for (int k = 0; k < K; ++k) {
-          const float av = A[m * sam + k * sak];
-          const float* br = B + k * sbk;
-          for (int n = 0; n < N; ++n) acc[n] += av * br[n];
-        }
-      } else {
-        for (int n = 0; n < N; ++n) {
-          float a = 0.f;
-          const float* bc = B + n * sbn;
-          for (int k = 0; k < K; ++k) a += A[m * sam + k * sak] * bc[k * sbk];
-          acc[n] += a;
-        }
+  const int panels = (N + kNR - 1) / kNR;
+  std::vector<float> packed((size_t)panels * K * kNR);
+  parallel_for(panels, 1, [&](int64_t p0, int64_t p1) {
+    for (int64_t p = p0; p < p1; ++p) {
+      float* dst = packed.data() + p * (int64_t)K * kNR;
+      const int n0 = (int)p * kNR, nr = std::min(kNR, N - n0);
+      for (int k = 0; k < K; ++k) {
+        const float* src = B + k * sbk + (int64_t)n0 * sbn;
+        for (int j = 0; j < nr; ++j) dst[k * kNR + j] = src[j * sbn];
+        for (int j = nr; j < kNR; ++j) dst[k * kNR + j] = 0.f;
       }
-      float* dr = D + m * ldd;
-      for (int n = 0; n < N; ++n) {
-        const float v = relu ? std::max(acc[n], 0.f) : acc[n];
-        dr[n] = accumulate ? dr[n] + v : v;
+    }
+  });
+  const int mblocks = (M + kMR - 1) / kMR;
+  // one task = one (panel, row block); panels outermost so a thread keeps its B panel in cache
+  parallel_for((int64_t)panels * mblocks, 8, [&](int64_t t0, int64_t t1) {
+    for (int64_t t = t0; t < t1; ++t) {
+      const int p = (int)(t / mblocks), mb = (int)(t % mblocks);
+      const int m0 = mb * kMR, rows = std::min(kMR, M - m0);
+      const int n0 = p * kNR, nr = std::min(kNR, N - n0);
+      float c[kMR][kNR];
+      for (int r = 0; r < kMR; ++r)
+        for (int j = 0; j < kNR; ++j) c[r][j] = (bias != nullptr && j < nr) ? bias[n0 + j] : 0.f;
+      gemm_tile(A + (int64_t)m0 * sam, sam, sak, packed.data() + (int64_t)p * K * kNR, K, rows, c);
+      for (int r = 0; r < rows; ++r) {
+        float* dr = D + (int64_t)(m0 + r) * ldd + n0;
+        for (int j = 0; j < nr; ++j) {
+          const float v = relu ? std::max(c[r][j], 0.f) : c[r][j];
+          dr[j] = accumulate ? dr[j] + v : v;
+        }
       }
     }
   });
