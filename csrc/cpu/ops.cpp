@@ -28,6 +28,7 @@
 namespace {
 
 int g_threads = 0;
+int g_cpu_offset = -1;   // index (into the affinity mask) of the CPU the calling thread's share starts at
 
 int num_threads() {
   if (g_threads > 0) return g_threads;
@@ -102,7 +103,8 @@ class Pool {
     for (int c = 0; c < CPU_SETSIZE; ++c)
       if (CPU_ISSET(c, &allowed)) cpus.push_back(c);
     if (cpus.size() < 2) return;
-    const size_t off = static_cast<size_t>(getpid()) % cpus.size();
+    const size_t off = g_cpu_offset >= 0 ? static_cast<size_t>(g_cpu_offset) % cpus.size()
+                                         : static_cast<size_t>(getpid()) % cpus.size();
     cpu_set_t one;
     CPU_ZERO(&one);
     CPU_SET(cpus[(off + id + 1) % cpus.size()], &one);
@@ -181,6 +183,9 @@ ConvShape make_shape(int N, int H, int W, int Ci, int Co, int KH, int KW, int sh
 }  // namespace
 
 B2C_API void b2c_set_num_threads(int n) { g_threads = n; }
+// Several worker processes on one host: give each `threads` CPUs starting at index `first_cpu` of the
+// affinity mask (call before the first op; the worker pool pins its threads when it creates them).
+B2C_API void b2c_set_thread_layout(int threads, int first_cpu) { g_threads = threads, g_cpu_offset = first_cpu; }
 
 // y[n,oh,ow,:] = act(b + sum_{kh,kw,ci} x[n,ih,iw,ci] * w[kh,kw,ci,:])               [K1]
 B2C_API void b2c_conv2d_fwd(const float* x, const float* w, const float* bias, float* y, int N, int H,

@@ -18,6 +18,8 @@ def lib():
         vp, i, f, i64, d = C.c_void_p, C.c_int, C.c_float, C.c_int64, C.c_double
         conv = [i] * 13
         l.b2c_set_num_threads.argtypes = [i]
+        l.b2c_set_thread_layout.argtypes = [i, i]
+        l.b2c_set_thread_layout.restype = None
         l.b2c_conv2d_fwd.argtypes = [vp, vp, vp, vp, *conv, i]
         l.b2c_conv2d_wgrad.argtypes = [vp, vp, vp, vp, *conv]
         l.b2c_conv2d_dgrad.argtypes = [vp, vp, vp, *conv]

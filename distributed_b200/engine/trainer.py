@@ -64,6 +64,7 @@ class Trainer:
         else:
             from .cpu_backend import CpuBackend
             self.be = CpuBackend()
+            self._cpu_thread_layout(strategy)
         self.comm = strategy.make_comm(self.layout.n_total, self.be)
         self.params = self.comm.alloc(self.layout.n_total, self.be)
         self.use_graph = bool(use_graph and self.backend_name == "cuda" and self.comm.capturable)
@@ -79,6 +80,20 @@ class Trainer:
             raise RuntimeError("replicas were not initialised identically (mirrored variables differ)")
         self._exec = None
         self._build()
+
+    @staticmethod
+    def _cpu_thread_layout(strategy):
+        """Co-located CPU workers (the reference's multi-worker run on one host, BASELINE config 1) share the
+        cores: worker r gets cores // world pool threads pinned to its own slice, instead of every worker
+        spawning one thread per core.  B200DIST_CPU_THREADS overrides the per-worker thread count."""
+        import os
+        from .._native import cpu_lib
+        world, rank = int(strategy.num_replicas_in_sync), int(getattr(strategy, "rank", 0))
+        cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+        threads = int(os.environ.get("B200DIST_CPU_THREADS", "0")) or max(1, min(8, cores // max(world, 1)))
+        if world > 1 or "B200DIST_CPU_THREADS" in os.environ:
+            # slot 0 of the slice stays free for the (unpinned) calling thread: workers start one further on
+            cpu_lib.lib().b2c_set_thread_layout(threads, (rank * threads) % max(cores, 1))
 
     # ------------------------------------------------------------------------------
     def _io_buffers(self):

@@ -327,6 +327,8 @@ int b2d_host_free(void* p);
  * CPU backend (libb200dist_cpu.so): C++ reference ops + shared-memory fused all-reduce/SGD.
  * ------------------------------------------------------------------------------------- */
 void b2c_set_num_threads(int n);
+/* co-located worker processes: `threads` pool threads pinned to CPUs first_cpu.. of the affinity mask */
+void b2c_set_thread_layout(int threads, int first_cpu);
 /* ph, pw = padding at the top / left; OH, OW = output size (<= 0: derive from symmetric padding). */
 void b2c_conv2d_fwd(const float* x, const float* w, const float* bias, float* y, int N, int H, int W,
                     int Ci, int Co, int KH, int KW, int sh, int sw, int ph, int pw, int OH, int OW, int relu);
