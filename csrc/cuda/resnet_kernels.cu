@@ -708,6 +708,17 @@ typedef __nv_bfloat16 bf16_t;
 
 static inline int vec_of(int dtype) { return dtype == B2D_F32 ? 4 : 8; }
 constexpr int kReduceCtas = 148 * 2;
+// Reduction kernels end in atomics on 2C floats: few fat CTAs when those floats are a handful of L2 lines
+// (C <= 128), more CTAs (better latency hiding: the kernels run at ~25 % occupancy) when they spread out.
+// B2D_BN_REDUCE_CTAS_PER_SM overrides the per-SM count for wide tensors (default 2 = same as narrow).
+static int reduce_ctas(int C) {
+  static const int wide = [] {
+    const char* e = getenv("B2D_BN_REDUCE_CTAS_PER_SM");
+    const int v = e != nullptr ? atoi(e) : 2;
+    return v >= 1 && v <= 8 ? v : 2;
+  }();
+  return C <= 128 ? kReduceCtas : 148 * wide;
+}
 
 static int fill_bn_args(const b2d_bn_desc& d, BnArgs* a) {
   B2D_DTYPE_OK(d.dtype);
@@ -738,7 +749,7 @@ extern "C" int b2d_bn_forward(const b2d_bn_desc* dp, void* stream) {
                   (d.moving_mean_grad == nullptr || (d.moving_mean && d.moving_var)),
               "bn_forward: inconsistent moving-statistics pointers");
   const ChanGrid g = chan_grid(d.M, d.C, vec_of(d.dtype));
-  const ChanGrid gr = chan_grid(d.M, d.C, vec_of(d.dtype), kReduceCtas);
+  const ChanGrid gr = chan_grid(d.M, d.C, vec_of(d.dtype), reduce_ctas(d.C));
   a.rows_per_cta = g.rows_per_cta, a.lanes_c = g.lanes_c;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (d.dtype == B2D_F32) {
@@ -766,7 +777,7 @@ extern "C" int b2d_bn_backward(const b2d_bn_desc* dp, void* stream) {
   if (d.residual != nullptr) a.relu = 0;   // dy is already the gradient of the pre-activation sum
   B2D_REQUIRE(!a.relu || d.beta, "bn_backward: the ReLU mask is recomputed from x and needs beta");
   const ChanGrid g = chan_grid(d.M, d.C, vec_of(d.dtype));
-  const ChanGrid gr = chan_grid(d.M, d.C, vec_of(d.dtype), kReduceCtas);
+  const ChanGrid gr = chan_grid(d.M, d.C, vec_of(d.dtype), reduce_ctas(d.C));
   a.rows_per_cta = g.rows_per_cta, a.lanes_c = g.lanes_c;
   BnArgs ar = a;
   ar.rows_per_cta = gr.rows_per_cta;
@@ -933,7 +944,7 @@ extern "C" int b2d_colsum_t(int dtype, const void* dy, float* db, int M, int C, 
   B2D_DTYPE_OK(dtype);
   const int V = vec_of(dtype);
   B2D_REQUIRE(C % V == 0, "colsum: C (%d) must be a multiple of %d", C, V);
-  const ChanGrid g = chan_grid(M, C, V, kReduceCtas);
+  const ChanGrid g = chan_grid(M, C, V, reduce_ctas(C));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (dtype == B2D_F32)
     B2D_CUDA_CHECK(launch_pdl(col_stats_kernel<float, false>, g.grid, dim3(256), 0, st, static_cast<const float*>(dy), db,
