@@ -187,11 +187,80 @@ B2C_API void b2c_set_num_threads(int n) { g_threads = n; }
 // affinity mask (call before the first op; the worker pool pins its threads when it creates them).
 B2C_API void b2c_set_thread_layout(int threads, int first_cpu) { g_threads = threads, g_cpu_offset = first_cpu; }
 
+B2C_API void b2c_gemm(const float* A, int64_t sam, int64_t sak, const float* B, int64_t sbk, int64_t sbn,
+                      float* D, int64_t ldd, const float* bias, int M, int N, int K, int relu, int accumulate);
+
+namespace {
+// Convolutions with a reduction of at least kGemmConvK go through a patch matrix and the tiled GEMM
+// (col[pixel][(kh, kw, ci)] matches the row order of the HWIO filter viewed as [KH*KW*Ci][Co]); the tiny
+// first-layer filters (README: K = 9) keep the direct loops below.
+constexpr int kGemmConvK = 32;
+
+void im2col(const float* x, float* col, const ConvShape& s) {
+  const int K = s.KH * s.KW * s.Ci;
+  parallel_for((int64_t)s.N * s.OH, 2, [&](int64_t b, int64_t e) {
+    for (int64_t r = b; r < e; ++r) {
+      const int n = r / s.OH, oh = r % s.OH;
+      for (int ow = 0; ow < s.OW; ++ow) {
+        float* dst = col + ((r * s.OW) + ow) * (int64_t)K;
+        for (int kh = 0; kh < s.KH; ++kh) {
+          const int ih = oh * s.sh - s.ph + kh;
+          for (int kw = 0; kw < s.KW; ++kw) {
+            const int iw = ow * s.sw - s.pw + kw;
+            float* d = dst + (int64_t)(kh * s.KW + kw) * s.Ci;
+            if (ih < 0 || ih >= s.H || iw < 0 || iw >= s.W) {
+              for (int ci = 0; ci < s.Ci; ++ci) d[ci] = 0.f;
+            } else {
+              const float* src = x + (((int64_t)n * s.H + ih) * s.W + iw) * s.Ci;
+              for (int ci = 0; ci < s.Ci; ++ci) d[ci] = src[ci];
+            }
+          }
+        }
+      }
+    }
+  });
+}
+
+// dx[n, ih, iw, :] += dcol entries of every (output pixel, tap) that read it; one image per task.
+void col2im(const float* dcol, float* dx, const ConvShape& s) {
+  const int K = s.KH * s.KW * s.Ci;
+  parallel_for(s.N, 1, [&](int64_t b, int64_t e) {
+    for (int64_t n = b; n < e; ++n) {
+      float* img = dx + n * (int64_t)s.H * s.W * s.Ci;
+      for (int64_t i = 0; i < (int64_t)s.H * s.W * s.Ci; ++i) img[i] = 0.f;
+      for (int oh = 0; oh < s.OH; ++oh)
+        for (int ow = 0; ow < s.OW; ++ow) {
+          const float* src = dcol + (((n * s.OH) + oh) * s.OW + ow) * (int64_t)K;
+          for (int kh = 0; kh < s.KH; ++kh) {
+            const int ih = oh * s.sh - s.ph + kh;
+            if (ih < 0 || ih >= s.H) continue;
+            for (int kw = 0; kw < s.KW; ++kw) {
+              const int iw = ow * s.sw - s.pw + kw;
+              if (iw < 0 || iw >= s.W) continue;
+              float* d = img + ((int64_t)ih * s.W + iw) * s.Ci;
+              const float* g = src + (int64_t)(kh * s.KW + kw) * s.Ci;
+              for (int ci = 0; ci < s.Ci; ++ci) d[ci] += g[ci];
+            }
+          }
+        }
+    }
+  });
+}
+}  // namespace
+
 // y[n,oh,ow,:] = act(b + sum_{kh,kw,ci} x[n,ih,iw,ci] * w[kh,kw,ci,:])               [K1]
 B2C_API void b2c_conv2d_fwd(const float* x, const float* w, const float* bias, float* y, int N, int H,
                             int W, int Ci, int Co, int KH, int KW, int sh, int sw, int ph, int pw,
                             int OH, int OW, int relu) {
   const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw, OH, OW);
+  if (KH * KW * Ci >= kGemmConvK) {
+    const int K = KH * KW * Ci;
+    const int64_t pix = (int64_t)N * s.OH * s.OW;
+    std::vector<float> col((size_t)pix * K);
+    im2col(x, col.data(), s);
+    b2c_gemm(col.data(), K, 1, w, Co, 1, y, Co, bias, (int)pix, Co, K, relu, 0);
+    return;
+  }
   parallel_for((int64_t)N * s.OH, 4, [&](int64_t b, int64_t e) {
     std::vector<float> acc(Co);
     for (int64_t r = b; r < e; ++r) {
@@ -226,6 +295,18 @@ B2C_API void b2c_conv2d_wgrad(const float* x, const float* dy, float* dw, float*
                               int OH, int OW) {
   const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw, OH, OW);
   const int64_t taps = (int64_t)KH * KW * Ci;
+  if (taps >= kGemmConvK) {
+    // dW[K, Co] += col^T . dy ; db += column sums of dy
+    const int K = (int)taps;
+    const int64_t pix = (int64_t)N * s.OH * s.OW;
+    std::vector<float> col((size_t)pix * K);
+    im2col(x, col.data(), s);
+    b2c_gemm(col.data(), 1, K, dy, Co, 1, dw, Co, nullptr, K, Co, (int)pix, 0, 1);
+    if (db != nullptr)
+      for (int64_t r = 0; r < pix; ++r)
+        for (int c = 0; c < Co; ++c) db[c] += dy[r * Co + c];
+    return;
+  }
   if (taps * Co <= 16384 && N >= 2) {
     // Small filter (e.g. the README's 3x3x1x32): the reduction runs over many pixels and few taps, so the
     // work is split over fixed groups of images, each into its own partial filter, and the partials are
@@ -298,6 +379,15 @@ B2C_API void b2c_conv2d_wgrad(const float* x, const float* dy, float* dw, float*
 B2C_API void b2c_conv2d_dgrad(const float* dy, const float* w, float* dx, int N, int H, int W, int Ci,
                               int Co, int KH, int KW, int sh, int sw, int ph, int pw, int OH, int OW) {
   const ConvShape s = make_shape(N, H, W, Ci, Co, KH, KW, sh, sw, ph, pw, OH, OW);
+  if (KH * KW * Ci >= kGemmConvK) {
+    // dcol[pix, K] = dy[pix, Co] . W^T, then scattered back onto the input pixels
+    const int K = KH * KW * Ci;
+    const int64_t pix = (int64_t)N * s.OH * s.OW;
+    std::vector<float> dcol((size_t)pix * K);
+    b2c_gemm(dy, Co, 1, w, 1, Co, dcol.data(), K, nullptr, (int)pix, K, Co, 0, 0);
+    col2im(dcol.data(), dx, s);
+    return;
+  }
   parallel_for((int64_t)N * H, 4, [&](int64_t b, int64_t e) {
     for (int64_t r = b; r < e; ++r) {
       const int n = r / H, ih = r % H;

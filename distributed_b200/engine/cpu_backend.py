@@ -20,7 +20,8 @@ class CpuBackend:
         return False
 
     def describe_conv(self, layer):
-        return "C++ direct conv"
+        k = layer.kernel_size[0] * layer.kernel_size[1] * layer.input_shape[2]
+        return "C++ im2col + tiled GEMM" if k >= 32 else "C++ direct conv"
 
     def describe_dense(self, b, k, n):
         return "C++ gemm"
