@@ -258,6 +258,29 @@ class _Lowerer:
                 i += 1
                 continue
 
+            if isinstance(layer, L.Activation):
+                # stand-alone activation (one that could not be folded into its producer, e.g. after a pooling
+                # layer or a residual block): y = relu(x); the consumer masks dy with y > 0 (post_relu), so the
+                # backward pass is a copy
+                if layer.activation is None or st.post_relu:
+                    i += 1                              # identity / relu(relu(x)): nothing to do
+                    continue
+                if layer.activation != "relu":
+                    raise NotImplementedError(f"activation {layer.activation!r} is not supported")
+                if st.cur.dim() != 4:
+                    raise NotImplementedError("a stand-alone ReLU is supported on 4-D activations only; "
+                                              "pass activation='relu' to the Dense layer instead")
+                shape = tuple(st.cur.shape)
+                y = be.alloc(shape, st.cur.dtype)
+                dy = (fdy if fdy is not None else be.alloc(shape, st.cur.dtype)) if training else None
+                prog.forward.append(be.add_act(st.cur, None, y, 1))
+                if training:
+                    self.stages.append([be.add_act(dy, None, st.d_cur, 0)] if st.d_cur is not None else [])
+                prog.description.append(f"relu -> {shape}")
+                st = _State(y, dy, True)
+                i += 1
+                continue
+
             if isinstance(layer, L.Dense):
                 if st.cur.dim() != 2 or st.cur.dtype != torch.float32:
                     raise ValueError("Dense expects a flattened fp32 input: put Flatten or "

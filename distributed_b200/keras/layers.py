@@ -254,8 +254,8 @@ class Residual(Layer):
 
     def __init__(self, main, shortcut=None, activation="relu", **kw):
         super().__init__(**kw)
-        self.main = list(main)
-        self.shortcut = list(shortcut) if shortcut else []
+        self.main = fold_activations(main)
+        self.shortcut = fold_activations(shortcut) if shortcut else []
         self.activation = _norm_activation(activation)
 
     def sublayers(self):
@@ -279,6 +279,19 @@ class Residual(Layer):
 
     def param_specs(self):
         return [s for l in self.sublayers() for s in l.param_specs()]
+
+
+def fold_activations(layers):
+    """An Activation that follows a Conv2D / Dense / BatchNormalization without one becomes that layer's
+    fused activation (the same rule ``Sequential.add`` applies); any other Activation stays a layer."""
+    out = []
+    for l in layers:
+        if (type(l).__name__ in ("Activation", "ReLU") and out and getattr(out[-1], "activation", "x") is None
+                and type(out[-1]).__name__ in ("Conv2D", "Dense", "BatchNormalization")):
+            out[-1].activation = l.activation
+        else:
+            out.append(l)
+    return out
 
 
 def flatten_layers(layers):

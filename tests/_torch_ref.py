@@ -70,7 +70,13 @@ def torch_forward(w, x, model, training=True, running=None, emulate_bf16=False):
             elif isinstance(layer, L.Residual):
                 m = run(layer.main, t)
                 sc = run(layer.shortcut, t) if layer.shortcut else t
-                t = q(torch.relu(m + sc))
+                t = m + sc
+                if layer.activation == "relu":
+                    t = torch.relu(t)
+                t = q(t)
+            elif isinstance(layer, L.Activation):
+                if layer.activation == "relu":
+                    t = torch.relu(t)
             elif isinstance(layer, L.GlobalAveragePooling2D):
                 t = t.mean((2, 3))
             elif isinstance(layer, L.Flatten):
@@ -82,4 +88,6 @@ def torch_forward(w, x, model, training=True, running=None, emulate_bf16=False):
             else:
                 raise AssertionError(type(layer))
         return t
-    return run(model.layers, x)
+    # contiguous NCHW: PyTorch 2.11's CPU convolution backward returns run-to-run different (wrong) weight
+    # gradients — and occasionally crashes — for a strided 1x1 convolution fed by a permuted NHWC view
+    return run(model.layers, x.contiguous())
