@@ -26,12 +26,18 @@ def _build(tf, L, draw):
     c = draw(st.sampled_from([4, 8]))
     layers.append(conv(c, draw(st.sampled_from([1, 3])), relu=draw(st.booleans()), bias=draw(st.booleans())))
     for _ in range(draw(st.integers(1, 3))):
-        kind = draw(st.sampled_from(["conv", "bn", "pool", "res_id", "res_proj"]))
+        kind = draw(st.sampled_from(["conv", "conv_valid", "bn", "pool", "relu", "res_id", "res_proj"]))
         if kind == "conv":
             stride = draw(st.sampled_from([1, 2])) if hw >= 6 else 1
             c2 = draw(st.sampled_from([4, 8]))
             layers.append(conv(c2, draw(st.sampled_from([1, 3])), stride, "same", draw(st.booleans()), draw(st.booleans())))
             c, hw = c2, -(-hw // stride)
+        elif kind == "conv_valid" and hw >= 5:
+            c2 = draw(st.sampled_from([4, 8]))
+            layers.append(conv(c2, 3, 1, "valid", draw(st.booleans()), draw(st.booleans())))
+            c, hw = c2, hw - 2
+        elif kind == "relu":
+            layers.append(L.ReLU())          # folded into a producer without activation, else a stand-alone layer
         elif kind == "bn":
             layers.append(L.BatchNormalization(momentum=0.9))
             if draw(st.booleans()):
