@@ -111,3 +111,40 @@ def test_batchnorm_moving_statistics_are_averaged_over_replicas():
     # moving_mean = 0.5 * 0 + 0.5 * mean over replicas of the per-replica batch mean
     expect = 0.5 * np.mean(np.asarray(r[0]["shard_means"]), axis=0)
     assert np.allclose(r[0]["mm"], expect, atol=1e-5)
+
+
+def _train_residual(ctx, num_workers, per_worker):
+    """A residual network without BatchNorm (so that N x B and 1 x NB are the same mathematics)."""
+    import os
+    os.environ["B200DIST_BACKEND"] = "cpu"
+    os.environ["TF_CONFIG"] = json.dumps(ctx.tf_config(base_port=int(ctx.address[0].split(":")[1]) % 20000 + 20000))
+    import numpy as np
+    import distributed_b200 as tf
+    L = tf.keras.layers
+    strategy = tf.distribute.experimental.MultiWorkerMirroredStrategy()
+    rng = np.random.default_rng(9)
+    gb = per_worker * num_workers
+    x = rng.standard_normal((gb * 3, 10, 10, 3)).astype(np.float32)
+    y = rng.integers(0, 4, len(x))
+    with strategy.scope():
+        model = tf.keras.Sequential([
+            L.Conv2D(8, 3, padding="same", activation="relu", input_shape=(10, 10, 3)),
+            L.Residual([L.Conv2D(4, 1, activation="relu"), L.Conv2D(8, 3, padding="same")]),
+            L.MaxPooling2D(),
+            L.Residual([L.Conv2D(4, 1, activation="relu"), L.Conv2D(16, 3, strides=2, padding="same")],
+                       [L.Conv2D(16, 1, strides=2, padding="same", use_bias=False)]),
+            L.GlobalAveragePooling2D(), L.Dense(4)])
+        model.compile(loss=tf.keras.losses.SparseCategoricalCrossentropy(from_logits=True),
+                      optimizer=tf.keras.optimizers.SGD(0.05), metrics=["accuracy"])
+    h = model.fit(x, y, batch_size=gb, epochs=1, steps_per_epoch=3, verbose=0)
+    return json.dumps({"loss": h.history["loss"],
+                       "digest": [float(np.abs(a).astype(np.float64).sum()) for a in model.get_weights()]})
+
+
+def test_residual_network_two_workers_equal_one_worker():
+    two = [json.loads(s) for s in barrier_apply(lambda ctx: _train_residual(ctx, 2, 6), 2, timeout=300)]
+    one = json.loads(barrier_apply(lambda ctx: _train_residual(ctx, 1, 12), 1, timeout=300)[0])
+    assert two[0] == two[1]                                        # mirrored: identical loss and weights
+    assert abs(two[0]["loss"][0] - one["loss"][0]) < 1e-4
+    for a, b in zip(two[0]["digest"], one["digest"]):
+        assert abs(a - b) <= 1e-4 * max(abs(a), 1.0)
