@@ -36,12 +36,15 @@ def run(args, ClockSampler, dist_env, max_over_ranks, barrier) -> dict:
     torch.backends.cudnn.allow_tf32 = True
     torch.backends.cuda.matmul.allow_tf32 = True
     torch.backends.cudnn.benchmark = True
+    pg = None
     if world > 1 and not dist.is_initialized():
         dist.init_process_group("cpu:gloo,cuda:nccl", device_id=dev)    # gloo only for the timing reductions
+    elif world > 1 and "nccl" not in str(dist.get_backend()):
+        pg = dist.new_group(backend="nccl")      # same process as the framework's arm (gloo control plane)
     torch.manual_seed(0)
     model = build_model(args.model).to(dev)
     if world > 1:
-        model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local])
+        model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local], process_group=pg)
     opt = torch.optim.SGD(model.parameters(), lr=1e-3)
     per_gpu = args.batch_per_gpu
     global_batch = per_gpu * world

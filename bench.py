@@ -43,7 +43,7 @@ class ClockSampler:
     REASONS = {"hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40,
                "hw_power_brake_slowdown": 0x80, "sw_power_cap": 0x4}
 
-    def __init__(self, index: int, period_ms: float = 4.0):
+    def __init__(self, index: int, period_ms: float = 0.5):
         self.index, self.period = index, period_ms / 1000.0
         self.sm: list[float] = []
         self.mask = 0
@@ -164,26 +164,32 @@ def run_ours(args) -> dict:
     torch.cuda.synchronize()
 
     # --- device-timed region: exactly K steps, CUDA events on the launching stream --------
-    launches0 = cuda_lib.launch_count()
+    # The processes leave the host barrier milliseconds apart, which is longer than the whole timed region
+    # of a short run.  ALIGN untimed steps are therefore enqueued on the same stream right before the start
+    # event, with no host synchronisation in between: their fused all-reduce lines the replicas up on the
+    # device, so the K timed steps are steady-state steps on every rank.
+    align = ALIGN_STEPS
     _barrier(world)
     torch.cuda.synchronize()
     with ClockSampler(local) as clocks:
-        ms = trainer.run_steps(x_dev, y_dev, model._global_step, steps_in_src, args.steps, global_batch, timed=True)
+        launches0 = cuda_lib.launch_count()
+        ms = trainer.run_steps(x_dev, y_dev, model._global_step, steps_in_src, args.steps, global_batch,
+                               timed=True, pre_steps=align)
         torch.cuda.synchronize()
-    _barrier(world)
-    launches = cuda_lib.launch_count() - launches0
-    model._global_step += args.steps
-    ms = _max_over_ranks(ms, world)
-    value = args.steps * global_batch / (ms / 1e3)
+        launches = (cuda_lib.launch_count() - launches0) * args.steps // (args.steps + align)
+        _barrier(world)
+        model._global_step += args.steps + align
+        ms = _max_over_ranks(ms, world)
+        value = args.steps * global_batch / (ms / 1e3)
 
-    # --- end to end through model.fit: per-step H2D from pinned memory + per-step D2H -------
-    _barrier(world)
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    hist = model.fit(x_host, y_host, batch_size=global_batch, epochs=1, steps_per_epoch=args.steps, verbose=0)
-    torch.cuda.synchronize()
-    e2e_s = _max_over_ranks(time.perf_counter() - t0, world)
-    e2e = args.steps * global_batch / e2e_s
+        # --- end to end through model.fit: per-step H2D from pinned memory + per-step D2H -------
+        _barrier(world)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        hist = model.fit(x_host, y_host, batch_size=global_batch, epochs=1, steps_per_epoch=args.steps, verbose=0)
+        torch.cuda.synchronize()
+        e2e_s = _max_over_ranks(time.perf_counter() - t0, world)
+        e2e = args.steps * global_batch / e2e_s
 
     out = {
         "metric": "images/sec (device-timed, max over ranks)", "value": value, "unit": "images/s",
@@ -199,7 +205,8 @@ def run_ours(args) -> dict:
                    "all_reduce": trainer.comm.description,
                    "l2_policy": f"inputs larger than L2: each step reads a fresh batch of a {n_images}-image "
                                 f"({n_images * row_bytes / 1e6:.0f} MB) data set",
-                   "kernels_per_step": trainer.kernels_per_step, "cuda_graph": trainer.use_graph},
+                   "kernels_per_step": trainer.kernels_per_step, "cuda_graph": trainer.use_graph,
+                   "rank_alignment": f"{align} untimed steps enqueued on the same stream before the start event"},
         "clocks": clocks.summary(),
         "e2e": {"value": e2e, "unit": "images/s", "h2d_bytes_per_step": per_gpu * row_bytes + per_gpu * 4,
                 "d2h_bytes_per_step": 16, "ms_per_step": 1e3 * e2e_s / args.steps,
@@ -207,8 +214,45 @@ def run_ours(args) -> dict:
         "gpu_launches": int(launches),
         "final_loss": hist.history["loss"][-1],
     }
+    # vs_baseline: value / the BASELINE.md section 3 number for this model and GPU count (stock PyTorch,
+    # cuDNN/cuBLAS + DDP/NCCL, best recorded arrangement).  The reference itself publishes nothing.
+    base = BASELINE_MD.get((args.model, world))
+    if base is not None and args.batch_per_gpu == DEFAULT_BATCH[args.model]:
+        out["vs_baseline"] = value / base
+        out["baseline_md_images_per_s"] = base
+    # Same-box baseline: the stock-PyTorch arm measured in this very process right after the framework's arm
+    # (same steps / warm-up / data policy / GPU count), so the line carries a ratio taken on this box.
+    if args.same_box_baseline:
+        model._trainer.close()
+        del x_dev, y_dev
+        torch.cuda.empty_cache()
+        same = {}
+        variants = [("eager", False)] + ([("graph", True)] if world == 1 else [])
+        for name, use_graph in variants:
+            try:
+                a2 = argparse.Namespace(**vars(args))
+                a2.torch_graph, a2.channels_last = use_graph, (args.dtype == "bf16")
+                a2.steps = min(args.steps, args.baseline_steps)
+                r = run_torch(a2)
+                if rank == 0:
+                    same[name] = {"value": r["value"], "ms_per_step": r["ms_per_step"], "e2e": r["e2e"]["value"],
+                                  "steps": a2.steps, "clocks": r["clocks"], "dtype": r["dtype"]}
+                    same[f"ratio_vs_{name}"] = value / r["value"]
+                    same[f"e2e_ratio_vs_{name}"] = e2e / r["e2e"]["value"]
+            except Exception as exc:                                   # the framework's own line must survive
+                same[name] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+        out["baseline_same_box"] = same
     return out if rank == 0 else {}
 
+
+# BASELINE.md section 3, stock PyTorch on the same 8 x B200 box (images/s; best recorded arrangement:
+# whole-step CUDA graph at 1 GPU, eager DDP/NCCL otherwise)
+BASELINE_MD = {("mnist_cnn", 1): 361255.0, ("mnist_cnn", 2): 154879.0, ("mnist_cnn", 4): 296761.0,
+               ("mnist_cnn", 8): 453330.0, ("scaled_cnn", 1): 503250.0, ("scaled_cnn", 8): 3665566.0,
+               ("resnet50", 1): 3151.0, ("resnet50", 8): 15868.0}
+DEFAULT_BATCH = {"mnist_cnn": 64, "scaled_cnn": 1024, "resnet50": 32}
+
+ALIGN_STEPS = 8      # untimed steps enqueued right before the start event (device-side rank alignment)
 
 MODEL_INPUT = {"mnist_cnn": ((28, 28, 1), 10), "scaled_cnn": ((28, 28, 1), 10), "resnet50": ((224, 224, 3), 1000)}
 MODEL_NAMES = {"mnist_cnn": "README MNIST CNN (conv32-3x3/maxpool/dense64/dense10, SGD lr=1e-3)",
@@ -242,13 +286,16 @@ def main():
                          "BASELINE.json names it, tf32-on-fp32 for the MNIST CNNs as the reference trains in float32)")
     ap.add_argument("--channels-last", action="store_true", help="torch baseline: channels_last + bf16 autocast")
     ap.add_argument("--torch-graph", action="store_true", help="torch baseline: capture the step in a CUDA graph")
+    ap.add_argument("--same-box-baseline", type=int, default=1,
+                    help="ours: also run the stock-PyTorch arm in this process and report the ratio (0 = skip)")
+    ap.add_argument("--baseline-steps", type=int, default=200, help="steps of the same-box baseline arm")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
     if args.dtype is None:
         args.dtype = "bf16" if args.model == "resnet50" else "tf32"
     if args.batch_per_gpu is None:
-        args.batch_per_gpu = 32 if args.model == "resnet50" else 64
+        args.batch_per_gpu = DEFAULT_BATCH[args.model] if args.model != "scaled_cnn" else 64
     if args.dataset_images is None:
         args.dataset_images = 512 if args.model == "resnet50" else 60000        # both > 126 MB of L2
     if args.impl == "reference":

@@ -23,6 +23,19 @@
 //
 // Cross-GPU barriers are per block: block b of every rank meets block b of every other rank
 // on monotone epoch counters in the peers' signal pads (st.release.sys / ld.acquire.sys).
+//
+// Step schedule with weight ping-pong (engine/trainer.py): step t reads W[t&1] and the update
+// writes W[(t+1)&1], so an update can never collide with a kernel of the same step that still
+// reads the weights.  The gradient buckets of the later layers are therefore reduced on a side
+// branch of the step graph as soon as their weight gradients are final, under the rest of the
+// backward pass; only the first layer's (small) bucket and the metric sums remain on the
+// critical path, and they travel by the LL kernel below: every rank pushes {value, epoch} pairs
+// as single 8-byte stores into the peers' inboxes, so the data is its own arrival flag (one
+// one-way NVLink trip, no separate barrier).  That exchange is also the step's closing barrier:
+// a peer's LL flag proves that all of its earlier kernels — including the ones that wrote into
+// this rank's next weight buffer — have completed.
+#include <cstdlib>
+
 #include "host_common.h"
 #include "ptx.cuh"
 
@@ -52,6 +65,12 @@ struct ArArgs {
   long long* dbg;             // optional timeline (globaltimer ns), 8 slots per block
   float* gz;                  // double-buffered gradients: the OTHER local buffer, zeroed during
                               // the reduction (null: single buffer, zeroed after a second barrier)
+  float* wo[kMaxRanks];       // where the updated weights go: == w (in place) or the other weight buffer
+  float* wo_mc;
+  int no_exit;                // 1: skip barrier B (a later kernel of the step closes it, see above)
+  int strict;                 // 1: entry barrier with st.release.sys / ld.acquire.sys
+  int debug;                  // B200DIST_AR_DEBUG: random delays, flag monotonicity checks, poison
+  long long timeout_ns;       // a barrier that waits longer than this traps (fail-stop)
 };
 
 __device__ __forceinline__ long long ar_time_ns() {
@@ -67,6 +86,18 @@ __device__ __forceinline__ long long ar_time_ns() {
 // announces were produced by earlier kernels and are already complete in this GPU's L2, which is
 // where peers read them — so a relaxed flag store and relaxed polling suffice (measured: 4.0 us
 // -> see profiles/).
+__device__ __forceinline__ uint32_t ar_hash(uint32_t x) {
+  x ^= x >> 16, x *= 0x7feb352dU, x ^= x >> 15, x *= 0x846ca68bU, x ^= x >> 16;
+  return x;
+}
+// Debug mode: a pseudo-random pause per (rank, block, epoch, phase) widens every race window.
+__device__ __forceinline__ void ar_debug_delay(const ArArgs& a, int rank, uint32_t epoch, int phase) {
+  if (a.debug && threadIdx.x == 0) {
+    const uint32_t h = ar_hash(rank * 0x9e3779b9U ^ blockIdx.x * 0x85ebca6bU ^ epoch * 0xc2b2ae35U ^ phase);
+    if ((h & 3) == 0) __nanosleep(h % 20000);
+  }
+}
+
 template <bool kPublish>
 __device__ __forceinline__ void rank_barrier(const ArArgs& a, int rank, uint32_t* s_epoch,
                                              long long* dbg = nullptr) {
@@ -79,6 +110,8 @@ __device__ __forceinline__ void rank_barrier(const ArArgs& a, int rank, uint32_t
   }
   __syncthreads();
   const uint32_t e = *s_epoch;
+  ar_debug_delay(a, rank, e, 0);
+  if (a.debug) __syncthreads();
   if (threadIdx.x < a.world) {
     const int p = threadIdx.x;
     if (kPublish)
@@ -87,12 +120,28 @@ __device__ __forceinline__ void rank_barrier(const ArArgs& a, int rank, uint32_t
       st_relaxed_sys(a.sig[p] + b * kMaxRanks + rank, e);
     if (dbg != nullptr && threadIdx.x == 0) dbg[0] = ar_time_ns();   // signals sent (dbg = &local[2])
     const uint32_t* mine = a.sig[rank] + b * kMaxRanks + p;
-    long long spins = 0;
-    while (static_cast<int32_t>((kPublish ? ld_acquire_sys(mine) : ld_relaxed_sys(mine)) - e) < 0) {
-      if (++spins > (1ll << 31)) {  // a peer died: fail loudly instead of hanging the GPU forever
-        printf("b200dist: rank %d block %d timed out waiting for rank %d (epoch %u)\n", rank, b, p, e);
+    long long t_start = 0;
+    uint32_t spins = 0, v;
+    // Polling with acquire costs nothing measurable (it only keeps the later loads behind it).
+    while (static_cast<int32_t>((v = ld_acquire_sys(mine)) - e) < 0) {
+      if ((++spins & 0x3ff) == 0) {  // a peer died: fail loudly instead of hanging the GPU forever
+        const long long now = ar_time_ns();
+        if (t_start == 0) t_start = now;
+        if (now - t_start > a.timeout_ns) {
+          printf("b200dist: rank %d block %d timed out waiting for rank %d (epoch %u, saw %u)\n", rank, b, p, e, v);
+          __trap();
+        }
+      }
+    }
+    if (a.debug) {
+      // Monotone epochs: a flag never runs backwards, and a peer can be at most one barrier ahead
+      // of this block (it cannot pass barrier e+1 before this block has signalled it).
+      uint32_t* seen = a.epoch[rank] + kMaxArBlocks + b * kMaxRanks + p;   // behind the epochs, same allocation
+      if (static_cast<int32_t>(v - *seen) < 0 || static_cast<int32_t>(v - e) > 1) {
+        printf("b200dist[debug]: rank %d block %d: flag of rank %d went %u -> %u at epoch %u\n", rank, b, p, *seen, v, e);
         __trap();
       }
+      *seen = v;
     }
   }
   __syncthreads();
@@ -126,7 +175,25 @@ __global__ void __launch_bounds__(kArThreads) allreduce_sgd_kernel(const ArArgs 
   pdl_wait();     // this replica's backward has finished writing its gradients
   pdl_trigger();
   if (dbg != nullptr && threadIdx.x == 0) s_t[1] = ar_time_ns();
-  rank_barrier<false>(a, rank, &s_epoch, dbg == nullptr ? nullptr : &s_t[2]);  // A: every replica's gradients are complete
+  // A: every replica's gradients are complete
+  if (a.strict)
+    rank_barrier<true>(a, rank, &s_epoch, dbg == nullptr ? nullptr : &s_t[2]);
+  else
+    rank_barrier<false>(a, rank, &s_epoch, dbg == nullptr ? nullptr : &s_t[2]);
+  ar_debug_delay(a, rank, s_epoch, 1);
+  if (a.debug) __syncthreads();
+  // Zeroing of the gradient buffer consumed one step ago.  Debug mode first poisons it and keeps the
+  // poison up for a while: a peer that still read it (a protocol violation) would turn its weights into NaNs.
+  auto zero_range = [&](float4* base, long long b4, long long e4) {
+    if (a.debug) {
+      const float4 poison = make_float4(__int_as_float(0x7fc0dead), __int_as_float(0x7fc0dead),
+                                        __int_as_float(0x7fc0dead), __int_as_float(0x7fc0dead));
+      for (long long i = b4 + t0; i < e4; i += stride) base[i] = poison;
+      __threadfence_system();
+      __nanosleep(20000);
+    }
+    for (long long i = b4 + t0; i < e4; i += stride) base[i] = zero;
+  };
   if (dbg != nullptr && threadIdx.x == 0) s_t[3] = ar_time_ns();
 
   // Peer loads have ~2 us latency.  All loads of a batch — every peer x kUnroll float4 — are issued
@@ -156,7 +223,8 @@ __global__ void __launch_bounds__(kArThreads) allreduce_sgd_kernel(const ArArgs 
   for (int sg = 0; sg < a.nseg; ++sg) {
   const long long seg_b = a.seg_begin4[sg], seg_e = a.seg_end4[sg];
   if (ALGO == kOneShot) {
-    float4* wl = reinterpret_cast<float4*>(a.plain ? a.out[rank] : a.w[rank]);
+    const float4* wl = reinterpret_cast<const float4*>(a.w[rank]);
+    float4* wol = reinterpret_cast<float4*>(a.plain ? a.out[rank] : a.wo[rank]);
     for (long long i0 = seg_b + t0; i0 < seg_e; i0 += stride * kUnroll) {
       float4 acc[kUnroll];
       float4 wv[kUnroll];
@@ -170,16 +238,18 @@ __global__ void __launch_bounds__(kArThreads) allreduce_sgd_kernel(const ArArgs 
       for (int u = 0; u < kUnroll; ++u) {
         const long long i = i0 + u * stride;
         if (i < seg_e) {
-          wl[i] = a.plain ? acc[u] : apply_update(wv[u], acc[u], i < a.n_params4, a.scale);
-          if (a.gz != nullptr) reinterpret_cast<float4*>(a.gz)[i] = zero;
+          wol[i] = a.plain ? acc[u] : apply_update(wv[u], acc[u], i < a.n_params4, a.scale);
+          if (a.gz != nullptr && !a.debug) reinterpret_cast<float4*>(a.gz)[i] = zero;
         }
       }
     }
+    if (a.gz != nullptr && a.debug) zero_range(reinterpret_cast<float4*>(a.gz), seg_b, seg_e);
   } else if (ALGO == kPull) {
-    // phase 1: reduce my shard, update my own weights (local stores only)
+    // phase 1: reduce my shard, write my own copy of the new weights (local stores only)
     const long long per = (seg_e - seg_b + world - 1) / world;
     const long long s0 = min(seg_e, seg_b + per * rank), s1 = min(seg_e, s0 + per);
-    float4* wl = reinterpret_cast<float4*>(a.w[rank]);
+    const float4* wl = reinterpret_cast<const float4*>(a.w[rank]);
+    float4* wol = reinterpret_cast<float4*>(a.wo[rank]);
     for (long long i0 = s0 + t0; i0 < s1; i0 += stride * kUnroll) {
       float4 acc[kUnroll];
       float4 wv[kUnroll];
@@ -192,34 +262,33 @@ __global__ void __launch_bounds__(kArThreads) allreduce_sgd_kernel(const ArArgs 
 #pragma unroll
       for (int u = 0; u < kUnroll; ++u) {
         const long long i = i0 + u * stride;
-        if (i < s1) wl[i] = apply_update(wv[u], acc[u], i < a.n_params4, a.scale);
+        if (i < s1) wol[i] = apply_update(wv[u], acc[u], i < a.n_params4, a.scale);
       }
     }
-    if (a.gz != nullptr)
-      for (long long i = seg_b + t0; i < seg_e; i += stride) reinterpret_cast<float4*>(a.gz)[i] = zero;
-    // phase 2: my shard is complete in my own L2 (gpu-scope fence), tell the peers, then pull
-    // every other owner's shard of the new weights.
-    __threadfence();
-    rank_barrier<false>(a, rank, &s_epoch);
-    // One flat loop over "every element that is not mine", 4 remote loads in flight per thread;
-    // consecutive strides of the grid hit different owners, so all links are busy at once.
-    const long long others = per * (world - 1);
-    for (long long j0 = t0; j0 < others; j0 += stride * 4) {
-      float4 v[4];
-      long long idx[4];
+    if (a.gz != nullptr) zero_range(reinterpret_cast<float4*>(a.gz), seg_b, seg_e);
+    // phase 2: tell the peers that my shard is written, then pull every other owner's shard.
+    // The barrier pairs block b of this rank with block b of the owner ONLY, so block b pulls
+    // exactly the elements the owner's block b wrote in phase 1: offsets t0 + m * stride inside
+    // the owner's shard (any other mapping reads elements of blocks it never synchronised with).
+    rank_barrier<true>(a, rank, &s_epoch);
+    ar_debug_delay(a, rank, s_epoch, 2);
+    if (a.debug) __syncthreads();
+    for (int q = 1; q < world; ++q) {
+      const int p = (rank + q) % world;               // stagger the owners across ranks
+      const long long p0 = min(seg_e, seg_b + per * p), p1 = min(seg_e, p0 + per);
+      const float4* src = reinterpret_cast<const float4*>(a.wo[p]);
+      for (long long i0 = p0 + t0; i0 < p1; i0 += stride * 4) {
+        float4 v[4];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const long long j = j0 + u * stride;
-        const int q = 1 + static_cast<int>(j / per);
-        const int p = (rank + q) % world;            // stagger the owners across ranks
-        idx[u] = seg_b + per * p + (j - (long long)(q - 1) * per);
-        if (j < others && idx[u] < seg_e)
-          v[u] = ld_nc_na_f4(reinterpret_cast<const float4*>(a.w[p]) + idx[u]);
-      }
+        for (int u = 0; u < 4; ++u) {
+          const long long i = i0 + u * stride;
+          if (i < p1) v[u] = ld_nc_na_f4(src + i);
+        }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const long long j = j0 + u * stride;
-        if (j < others && idx[u] < seg_e) wl[idx[u]] = v[u];
+        for (int u = 0; u < 4; ++u) {
+          const long long i = i0 + u * stride;
+          if (i < p1) wol[i] = v[u];
+        }
       }
     }
   } else {
@@ -248,11 +317,11 @@ __global__ void __launch_bounds__(kArThreads) allreduce_sgd_kernel(const ArArgs 
         if (i >= s1) continue;
         const float4 v = a.plain ? acc[u] : apply_update(wv[u], acc[u], i < a.n_params4, a.scale);
         if (ALGO == kNvls) {
-          multimem_st_f4(reinterpret_cast<float4*>(a.plain ? a.g_mc : a.w_mc) + i, v);
+          multimem_st_f4(reinterpret_cast<float4*>(a.plain ? a.g_mc : a.wo_mc) + i, v);
         } else {
 #pragma unroll
           for (int p = 0; p < kMaxRanks; ++p)
-            if (p < world) st_na_f4(reinterpret_cast<float4*>(a.plain ? a.g[p] : a.w[p]) + i, v);
+            if (p < world) st_na_f4(reinterpret_cast<float4*>(a.plain ? a.g[p] : a.wo[p]) + i, v);
         }
       }
     }
@@ -274,10 +343,11 @@ __global__ void __launch_bounds__(kArThreads) allreduce_sgd_kernel(const ArArgs 
   }
   if (a.gz != nullptr) {
     if (ALGO == kOneShot || ALGO == kPull) return;
-    float4* gzl = reinterpret_cast<float4*>(a.gz);
     for (int sg = 0; sg < a.nseg; ++sg)
-      for (long long i = a.seg_begin4[sg] + t0; i < a.seg_end4[sg]; i += stride) gzl[i] = zero;
-    rank_barrier<true>(a, rank, &s_epoch);  // B: all writes of W have completed
+      zero_range(reinterpret_cast<float4*>(a.gz), a.seg_begin4[sg], a.seg_end4[sg]);
+    // B: all writes of W have completed.  Skipped when a later kernel of the same step closes the
+    // step for every bucket at once (the LL exchange of the last bucket).
+    if (!a.no_exit) rank_barrier<true>(a, rank, &s_epoch);
     return;
   }
 
@@ -301,30 +371,122 @@ __global__ void __launch_bounds__(kArThreads) allreduce_sgd_kernel(const ArArgs 
   }
 }
 
+// ----------------------------------------------------------------------------------------
+// LL all-reduce + SGD for small buckets: the data is its own flag.
+//
+// Every rank pushes each of its gradient values to every peer as ONE 8-byte store
+// {value bits, epoch}; 8-byte aligned stores are single-copy atomic, so a reader that sees the
+// epoch also sees the value — no fence, no separate barrier, one one-way NVLink trip.  Each rank
+// then sums the world contributions per element in rank order (bit-identical everywhere) and
+// applies the update to its own weights only (no remote weight writes).  Inboxes are double
+// buffered by epoch parity, so a fast peer's next exchange cannot overwrite values that a slow
+// rank has not read yet.  Up to kLlMaxFloats values per launch (first layer + metric tail).
+// ----------------------------------------------------------------------------------------
+constexpr int kLlThreads = 256;
+constexpr int kLlMaxFloats = 16384;
+constexpr int kLlMaxBlocks = kLlMaxFloats / kLlThreads;
+
+struct LlArgs {
+  unsigned long long* inbox[kMaxRanks];  // [2 parities][kMaxRanks senders][kLlMaxFloats] per rank
+  uint32_t* epoch[kMaxRanks];            // per-block launch counters (local to each rank)
+  const float* w[kMaxRanks];             // weights read (only [rank]; all set in emulation)
+  float* wo[kMaxRanks];                  // weights written
+  const float* g[kMaxRanks];             // gradients of this step
+  float* gz[kMaxRanks];                  // the other gradient buffer: zeroed (may be null)
+  long long seg_begin[2], seg_end[2];    // float ranges of the arenas
+  int nseg;
+  long long n_params;
+  float scale;
+  int rank, world, emulate, debug;
+  long long timeout_ns;
+};
+
+__device__ __forceinline__ void st_relaxed_sys_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_sys_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__global__ void __launch_bounds__(kLlThreads) ll_allreduce_sgd_kernel(const LlArgs a) {
+  __shared__ uint32_t s_epoch;
+  const int rank = a.emulate ? blockIdx.y : a.rank;
+  const int world = a.world;
+  pdl_wait();     // this replica's backward has finished writing these gradients
+  pdl_trigger();
+  if (threadIdx.x == 0) {
+    uint32_t* ep = a.epoch[rank] + blockIdx.x;
+    uint32_t e = *ep + 1;
+    if (e == 0) e = 1;               // 0 is the "never written" value of the inboxes
+    *ep = e;
+    s_epoch = e;
+  }
+  __syncthreads();
+  const uint32_t e = s_epoch;
+  const long long len0 = a.seg_end[0] - a.seg_begin[0];
+  const long long n = len0 + (a.nseg > 1 ? a.seg_end[1] - a.seg_begin[1] : 0);
+  const long long i = (long long)blockIdx.x * kLlThreads + threadIdx.x;
+  if (a.debug && threadIdx.x == 0) {
+    const uint32_t h = ar_hash(rank * 0x9e3779b9U ^ blockIdx.x * 0x85ebca6bU ^ e * 0xc2b2ae35U ^ 7);
+    if ((h & 3) == 0) __nanosleep(h % 20000);
+  }
+  if (a.debug) __syncthreads();
+  if (i >= n) return;
+  const long long idx = i < len0 ? a.seg_begin[0] + i : a.seg_begin[1] + (i - len0);
+  const size_t slot = static_cast<size_t>(e & 1) * kMaxRanks * kLlMaxFloats + i;
+  const float mine = a.g[rank][idx];
+  const unsigned long long packed = (static_cast<unsigned long long>(e) << 32) | __float_as_uint(mine);
+  for (int q = 1; q < world; ++q) {
+    const int p = (rank + q) % world;
+    st_relaxed_sys_u64(a.inbox[p] + slot + static_cast<size_t>(rank) * kLlMaxFloats, packed);
+  }
+  const float wv = a.w[rank][idx];
+  float sum = 0.f;
+  long long t_start = 0;
+  for (int p = 0; p < world; ++p) {          // fixed order: identical bits on every rank
+    float v = mine;
+    if (p != rank) {
+      const unsigned long long* src = a.inbox[rank] + slot + static_cast<size_t>(p) * kLlMaxFloats;
+      unsigned long long u;
+      uint32_t spins = 0;
+      while (static_cast<uint32_t>((u = ld_relaxed_sys_u64(src)) >> 32) != e) {
+        if ((++spins & 0x3ff) == 0) {
+          const long long now = ar_time_ns();
+          if (t_start == 0) t_start = now;
+          if (now - t_start > a.timeout_ns) {
+            printf("b200dist: rank %d timed out waiting for the LL value %lld of rank %d (epoch %u, saw %u)\n",
+                   rank, i, p, e, static_cast<uint32_t>(u >> 32));
+            __trap();
+          }
+        }
+      }
+      v = __uint_as_float(static_cast<uint32_t>(u));
+    }
+    sum += v;
+  }
+  a.wo[rank][idx] = idx < a.n_params ? wv - a.scale * sum : wv + sum;
+  if (a.gz[rank] != nullptr) a.gz[rank][idx] = 0.f;
+}
+
 }  // namespace b2d
 
 using namespace b2d;
 
 // b2d_allreduce_desc is declared in include/b200dist.h
 
-extern "C" size_t b2d_allreduce_signal_bytes(void) {
-  return sizeof(uint32_t) * kMaxArBlocks * kMaxRanks;
+static bool ar_env_flag(const char* name) {
+  const char* v = getenv(name);
+  return v != nullptr && v[0] != '\0' && v[0] != '0';
 }
-extern "C" size_t b2d_allreduce_epoch_bytes(void) { return sizeof(uint32_t) * kMaxArBlocks; }
-
-// Size-based dispatch: below the crossover the single pass of one-shot wins on latency; above
-// it the (N-1)/N traffic of two-shot (or S/N of NVLS) wins on bandwidth.
-extern "C" int b2d_allreduce_pick_algo(int64_t n_total_floats, int world, int have_multicast) {
-  const int64_t bytes = n_total_floats * 4;
-  // Measured on 8 x B200 (profiles/r01_allreduce.md): one-shot (single barrier, reads only) wins
-  // at 2 ranks and for tiny messages; with multicast bound the switch reduction wins from
-  // ~256 KB up at >= 4 ranks; without it the pull variant is the latency choice up to a few MB.
-  if (world <= 2 || bytes <= (256 << 10) / world * 2) return kOneShot;
-  if (have_multicast && bytes >= (256 << 10)) return kNvls;
-  if (bytes <= (4 << 20)) return kPull;
-  return kTwoShot;
+// B200DIST_AR_TIMEOUT_S: how long a cross-GPU wait may last before the kernel traps (default 30 s).
+static long long ar_timeout_ns() {
+  const char* v = getenv("B200DIST_AR_TIMEOUT_S");
+  double s = v != nullptr ? atof(v) : 30.0;
+  if (!(s > 0.0)) s = 30.0;
+  return static_cast<long long>(s * 1e9);
 }
-
 extern "C" int b2d_allreduce_sgd(const b2d_allreduce_desc* d, void* stream) {
   B2D_REQUIRE(d != nullptr, "allreduce_sgd: null descriptor");
   B2D_REQUIRE(d->world >= 1 && d->world <= kMaxRanks, "allreduce_sgd: world must be in [1, %d]", kMaxRanks);
@@ -348,6 +510,12 @@ extern "C" int b2d_allreduce_sgd(const b2d_allreduce_desc* d, void* stream) {
   a.rank = d->rank, a.world = d->world, a.emulate = d->emulate, a.plain = d->plain;
   a.gz = d->emulate ? nullptr : static_cast<float*>(d->g_zero);
   a.dbg = static_cast<long long*>(d->timeline);
+  for (int p = 0; p < d->world; ++p) a.wo[p] = d->w_out[p] != nullptr ? static_cast<float*>(d->w_out[p]) : a.w[p];
+  a.wo_mc = d->w_out_mc != nullptr ? static_cast<float*>(d->w_out_mc) : a.w_mc;
+  a.no_exit = (d->flags & B2D_AR_NO_EXIT_BARRIER) != 0 && a.gz != nullptr;
+  a.strict = (d->flags & B2D_AR_STRICT_ENTRY) != 0 || ar_env_flag("B200DIST_AR_STRICT");
+  a.debug = ar_env_flag("B200DIST_AR_DEBUG");
+  a.timeout_ns = ar_timeout_ns();
   long long span4 = 0;
   if (d->nseg <= 0) {
     a.nseg = 1, a.seg_begin4[0] = 0, a.seg_end4[0] = a.n_total4;
@@ -386,6 +554,52 @@ extern "C" int b2d_allreduce_sgd(const b2d_allreduce_desc* d, void* stream) {
     count_launch();
   } else {
     B2D_CUDA_CHECK(launch_pdl(kern, dim3(blocks), dim3(kArThreads), 0, st, a));
+  }
+  return B2D_OK;
+}
+
+extern "C" size_t b2d_ll_inbox_bytes(void) {
+  return sizeof(unsigned long long) * 2 * kMaxRanks * kLlMaxFloats;
+}
+extern "C" size_t b2d_ll_epoch_bytes(void) { return sizeof(uint32_t) * kLlMaxBlocks; }
+extern "C" int64_t b2d_ll_max_floats(void) { return kLlMaxFloats; }
+
+extern "C" int b2d_ll_allreduce_sgd(const b2d_ll_desc* d, void* stream) {
+  B2D_REQUIRE(d != nullptr, "ll_allreduce_sgd: null descriptor");
+  B2D_REQUIRE(d->world >= 1 && d->world <= kMaxRanks, "ll_allreduce_sgd: world must be in [1, %d]", kMaxRanks);
+  B2D_REQUIRE(d->nseg >= 1 && d->nseg <= 2, "ll_allreduce_sgd: one or two segments");
+  LlArgs a{};
+  long long n = 0;
+  for (int k = 0; k < d->nseg; ++k) {
+    B2D_REQUIRE(d->seg_begin[k] >= 0 && d->seg_begin[k] <= d->seg_end[k],
+                "ll_allreduce_sgd: bad segment [%lld, %lld)", (long long)d->seg_begin[k], (long long)d->seg_end[k]);
+    a.seg_begin[k] = d->seg_begin[k], a.seg_end[k] = d->seg_end[k];
+    n += d->seg_end[k] - d->seg_begin[k];
+  }
+  B2D_REQUIRE(n >= 1 && n <= kLlMaxFloats, "ll_allreduce_sgd: %lld values per launch, the limit is %d", n, kLlMaxFloats);
+  a.nseg = d->nseg;
+  for (int p = 0; p < d->world; ++p) {
+    a.inbox[p] = static_cast<unsigned long long*>(d->inbox[p]);
+    a.epoch[p] = static_cast<uint32_t*>(d->epoch[p]);
+    a.w[p] = static_cast<const float*>(d->w[p]);
+    a.wo[p] = d->w_out[p] != nullptr ? static_cast<float*>(d->w_out[p]) : static_cast<float*>(d->w[p]);
+    a.g[p] = static_cast<const float*>(d->g[p]);
+    a.gz[p] = static_cast<float*>(d->g_zero[p]);
+  }
+  a.n_params = d->n_params;
+  a.scale = d->lr / static_cast<float>(d->world);
+  a.rank = d->rank, a.world = d->world, a.emulate = d->emulate;
+  a.debug = ar_env_flag("B200DIST_AR_DEBUG");
+  a.timeout_ns = ar_timeout_ns();
+  const int blocks = static_cast<int>((n + kLlThreads - 1) / kLlThreads);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (d->emulate) {
+    void* params[] = {&a};
+    B2D_CUDA_CHECK(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(ll_allreduce_sgd_kernel),
+                                               dim3(blocks, d->world), dim3(kLlThreads), params, 0, st));
+    count_launch();
+  } else {
+    B2D_CUDA_CHECK(launch_pdl(ll_allreduce_sgd_kernel, dim3(blocks), dim3(kLlThreads), 0, st, a));
   }
   return B2D_OK;
 }

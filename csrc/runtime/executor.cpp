@@ -31,6 +31,7 @@ struct b2d_executor {
   void* y_dev[2] = {nullptr, nullptr};
   size_t x_bytes = 0, y_bytes = 0;
   const void* metrics_dev = nullptr;
+  const void* metrics_dev_slot[2] = {nullptr, nullptr};  // weight ping-pong: where slot s leaves the sums
   void* metrics_ring = nullptr;  // pinned host, ring_len entries of metrics_bytes
   size_t metrics_bytes = 0;
   int ring_len = 0;
@@ -111,6 +112,14 @@ extern "C" int b2d_exec_set_metrics(b2d_executor* e, const void* metrics_dev, si
   return B2D_OK;
 }
 
+// With weight ping-pong the running sums alternate between the two weight buffers: the step replayed
+// from `slot` leaves them at `metrics_dev`.
+extern "C" int b2d_exec_set_metrics_slot(b2d_executor* e, int slot, const void* metrics_dev) {
+  B2D_REQUIRE(e != nullptr && (slot == 0 || slot == 1), "exec_set_metrics_slot: bad arguments");
+  e->metrics_dev_slot[slot] = metrics_dev;
+  return B2D_OK;
+}
+
 // Everything launched on b2d_exec_stream() between begin and end becomes the step graph.
 extern "C" int b2d_exec_begin_capture(b2d_executor* e) {
   B2D_REQUIRE(e != nullptr && !e->capturing, "exec_begin_capture: bad state");
@@ -166,8 +175,8 @@ extern "C" int b2d_exec_run(b2d_executor* e, const void* x_src, size_t x_stride,
     if (e->metrics_ring != nullptr) {
       char* dst = static_cast<char*>(e->metrics_ring) +
                   ((e->steps_done + t) % e->ring_len) * e->metrics_bytes;
-      B2D_CUDA_CHECK(cudaMemcpyAsync(dst, e->metrics_dev, e->metrics_bytes, cudaMemcpyDeviceToHost,
-                                     e->main));
+      const void* src = e->metrics_dev_slot[slot] != nullptr ? e->metrics_dev_slot[slot] : e->metrics_dev;
+      B2D_CUDA_CHECK(cudaMemcpyAsync(dst, src, e->metrics_bytes, cudaMemcpyDeviceToHost, e->main));
     }
     count_launch(e->nodes[slot]);
   }

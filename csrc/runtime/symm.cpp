@@ -9,7 +9,9 @@
 // (SURVEY.md section 5.9 / W12.  The reference's transport is gRPC between hosts,
 // README.md:395; nothing of it is reused.)
 #include <errno.h>
+#include <poll.h>
 #include <sys/socket.h>
+#include <sys/time.h>
 #include <sys/un.h>
 #include <time.h>
 #include <unistd.h>
@@ -133,10 +135,25 @@ static int exchange_fds(b2d_symm* s, const char* phase, int my_fd, int root, int
   }
   if (rc == B2D_OK && i_receive) {
     const int expect = root < 0 ? s->world - 1 : 1;
+    const double t0 = now_s();
     for (int k = 0; k < expect; ++k) {
+      // a peer that died after the rendezvous must not hang this rank: wait for the connection with the
+      // remaining time budget, and bound the receive as well
+      pollfd pfd{lsock, POLLIN, 0};
+      const double left = s->timeout_s - (now_s() - t0);
+      if (left <= 0 || poll(&pfd, 1, static_cast<int>(left * 1000)) <= 0) {
+        set_error("symm: timed out after %.0f s waiting for descriptor %d of %d (phase %s)", s->timeout_s, k + 1,
+                  expect, phase);
+        rc = B2D_ERR_SYS;
+        break;
+      }
       int c = accept(lsock, nullptr, nullptr);
       int fd = -1;
       int32_t from = -1;
+      if (c >= 0) {
+        timeval tv{static_cast<time_t>(s->timeout_s), 0};
+        setsockopt(c, SOL_SOCKET, SO_RCVTIMEO, &tv, sizeof(tv));
+      }
       if (c < 0 || recv_fd(c, &fd, &from) != 0 || from < 0 || from >= s->world) {
         set_error("symm: receiving a descriptor failed (%s)", strerror(errno));
         rc = B2D_ERR_SYS;
@@ -167,23 +184,36 @@ static int map_handle(CUmemGenericAllocationHandle h, size_t bytes, size_t gran,
   return B2D_OK;
 }
 
+static int symm_create_impl(b2d_symm* s, size_t bytes);
+
 // Collective over all ranks of `tag`: allocate, exchange, map.  `bytes` must be equal everywhere.
+// Every failure path releases what was created so far (handle, address ranges, mappings, imported peers).
 extern "C" int b2d_symm_create(b2d_symm** out, const char* tag, int rank, int world, int device,
                                size_t bytes, double timeout_s) {
   B2D_REQUIRE(out && tag && world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world && bytes > 0,
               "symm_create: bad arguments (world <= %d)", kMaxRanks);
   B2D_CUDA_CHECK(cudaSetDevice(device));
   B2D_CUDA_CHECK(cudaFree(nullptr));  // make sure the primary context exists
+  b2d_symm* s = new (std::nothrow) b2d_symm();
+  B2D_REQUIRE(s != nullptr, "symm_create: out of host memory");
+  s->rank = rank, s->world = world, s->device = device, s->tag = tag;
+  s->timeout_s = timeout_s > 0 ? timeout_s : 120.0;
+  const int rc = symm_create_impl(s, bytes);
+  if (rc != B2D_OK) {
+    b2d_symm_destroy(s);
+    return rc;
+  }
+  *out = s;
+  return B2D_OK;
+}
+
+static int symm_create_impl(b2d_symm* s, size_t bytes) {
+  const int rank = s->rank, world = s->world, device = s->device;
   auto get_gran = DRV(cuMemGetAllocationGranularity);
   auto create = DRV(cuMemCreate);
   auto export_h = DRV(cuMemExportToShareableHandle);
   auto import_h = DRV(cuMemImportFromShareableHandle);
   if (!get_gran || !create || !export_h || !import_h) return B2D_ERR_UNSUPPORTED;
-
-  b2d_symm* s = new (std::nothrow) b2d_symm();
-  B2D_REQUIRE(s != nullptr, "symm_create: out of host memory");
-  s->rank = rank, s->world = world, s->device = device, s->tag = tag;
-  s->timeout_s = timeout_s > 0 ? timeout_s : 120.0;
 
   CUmemAllocationProp prop{};
   prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
@@ -197,7 +227,7 @@ extern "C" int b2d_symm_create(b2d_symm** out, const char* tag, int rank, int wo
   int mc_attr = 0;
   if (auto get_attr = DRV(cuDeviceGetAttribute))
     get_attr(&mc_attr, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, device);
-  s->mc_supported = mc_attr != 0 && world > 1;
+  s->mc_supported = mc_attr != 0;   // world == 1 (a one-device multicast object) is used by the single-GPU test
   if (s->mc_supported) {
     auto mc_gran = DRV(cuMulticastGetGranularity);
     CUmulticastObjectProp mp{};
@@ -221,16 +251,21 @@ extern "C" int b2d_symm_create(b2d_symm** out, const char* tag, int rank, int wo
     rc = exchange_fds(s, "mem", my_fd, -1, fds);
     close(my_fd);
     if (rc != B2D_OK) return rc;
-    for (int p = 0; p < world; ++p) {
+    for (int p = 0; p < world && rc == B2D_OK; ++p) {
       if (p == rank) continue;
-      B2D_CU_CHECK(import_h(&s->peer_handle[p], reinterpret_cast<void*>(static_cast<uintptr_t>(fds[p])),
-                            CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR));
-      close(fds[p]);
+      const CUresult r = import_h(&s->peer_handle[p], reinterpret_cast<void*>(static_cast<uintptr_t>(fds[p])),
+                                  CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+      if (r != CUDA_SUCCESS) {
+        set_error("symm: importing the block of rank %d failed: CUresult %d", p, static_cast<int>(r));
+        rc = B2D_ERR_CUDA;
+        break;
+      }
       rc = map_handle(s->peer_handle[p], s->bytes, gran, device, &s->va[p]);
-      if (rc != B2D_OK) return rc;
     }
+    for (int p = 0; p < world; ++p)
+      if (fds[p] >= 0) close(fds[p]);   // the imported handles keep the allocations alive
+    if (rc != B2D_OK) return rc;
   }
-  *out = s;
   return B2D_OK;
 }
 

@@ -47,6 +47,10 @@ class StepProgram:
     early_backward: int = -1          # backward launches before the first parametrised layer's own backward stage
                                       # (everything after that layer is final there: bucket boundary); -1 = unknown
     first_param_layer: int = -1       # leaf index of that layer (bucket boundary for overlapped all-reduce)
+    grad_final: list = field(default_factory=list)
+    # grad_final: one (arena_begin, n_launches) pair per parametrised top-level layer, in forward order: once
+    # the first n_launches backward launches have completed, every gradient in [arena_begin, n_params) is final
+    # (the bucket schedule of the overlapped all-reduce is cut from this table, engine/trainer.py)
     description: list[str] = field(default_factory=list)
     keep: list = field(default_factory=list)        # buffers / plans kept alive
 
@@ -64,7 +68,14 @@ def _side(f):
     def run():
         f()
     run.side_ok = True
+    run.writes_grads = True
     return run
+
+
+def _grads(f):
+    """Tag a backward launch that writes parameter gradients (the bucket schedule needs to know which launch
+    is the LAST writer of a layer's gradients; data-gradient launches are not)."""
+    return _tag(f, writes_grads=True)
 
 
 def _tag(f, **attrs):
@@ -74,7 +85,7 @@ def _tag(f, **attrs):
     ``join_branch=True`` — the launch is the first consumer of that branch's results."""
     def run():
         f()
-    for k in ("side_ok", "branch", "join_branch"):
+    for k in ("side_ok", "branch", "join_branch", "writes_grads"):
         if getattr(f, k, False):
             setattr(run, k, True)
     for k, v in attrs.items():
@@ -104,6 +115,7 @@ class _Lowerer:
         self.head_done = False
         self.fused_tail = False
         self.first_param_stage = -1
+        self.top_marks: list = []         # (top-level layer, index of its first backward stage)
 
     # -- helpers ---------------------------------------------------------------------
     def pview(self, flat, layer):
@@ -165,6 +177,8 @@ class _Lowerer:
                 continue
             if isinstance(layer, (L.Conv2D, L.Dense, L.BatchNormalization)):
                 self.note_param_layer(layer, top_level)
+            if top_level:
+                self.top_marks.append((layer, len(self.stages)))
 
             if isinstance(layer, L.Conv2D):
                 w, b = self.kernel_bias(self.params, layer)
@@ -183,7 +197,7 @@ class _Lowerer:
                     dy = self.alloc_grad((batch, ph, pw, co))
                     prog.forward.append(be.conv_c1_pool_fwd(st.cur, w, b, y, code))
                     if training:
-                        self.stages.append([be.conv_c1_pool_bwd(st.cur, dy, code, dw, db)])
+                        self.stages.append([_grads(be.conv_c1_pool_bwd(st.cur, dy, code, dw, db))])
                     prog.description.append(
                         f"conv{layer.kernel_size[0]}x{layer.kernel_size[1]}(C_in=1)+bias+relu+maxpool2 fused -> {tuple(y.shape)}")
                     st = _State(y, dy, False)       # ReLU already folded into `code`
@@ -369,7 +383,7 @@ class _Lowerer:
                                     stats=stats, saved=saved, red=red, moving=(mmean, mvar),
                                     moving_grads=(g_mmean, g_mvar), inv_lr=self.inv_lr, inference=False,
                                     dy2d=dy.view(-1, c), dx2d=dx2d, dgamma=dgamma, dbeta=dbeta, **extra)
-            stage = [bwd]
+            stage = [_grads(bwd)]
             if st.d_cur is not None and st.post_relu:
                 stage.append(self.relu_mask(st.d_cur, st.cur))
             self.stages.append(stage)
@@ -482,6 +496,15 @@ def lower(layers, batch: int, be, layout: ArenaLayout, params, grads, x_in, labe
     if training and lw.first_param_stage >= 0:
         # stages after the first parametrised layer's run first in backward
         prog.early_backward = sum(len(stage) for stage in lw.stages[lw.first_param_stage + 1:])
+    if training:
+        from ..keras.layers import flatten_layers
+        for layer, stage0 in lw.top_marks:
+            offs = [s.offset for leaf in flatten_layers([layer]) for s in layout.layer_slots(leaf)]
+            if not offs:
+                continue
+            n_prefix = sum(len(stage) for stage in lw.stages[stage0:])       # launches of layers >= this one
+            last = max((k for k in range(n_prefix) if getattr(prog.backward[k], "writes_grads", False)), default=-1)
+            prog.grad_final.append((min(offs), last + 1))
     if begin is not None:
         prog.early_forward = 0       # the step starts by re-reading every weight: nothing to overlap
     return prog

@@ -33,6 +33,7 @@ def _declare_exec(lib):
     lib.b2d_exec_join.argtypes = [vp]
     lib.b2d_exec_set_io.argtypes = [vp, i, vp, sz, vp, sz]
     lib.b2d_exec_set_metrics.argtypes = [vp, vp, sz, vp, i]
+    lib.b2d_exec_set_metrics_slot.argtypes = [vp, i, vp]
     lib.b2d_exec_begin_capture.argtypes = [vp]
     lib.b2d_exec_end_capture.argtypes = [vp, i]
     lib.b2d_exec_graph_nodes.argtypes = [vp, i]
@@ -65,21 +66,35 @@ class Trainer:
             from .cpu_backend import CpuBackend
             self.be = CpuBackend()
             self._cpu_thread_layout(strategy)
+        self._exec = None
         self.comm = strategy.make_comm(self.layout.n_total, self.be)
-        self.params = self.comm.alloc(self.layout.n_total, self.be)
         self.use_graph = bool(use_graph and self.backend_name == "cuda" and self.comm.capturable)
-        # Gradient arena(s): communicators that ping-pong gradients get one per graph slot.
-        n_g = self.comm.num_grad_buffers if self.use_graph else 1
-        self.grad_bufs = [self.comm.alloc(self.layout.n_total, self.be) for _ in range(n_g)]
+        # Arenas.  Communicators that overlap the all-reduce with the backward pass (SymmComm) ping-pong both the
+        # gradients and the weights between two buffers, one per graph slot: step t reads W[t & 1], accumulates
+        # into G[t & 1], and its update writes W[(t + 1) & 1].  Everyone else has one buffer of each.
+        if hasattr(self.comm, "alloc_arenas"):
+            self.param_bufs, self.grad_bufs = self.comm.alloc_arenas(self.layout.n_total, self.be, self.use_graph)
+        else:
+            self.param_bufs = [self.comm.alloc(self.layout.n_total, self.be)]
+            n_g = self.comm.num_grad_buffers if self.use_graph else 1
+            self.grad_bufs = [self.comm.alloc(self.layout.n_total, self.be) for _ in range(n_g)]
         self.grads = self.grad_bufs[0]
         init = torch.from_numpy(self.layout.initial_values(self.layers, strategy.seed))
-        self.params.copy_(init)
+        for w in self.param_bufs:
+            w.copy_(init)
         for g in self.grad_bufs:
             g.zero_()
         if self.comm.world > 1 and not self.comm.all_equal(self.params):
             raise RuntimeError("replicas were not initialised identically (mirrored variables differ)")
         self._exec = None
         self._build()
+
+    @property
+    def params(self):
+        """The weight arena holding the CURRENT weights (with weight ping-pong: the buffer the next step reads)."""
+        if len(self.param_bufs) == 1:
+            return self.param_bufs[0]
+        return self.param_bufs[self.steps_done() & 1]
 
     @staticmethod
     def _cpu_thread_layout(strategy):
@@ -127,50 +142,44 @@ class Trainer:
         # metrics ring: pinned host memory the executor fills after every step
         self.ring_len = 4096
         self.metrics_host = torch.zeros((self.ring_len, TAIL), dtype=torch.float32).pin_memory()
-        tail = self.params[lay.n_params:lay.n_total]
+        tail = self.param_bufs[0][lay.n_params:lay.n_total]
         nl.check(lib.b2d_exec_set_metrics(h, tail.data_ptr(), TAIL * 4, self.metrics_host.data_ptr(),
                                           self.ring_len), "b2d_exec_set_metrics")
+        if len(self.param_bufs) == 2:
+            # the step replayed from slot s leaves the running sums in the tail of W[1 - s]
+            for slot in range(2):
+                t = self.param_bufs[1 - slot][lay.n_params:lay.n_total]
+                nl.check(lib.b2d_exec_set_metrics_slot(h, slot, t.data_ptr()), "b2d_exec_set_metrics_slot")
         self.side_stream = torch.cuda.ExternalStream(lib.b2d_exec_side_stream(h), device=self.be.device)
         self.branch_stream = torch.cuda.Stream(device=self.be.device)     # shortcut branches of residual blocks
         self._capture_events = []                                        # fork / join events of the captures
-        self.pipelined = []          # per slot: {"small", "deferred", "flush"} or empty
-        self.bucketed = []           # per slot: {"early", "late"} or empty (intra-step overlap, default)
+        self.schedules = []          # per slot: (list of (n_backward_launches, launch), closing launch) or None
+        self.comm_stream = torch.cuda.Stream(device=self.be.device)      # overlapped gradient buckets
         torch.cuda.synchronize(self.be.device)
-        import os
         with torch.cuda.stream(self.stream):
             for slot in range(n_slots):
                 g_slot = self.grad_bufs[slot % len(self.grad_bufs)]
-                prog = lower(self.layers, self.batch, be, lay, self.params, g_slot,
+                w_slot = self.param_bufs[slot % len(self.param_bufs)]
+                prog = lower(self.layers, self.batch, be, lay, w_slot, g_slot,
                              self.x_in[slot], self.y_in[slot], lr=self.lr)
-                if len(self.grad_bufs) > 1:
+                sched = None
+                if len(self.param_bufs) == 2:
+                    # Default for peer-memory replicas: the update is a bucket schedule overlapped with the
+                    # backward pass (see _bucket_plan); B200DIST_BUCKETS=0 falls back to one fused launch.
+                    g_other, w_other = self.grad_bufs[1 - slot], self.param_bufs[1 - slot]
+                    early, late_segs = self._bucket_plan(prog)
+                    fns, late, desc = self.comm.make_step_updates(
+                        be, w_slot, w_other, g_slot, g_other, lay.n_params, self.lr,
+                        [(b, e) for _, b, e in early], late_segs)
+                    sched = ([(n, f) for (n, _, _), f in zip(early, fns)], late)
+                    upd = late
+                    self.update_schedule = desc
+                elif len(self.grad_bufs) > 1:
                     g_other = self.grad_bufs[(slot + 1) % 2]
-                    upd = self.comm.make_update(be, self.params, g_slot, lay.n_params, self.lr,
-                                                grads_other=g_other)
-                    # Optional (B200DIST_PIPELINE=1) bucketed, cross-step-overlapped update: everything
-                    # but the first layer's parameters is reduced on a side branch while the NEXT
-                    # step's first kernels run.  Measured SLOWER for the README model (the overlap
-                    # window — one 5 us kernel — is shorter than the bucket's barrier + transfer), so
-                    # it is off by default; it pays once the first layer's forward is long.
-                    # Optional (B200DIST_BUCKETS=1): two buckets inside the step.  Everything after the first
-                    # parametrised layer is final once that layer's own backward starts, so its fused
-                    # all-reduce+SGD runs on the side branch UNDER the first layer's backward; only the first
-                    # layer's (small) bucket and the metric sums remain on the critical path.  Measured on the
-                    # README model: 57.1 vs 53.6 us/step at 2 GPUs, 66.2 vs 65.3 us at 8 — the second kernel's
-                    # cross-GPU barrier costs what the overlap hides, so one fused update per step stays the default.
-                    bucket_begin = self._bucket_begin(prog)
-                    if (self.use_graph and bucket_begin is not None and hasattr(self.comm, "make_bucketed_updates")
-                            and os.environ.get("B200DIST_BUCKETS", "0") == "1"
-                            and os.environ.get("B200DIST_PIPELINE", "0") != "1"):
-                        self.bucketed.append(self.comm.make_bucketed_updates(
-                            be, self.params, g_slot, g_other, lay.n_params, self.lr, bucket_begin))
-                    deferred_begin = self._deferred_begin(prog)
-                    if (self.use_graph and deferred_begin is not None
-                            and hasattr(self.comm, "make_pipelined_updates")
-                            and os.environ.get("B200DIST_PIPELINE", "0") == "1"):
-                        self.pipelined.append(self.comm.make_pipelined_updates(
-                            be, self.params, g_slot, g_other, lay.n_params, self.lr, deferred_begin))
+                    upd = self.comm.make_update(be, w_slot, g_slot, lay.n_params, self.lr, grads_other=g_other)
                 else:
-                    upd = self.comm.make_update(be, self.params, g_slot, lay.n_params, self.lr)
+                    upd = self.comm.make_update(be, w_slot, g_slot, lay.n_params, self.lr)
+                self.schedules.append(sched)
                 self.progs.append(prog)
                 self.updates.append(upd)
                 nl.check(lib.b2d_exec_set_io(h, slot, self.x_in[slot].data_ptr(), self.x_bytes,
@@ -184,47 +193,34 @@ class Trainer:
                 for slot in range(n_slots):
                     prog = self.progs[slot]
                     nl.check(lib.b2d_exec_begin_capture(h), "b2d_exec_begin_capture")
-                    if len(self.pipelined) == n_slots:
-                        pipe = self.pipelined[slot]
-                        nl.check(lib.b2d_exec_fork(h), "b2d_exec_fork")
-                        with torch.cuda.stream(self.side_stream):
-                            pipe["deferred"]()            # previous step's big bucket
-                        for f in prog.forward[:prog.early_forward]:
-                            f()                            # needs only the first layer's weights
-                        nl.check(lib.b2d_exec_join(h), "b2d_exec_join")
-                        for f in prog.forward[prog.early_forward:]:
-                            f()
-                        for f in prog.backward:
-                            f()
-                        pipe["small"]()                    # the only communication on the critical path
-                    elif len(self.bucketed) == n_slots:
-                        self._run_step_branches(prog, early=self.bucketed[slot]["early"])
-                        self.bucketed[slot]["late"]()
-                    else:
-                        self._run_step_branches(prog)
-                        self.updates[slot]()
+                    self._run_step_branches(prog, self.schedules[slot])
+                    self.updates[slot]()
                     nl.check(lib.b2d_exec_end_capture(h, slot), "b2d_exec_end_capture")
                 self.kernels_per_step = int(lib.b2d_exec_graph_nodes(h, 0))
             else:
                 self.kernels_per_step = None
         self.stream.synchronize()
 
-    def _run_step_branches(self, prog, early=None):
+    def _run_step_branches(self, prog, sched=None):
         """Issue one step for capture.  Weight-gradient launches (tagged ``side_ok`` by the lowering) go to
         the executor's side stream, forked right where they sit in the backward list and joined before the
         update: in the graph they become a branch that runs concurrently with the data-gradient chain
         (B200DIST_SIDE_WGRAD=0 keeps the step a single chain).  Launches tagged ``branch`` (the shortcut of a
         residual block, forward and backward) run on a third stream from their first launch to their first
-        consumer (``join_branch``); B200DIST_SIDE_SHORTCUT=0 keeps them on the main stream.  ``early``: the fused all-reduce+SGD of every
-        layer after the first parametrised one; it is queued on the side stream — behind the weight gradients
-        that feed it and after the main stream's data gradients that still read those weights — at the point
-        where only the first layer's backward remains."""
+        consumer (``join_branch``); B200DIST_SIDE_SHORTCUT=0 keeps them on the main stream.
+
+        ``sched`` = (early buckets, closing launch): every early bucket ``(n, launch)`` — a fused
+        all-reduce+SGD over gradients that are final once the first ``n`` backward launches are done — is
+        queued on the communication stream at that point, behind everything issued so far on the main, side and
+        shortcut streams, and runs under the rest of the backward pass.  The weights it writes belong to the
+        OTHER weight buffer, so nothing in this step reads them.  All branches join before the closing launch."""
         import os
         from .._native import cuda_lib as nl
         side = os.environ.get("B200DIST_SIDE_WGRAD", "1") != "0"
         use_branch = os.environ.get("B200DIST_SIDE_SHORTCUT", "1") != "0"
         main = torch.cuda.current_stream()
-        state = {"open": False}
+        state = {"open": False, "forked": False, "comm": False}
+        early = list(sched[0]) if sched else []
 
         def join_branch():
             if state["open"]:
@@ -245,6 +241,20 @@ class Trainer:
             with torch.cuda.stream(self.branch_stream):
                 f()
 
+        def issue_buckets(n_done):
+            while early and early[0][0] <= n_done:
+                _, launch = early.pop(0)
+                streams = [main] + ([self.side_stream] if state["forked"] else []) + \
+                          ([self.branch_stream] if state["open"] else [])
+                for st in streams:
+                    ev = torch.cuda.Event()
+                    ev.record(st)
+                    self.comm_stream.wait_event(ev)
+                    self._capture_events.append(ev)
+                with torch.cuda.stream(self.comm_stream):
+                    launch()
+                state["comm"] = True
+
         for f in prog.forward:
             if getattr(f, "join_branch", False):
                 join_branch()
@@ -253,67 +263,70 @@ class Trainer:
             else:
                 f()
         join_branch()
-        forked = False
+        issue_buckets(0)
         for i, f in enumerate(prog.backward):
             if getattr(f, "join_branch", False):
                 join_branch()
-            if early is not None and i == prog.early_backward:
-                nl.check(self._lib.b2d_exec_fork(self._exec), "b2d_exec_fork")
-                with torch.cuda.stream(self.side_stream):
-                    early()
-                forked, side = True, False      # later weight gradients stay on the main stream
             if use_branch and getattr(f, "branch", False):
                 on_branch(f)                    # incl. the branch's own weight gradients: they read its dy
             elif side and getattr(f, "side_ok", False):
                 nl.check(self._lib.b2d_exec_fork(self._exec), "b2d_exec_fork")
                 with torch.cuda.stream(self.side_stream):
                     f()
-                forked = True
+                state["forked"] = True
             else:
                 f()
+            issue_buckets(i + 1)
         join_branch()
-        if forked:
+        if state["forked"]:
             nl.check(self._lib.b2d_exec_join(self._exec), "b2d_exec_join")
+        if state["comm"]:
+            ev = torch.cuda.Event()
+            ev.record(self.comm_stream)
+            main.wait_event(ev)
+            self._capture_events.append(ev)
 
-    def _bucket_begin(self, prog):
-        """Arena offset where the early bucket starts (end of the first parametrised layer), or None."""
-        if prog.first_param_layer < 0 or not 0 <= prog.early_backward < len(prog.backward):
-            return None
-        later = [s for s in self.layout.slots if s.layer_index > prog.first_param_layer]
-        if not later:
-            return None
-        begin = min(s.offset for s in later)
-        return begin if 0 < begin < self.layout.n_params else None
+    def _bucket_plan(self, prog):
+        """Cut the gradient arena into buckets for the overlapped update.
 
-    def _deferred_begin(self, prog):
-        """Arena offset where the deferred bucket starts (end of the first parametrised layer), or
-        None when the model has nothing to defer."""
-        if prog.first_param_layer < 0 or prog.early_forward <= 0:
-            return None
-        later = [s for s in self.layout.slots if s.layer_index > prog.first_param_layer]
-        if not later:
-            return None
-        begin = min(s.offset for s in later)
-        return begin if 0 < begin < self.layout.n_params else None
-
-    def _flush_pending(self):
-        """Apply the deferred bucket of the last executed step (all replicas call this together)."""
-        if self.pipelined and self._pending_slot is not None:
-            with torch.cuda.stream(self.stream):
-                self.pipelined[self._pending_slot]["flush"]()
-            self._pending_slot = None
-
-    _pending_slot = None
+        Returns (early, late_segments).  ``early`` = [(n, begin, end)]: the floats [begin, end) are final once the
+        first n backward launches are done; buckets run from the last layer towards the first, each at least
+        B200DIST_BUCKET_MB (default 16 MB) unless the model is smaller, whole top-level layers only.
+        ``late_segments``: what only becomes final when the backward pass ends — the first parametrised layer —
+        plus the metric tail; it is the closing launch of the step."""
+        import os
+        lay = self.layout
+        n_bwd = len(prog.backward)
+        target = max(1, int(float(os.environ.get("B200DIST_BUCKET_MB", "16")) * (1 << 20) / 4))
+        table = list(prog.grad_final)
+        early, end = [], lay.n_params
+        rest = None                         # (n, begin) of the lowest layer that may still join an early bucket
+        for begin, n in reversed(table[1:]):
+            if n >= n_bwd or begin <= 0:
+                break
+            rest = (n, begin)
+            if end - begin >= target:
+                early.append((n, begin, end))
+                end, rest = begin, None
+        if rest is not None and rest[1] < end:
+            early.append((rest[0], rest[1], end))
+            end = rest[1]
+        return early, [(0, end), (lay.n_params, lay.n_total)]
 
     # ------------------------------------------------------------------------------
     def describe(self) -> list[str]:
         return list(self.progs[0].description)
 
     def run_steps(self, x_src, y_src, first_step: int, steps_in_src: int, n_steps: int,
-                  global_batch: int, timed: bool = False):
+                  global_batch: int, timed: bool = False, pre_steps: int = 0):
         """Run ``n_steps`` steps.  ``x_src`` [S,H,W,C] fp32 and ``y_src`` [S] int32 are pinned
         host or device tensors; step t of this replica reads rows
-        ``[(t % steps_in_src) * global_batch + rank * B, ... + B)``.  Returns elapsed ms if timed."""
+        ``[(t % steps_in_src) * global_batch + rank * B, ... + B)``.  Returns elapsed ms if timed.
+
+        ``pre_steps`` (timed runs): that many extra steps are enqueued on the same stream BEFORE the start
+        event, with no host synchronisation in between.  The fused all-reduce of those steps lines the
+        replicas up on the device, so the timed region starts with every GPU in lock step instead of
+        absorbing the host-side release skew of the processes (milliseconds at 8 ranks)."""
         B, r = self.batch, self.comm.rank
         row = int(np.prod(self.input_shape))
         if self._exec is not None and self.use_graph:
@@ -322,12 +335,13 @@ class Trainer:
             from .._native import cuda_lib as nl
             if timed:
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                if pre_steps > 0:
+                    nl.check(self._lib.b2d_exec_run(self._exec, xs, global_batch * row * 4, ys, global_batch * 4,
+                                                    first_step, steps_in_src, pre_steps, 0, None), "b2d_exec_run")
+                    first_step += pre_steps
                 e0.record(self.stream)
             nl.check(self._lib.b2d_exec_run(self._exec, xs, global_batch * row * 4, ys, global_batch * 4,
                                             first_step, steps_in_src, n_steps, 0, None), "b2d_exec_run")
-            if n_steps > 0 and self.pipelined:
-                self._pending_slot = (self.steps_done() - 1) & 1
-                self._flush_pending()          # inside the timed region: the work is not skipped
             if timed:
                 e1.record(self.stream)
                 e1.synchronize()
@@ -390,7 +404,8 @@ class Trainer:
 
     def reset_metrics(self):
         self.sync()
-        self.params[self.layout.n_params:self.layout.n_total].zero_()
+        for w in self.param_bufs:
+            w[self.layout.n_params:self.layout.n_total].zero_()
         if self.backend_name == "cuda":
             torch.cuda.synchronize(self.be.device)
         self.comm.barrier()
@@ -409,19 +424,24 @@ class Trainer:
             if tuple(a.shape) != s.shape:
                 raise ValueError(f"{s.name}: expected shape {s.shape}, got {a.shape}")
             flat[s.offset:s.offset + s.size] = torch.from_numpy(a.reshape(-1))
-        self.params.copy_(flat)
+        for w in self.param_bufs:
+            w.copy_(flat)
         if self.backend_name == "cuda":
             torch.cuda.synchronize(self.be.device)
 
     def forward_logits(self, x: torch.Tensor) -> torch.Tensor:
         """Inference on one batch of exactly ``batch`` rows (used by predict / evaluate)."""
         if not hasattr(self, "_infer"):
+            self._infer = {}
+        self.sync()
+        cur = (self.steps_done() & 1) if len(self.param_bufs) == 2 else 0      # the buffer with the current weights
+        if cur not in self._infer:
             xi, yi = self._io_buffers()
             ctx = torch.cuda.stream(self.stream) if self.backend_name == "cuda" else _null()
             with ctx:
-                self._infer = (xi, lower(self.layers, self.batch, self.be, self.layout, self.params,
-                                         self.grads, xi, yi, training=False))
-        xi, prog = self._infer
+                self._infer[cur] = (xi, lower(self.layers, self.batch, self.be, self.layout, self.param_bufs[cur],
+                                              self.grads, xi, yi, training=False))
+        xi, prog = self._infer[cur]
         ctx = torch.cuda.stream(self.stream) if self.backend_name == "cuda" else _null()
         with ctx:
             xi.copy_(x)

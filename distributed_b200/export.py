@@ -1,36 +1,40 @@
-"""Weight export in Keras layer order (README.md:234-247: ``save_model_hdf5`` then base64).
+"""Model and weight export in Keras layer order (README.md:234-247: ``save_model_hdf5`` then base64).
 
 Tensors are written in the order and layouts Keras uses — for the README model
 ``conv2d/kernel:0`` (3,3,1,32) HWIO, ``conv2d/bias:0``, ``dense/kernel:0`` (5408,64) (in,out)
 with Flatten in H,W,C order, ``dense/bias:0``, ``dense_1/kernel:0`` (64,10), ``dense_1/bias:0``.
 
-Formats: ``.npz`` is always available.  ``.h5`` / ``.hdf5`` uses h5py when it is installed and
-writes the Keras 2 weight-file layout; without h5py (this image) the same tensors are written
-as an ``.npz`` payload under the requested file name, which ``load_weights`` recognises by
-its magic bytes — so the README's save → base64 → decode → load round trip works either way.
+Formats, chosen by the file extension:
+
+* ``.h5`` / ``.hdf5`` — a real HDF5 file in the Keras-2 layout, written by the
+  dependency-free writer in ``utils/hdf5.py`` (h5py / libhdf5 are not needed): root attributes
+  ``model_config`` (JSON, ``{"class_name": "Sequential", "config": ...}``), ``keras_version``, ``backend``;
+  group ``model_weights`` with attribute ``layer_names``; one group per layer with attribute
+  ``weight_names``; one float32 data set per weight at ``model_weights/<layer>/<weight name>``.
+  ``save_weights`` writes the same groups at the root (Keras' weights-only layout).
+* anything else (``.npz``) — a NumPy archive with the same names, order and config.
+
+``load_weights`` / ``load_model`` recognise either container by its magic bytes, so the README's
+save -> base64 -> decode -> load round trip works with both.
 """
 from __future__ import annotations
 
 import base64
-import io
 import json
 from pathlib import Path
 
 import numpy as np
 
+from .utils import hdf5
 
-def _have_h5py():
-    try:
-        import h5py  # noqa: F401
-        return True
-    except Exception:
-        return False
+KERAS_VERSION = "2.2.4-tf"          # what TensorFlow 2.0 (the reference's version, README.md:260) writes
 
 
 def weights_dict(model) -> dict[str, np.ndarray]:
     return dict(zip(model.weight_names(), model.get_weights()))
 
 
+# ---- npz ---------------------------------------------------------------------------------------
 def _save_npz(path, tensors: dict, config: dict | None):
     payload = {k.replace("/", "__").replace(":", "--"): v for k, v in tensors.items()}
     payload["__order__"] = np.array(list(tensors.keys()))
@@ -48,46 +52,52 @@ def _load_npz(path):
     return tensors, config
 
 
+# ---- HDF5 (Keras-2 layout) -----------------------------------------------------------------------
 def _save_h5(path, model, tensors, config):
-    import h5py
-    with h5py.File(path, "w") as f:
-        g = f.create_group("model_weights") if config is not None else f
-        if config is not None:
-            f.attrs["model_config"] = json.dumps({"class_name": "Sequential", "config": config})
-        g.attrs["layer_names"] = [l.name.encode() for l in model.layers]
-        g.attrs["backend"] = b"distributed_b200"
-        for l in model.layers:
-            lg = g.create_group(l.name)
-            names = [s.name for s in l.param_specs()]
-            lg.attrs["weight_names"] = [n.encode() for n in names]
-            for n in names:
-                lg.create_dataset(n, data=tensors[n])
+    root = hdf5.Group()
+    g = root.create_group("model_weights") if config is not None else root
+    if config is not None:
+        root.attrs["model_config"] = json.dumps({"class_name": "Sequential", "config": config},
+                                                separators=(",", ":"))
+        root.attrs["keras_version"] = KERAS_VERSION
+        root.attrs["backend"] = "tensorflow"
+    g.attrs["layer_names"] = [l.name for l in model.layers]
+    g.attrs["backend"] = "tensorflow"
+    g.attrs["keras_version"] = KERAS_VERSION
+    for l in model.layers:
+        lg = g.create_group(l.name)
+        names = [s.name for s in l.param_specs()]
+        lg.attrs["weight_names"] = names
+        for n in names:
+            node = lg
+            *dirs, leaf = n.split("/")                  # "conv2d/kernel:0" -> group conv2d, data set kernel:0
+            for d in dirs:
+                node = node.children[d] if d in node.children else node.create_group(d)
+            node.create_dataset(leaf, np.asarray(tensors[n], np.float32))
+    hdf5.write_file(path, root)
 
 
 def _load_h5(path):
-    import h5py
-    tensors, config = {}, None
-    with h5py.File(path, "r") as f:
-        if "model_config" in f.attrs:
-            config = json.loads(f.attrs["model_config"])["config"]
-        g = f["model_weights"] if "model_weights" in f else f
-        for ln in g.attrs["layer_names"]:
-            ln = ln.decode() if isinstance(ln, bytes) else ln
-            for wn in g[ln].attrs["weight_names"]:
-                wn = wn.decode() if isinstance(wn, bytes) else wn
-                tensors[wn] = np.array(g[ln][wn])
+    root = hdf5.read_file(path)
+    config = None
+    if "model_config" in root.attrs:
+        config = json.loads(hdf5.as_text(root.attrs["model_config"]))["config"]
+        if isinstance(config, list):                    # very old Keras: the config IS the layer list
+            config = {"name": "sequential", "layers": config}
+    g = root["model_weights"] if "model_weights" in root else root
+    tensors = {}
+    for ln in np.atleast_1d(g.attrs["layer_names"]):
+        lg = g[hdf5.as_text(ln)]
+        for wn in np.atleast_1d(lg.attrs.get("weight_names", [])):
+            wn = hdf5.as_text(wn)
+            tensors[wn] = np.asarray(lg[wn], np.float32)
     return tensors, config
-
-
-def _is_zip(path) -> bool:
-    with open(path, "rb") as f:
-        return f.read(2) == b"PK"
 
 
 def _write(model, path, config):
     path = Path(path)
     tensors = weights_dict(model)
-    if path.suffix in (".h5", ".hdf5") and _have_h5py():
+    if path.suffix in (".h5", ".hdf5"):
         _save_h5(path, model, tensors, config)
     else:
         _save_npz(path, tensors, config)
@@ -103,11 +113,11 @@ def save_model(model, path):
 
 def _read(path):
     path = Path(path)
-    if _is_zip(path):
+    with open(path, "rb") as f:
+        magic = f.read(8)
+    if magic[:2] == b"PK":
         return _load_npz(path)
-    if _have_h5py():
-        return _load_h5(path)
-    raise RuntimeError(f"{path} is an HDF5 file but h5py is not installed")
+    return _load_h5(path)
 
 
 def load_weights(model, path):
@@ -120,19 +130,11 @@ def load_weights(model, path):
 
 
 def load_model(path):
-    from .keras import layers as L
     from .keras.models import Sequential
     tensors, config = _read(path)
     if config is None:
         raise ValueError("file holds weights only; build the model and call load_weights")
-    model = Sequential(name=config.get("name", "sequential"))
-    for lc in config["layers"]:
-        cls = getattr(L, lc["class_name"])
-        cfg = dict(lc["config"])
-        for k in ("kernel_size", "strides", "pool_size", "input_shape"):
-            if k in cfg and cfg[k] is not None:
-                cfg[k] = tuple(cfg[k])
-        model.add(cls(**cfg))
+    model = Sequential.from_config(config)
     model.set_weights([tensors[n] for n in model.weight_names()])
     return model
 

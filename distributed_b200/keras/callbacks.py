@@ -70,6 +70,3 @@ class EarlyStopping(Callback):
             self.stopped_epoch = epoch
             self.model.stop_training = True
 
-
-class History(Callback):
-    pass

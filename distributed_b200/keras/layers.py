@@ -80,11 +80,69 @@ class Layer:
     def count_trainable_params(self) -> int:
         return sum(p.size for p in self.param_specs() if p.trainable)
 
+    # -- serialisation (Keras-2 "config" dictionaries; model.save / load_model, README.md:237-246) ----------
+    def _base_config(self) -> dict:
+        cfg = {"name": self.name, "trainable": True, "dtype": "float32"}
+        if self.input_shape_arg is not None:
+            cfg["batch_input_shape"] = [None, *self.input_shape_arg]
+        return cfg
+
     def get_config(self) -> dict:
-        return {"name": self.name}
+        return self._base_config()
+
+    @classmethod
+    def from_config(cls, config: dict):
+        """Rebuild a layer from ``get_config()`` output.  Keys of a genuine Keras config that this framework
+        has no use for (dtype, trainable, data_format, regularizers, ...) are accepted and dropped; values it
+        cannot honour (e.g. ``data_format='channels_first'``) raise."""
+        import inspect
+        cfg = dict(config)
+        bis = cfg.pop("batch_input_shape", None)
+        if bis is not None and "input_shape" not in cfg:
+            cfg["input_shape"] = tuple(bis[1:])
+        if cfg.get("data_format", "channels_last") != "channels_last":
+            raise ValueError("only data_format='channels_last' is supported")
+        if tuple(np.atleast_1d(cfg.get("dilation_rate", 1))) not in ((1,), (1, 1)):
+            raise ValueError("dilated convolutions are not supported")
+        for k in ("kernel_size", "strides", "pool_size", "input_shape"):
+            if cfg.get(k) is not None:
+                cfg[k] = tuple(cfg[k])
+        for k in ("kernel_initializer", "bias_initializer"):
+            if isinstance(cfg.get(k), dict):          # Keras spells initializers as {"class_name": ..., "config": ...}
+                cfg[k] = _INITIALIZER_NAMES.get(cfg[k].get("class_name"), cfg[k].get("class_name"))
+        accepted = set()
+        for klass in cls.__mro__:
+            if klass is object:
+                continue
+            accepted |= set(inspect.signature(klass.__init__).parameters)
+        return cls(**{k: v for k, v in cfg.items() if k in accepted and k not in ("self", "kw", "kwargs")})
 
     def __repr__(self):
         return f"<{type(self).__name__} {self.name} {self.input_shape}->{self.output_shape}>"
+
+
+_INITIALIZER_NAMES = {"GlorotUniform": "glorot_uniform", "Zeros": "zeros", "Ones": "ones",
+                      "VarianceScaling": "glorot_uniform", "HeNormal": "he_normal", "HeUniform": "he_uniform"}
+_INITIALIZER_CLASSES = {"glorot_uniform": "GlorotUniform", "zeros": "Zeros", "ones": "Ones",
+                        "he_normal": "HeNormal", "he_uniform": "HeUniform"}
+
+
+def _init_config(name):
+    name = name if isinstance(name, str) else getattr(name, "__name__", str(name))
+    return {"class_name": _INITIALIZER_CLASSES.get(name, name), "config": {}}
+
+
+def layer_from_config(spec: dict):
+    """``{"class_name": ..., "config": {...}}`` -> layer (recursively for Residual blocks)."""
+    import sys
+    cls = getattr(sys.modules[__name__], spec["class_name"], None)
+    if cls is None or not (isinstance(cls, type) and issubclass(cls, Layer)):
+        raise ValueError(f"unknown layer class {spec['class_name']!r}")
+    return cls.from_config(spec["config"])
+
+
+def layer_to_config(layer) -> dict:
+    return {"class_name": type(layer).__name__, "config": layer.get_config()}
 
 
 class InputLayer(Layer):
@@ -112,6 +170,13 @@ class Conv2D(Layer):
         self.use_bias = bool(use_bias)
         self.kernel_initializer = kernel_initializer
         self.bias_initializer = bias_initializer
+
+    def get_config(self):
+        return {**self._base_config(), "filters": self.filters, "kernel_size": list(self.kernel_size),
+                "strides": list(self.strides), "padding": self.padding, "data_format": "channels_last",
+                "dilation_rate": [1, 1], "activation": self.activation or "linear", "use_bias": self.use_bias,
+                "kernel_initializer": _init_config(self.kernel_initializer),
+                "bias_initializer": _init_config(self.bias_initializer)}
 
     def pad_amounts(self, input_shape=None) -> tuple[int, int]:
         """Symmetric zero padding (top/left); 'same' with odd kernels and these strides."""
@@ -163,6 +228,10 @@ class MaxPooling2D(Layer):
         if self.pool_size[0] != self.pool_size[1] or self.strides[0] != self.strides[1]:
             raise ValueError("MaxPooling2D supports square windows and strides")
 
+    def get_config(self):
+        return {**self._base_config(), "pool_size": list(self.pool_size), "strides": list(self.strides),
+                "padding": self.padding, "data_format": "channels_last"}
+
     @property
     def is_default_2x2(self) -> bool:
         return self.pool_size == (2, 2) and self.strides == (2, 2) and self.padding == "valid"
@@ -187,6 +256,9 @@ class Flatten(Layer):
     """Row-major flatten of (H, W, C) — a view; no data moves (README.md:295)."""
     base_name = "flatten"
 
+    def get_config(self):
+        return {**self._base_config(), "data_format": "channels_last"}
+
     def compute_output_shape(self, input_shape):
         return (int(np.prod(input_shape)),)
 
@@ -203,6 +275,11 @@ class Dense(Layer):
         self.use_bias = bool(use_bias)
         self.kernel_initializer = kernel_initializer
         self.bias_initializer = bias_initializer
+
+    def get_config(self):
+        return {**self._base_config(), "units": self.units, "activation": self.activation or "linear",
+                "use_bias": self.use_bias, "kernel_initializer": _init_config(self.kernel_initializer),
+                "bias_initializer": _init_config(self.bias_initializer)}
 
     def compute_output_shape(self, input_shape):
         if len(input_shape) != 1:
@@ -229,6 +306,25 @@ class BatchNormalization(Layer):
         if axis not in (-1, 3):
             raise ValueError("BatchNormalization supports the channel (last) axis only")
         self.momentum, self.epsilon = float(momentum), float(epsilon)
+
+    def get_config(self):
+        cfg = {**self._base_config(), "axis": [3], "momentum": self.momentum, "epsilon": self.epsilon,
+               "center": True, "scale": True}
+        if self.activation is not None:
+            cfg["activation"] = self.activation          # a folded ReLU (not a Keras key; see from_config)
+        return cfg
+
+    @classmethod
+    def from_config(cls, config):
+        cfg = dict(config)
+        act = cfg.pop("activation", None)
+        axis = cfg.get("axis", -1)
+        cfg["axis"] = axis[0] if isinstance(axis, (list, tuple)) else axis
+        if not (cfg.pop("center", True) and cfg.pop("scale", True)):
+            raise ValueError("BatchNormalization without gamma / beta is not supported")
+        layer = super().from_config(cfg)
+        layer.activation = _norm_activation(act)
+        return layer
 
     def param_specs(self):
         c = self.input_shape[-1]
@@ -260,6 +356,20 @@ class Residual(Layer):
 
     def sublayers(self):
         return self.main + self.shortcut
+
+    def get_config(self):
+        return {**self._base_config(), "activation": self.activation or "linear",
+                "main": [layer_to_config(l) for l in self.main],
+                "shortcut": [layer_to_config(l) for l in self.shortcut]}
+
+    @classmethod
+    def from_config(cls, config):
+        cfg = dict(config)
+        main = [layer_from_config(c) for c in cfg.pop("main")]
+        shortcut = [layer_from_config(c) for c in cfg.pop("shortcut", [])]
+        bis = cfg.pop("batch_input_shape", None)
+        kw = {"input_shape": tuple(bis[1:])} if bis is not None else {}
+        return cls(main, shortcut or None, activation=cfg.get("activation", "relu"), name=cfg.get("name"), **kw)
 
     def build(self, input_shape):
         self.input_shape = tuple(int(d) for d in input_shape)
@@ -312,12 +422,23 @@ class Activation(Layer):
         super().__init__(**kw)
         self.activation = _norm_activation(activation)
 
+    def get_config(self):
+        return {**self._base_config(), "activation": self.activation or "linear"}
+
 
 class ReLU(Activation):
     base_name = "re_lu"
 
     def __init__(self, **kw):
         super().__init__("relu", **kw)
+
+    def get_config(self):
+        return self._base_config()
+
+    @classmethod
+    def from_config(cls, config):
+        bis = config.get("batch_input_shape")
+        return cls(name=config.get("name"), **({"input_shape": tuple(bis[1:])} if bis else {}))
 
 
 def initialize(spec: ParamSpec, rng: np.random.Generator) -> np.ndarray:

@@ -184,7 +184,17 @@ class Sequential(Model):
         return xt, yt
 
     def fit(self, x=None, y=None, batch_size=None, epochs=1, verbose=1, steps_per_epoch=None,
-            callbacks=None, shuffle=False, initial_epoch=0, **kwargs):
+            callbacks=None, shuffle=False, initial_epoch=0, validation_data=None, **kwargs):
+        """Train from in-memory arrays (README.md:304, 392).  ``batch_size`` is the GLOBAL batch under a
+        strategy.  Batches are taken in order (``shuffle=True`` is refused rather than ignored);
+        ``validation_data=(x, y)`` adds ``val_loss`` / ``val_accuracy`` to the logs after every epoch; any
+        other keyword raises instead of being silently dropped."""
+        if kwargs:
+            raise TypeError(f"fit() got unsupported keyword arguments {sorted(kwargs)}; supported: x, y, batch_size, "
+                            "epochs, verbose, steps_per_epoch, callbacks, shuffle=False, initial_epoch, validation_data")
+        if shuffle:
+            raise NotImplementedError("shuffle=True is not supported: every replica reads its slice of consecutive "
+                                      "global batches; shuffle the arrays before calling fit()")
         if self.optimizer is None or self.loss is None:
             raise RuntimeError("call compile(loss=..., optimizer=...) before fit()")
         strat = self._strategy
@@ -216,6 +226,10 @@ class Sequential(Model):
         history = History()
         history.params = {"epochs": epochs, "steps": steps, "batch_size": global_batch, "samples": n_samples}
         out = sys.stdout
+        # verbose=1 on a terminal: the Keras progress line is refreshed while the epoch runs (README.md:307-311
+        # shows lines captured mid-epoch: "192/60000 [...] - ETA: 29s - loss: 2.3059 - accuracy: 0.2240").  The
+        # epoch is then run in up to 10 chunks, each ending with a read of the running sums.
+        live = verbose == 1 and hasattr(out, "isatty") and out.isatty()
         if verbose:
             print(f"Train on {n_samples} samples", file=out)
         for cb in callbacks:
@@ -229,7 +243,17 @@ class Sequential(Model):
             trainer = self._ensure_trainer(per_replica, sample_shape)     # a callback may have changed the lr
             trainer.reset_metrics()
             t0 = time.perf_counter()
-            trainer.run_steps(xt, yt, self._global_step, steps_in_src, steps, global_batch)
+            done = 0
+            chunk = max(1, -(-steps // 10)) if live else steps
+            while done < steps:
+                n = min(chunk, steps - done)
+                trainer.run_steps(xt, yt, self._global_step + done, steps_in_src, n, global_batch)
+                done += n
+                if live and done < steps:
+                    loss_sum, correct, seen = trainer.metric_sums()
+                    out.write("\r" + self._progress_line(seen, n_samples, time.perf_counter() - t0, done, loss_sum,
+                                                          correct, final=False))
+                    out.flush()
             loss_sum, correct, seen = trainer.metric_sums()
             dt = time.perf_counter() - t0
             self._global_step += steps
@@ -237,12 +261,17 @@ class Sequential(Model):
             if "accuracy" in self.metrics_names:
                 # float32 division so the value matches Keras' float32 metric (README.md:229-231)
                 logs["accuracy"] = float(np.float32(correct) / np.float32(max(seen, 1.0)))
+            if validation_data is not None:
+                val = self.evaluate(validation_data[0], validation_data[1], batch_size=per_replica)
+                val = val if isinstance(val, list) else [val]
+                logs["val_loss"] = val[0]
+                if len(val) > 1:
+                    logs["val_accuracy"] = val[1]
             history._append(epoch, logs)
             if verbose:
-                msg = " - ".join(f"{k}: {v:.4f}" for k, v in logs.items())
-                bar = "=" * min(30, int(30 * seen / max(n_samples, 1)))
-                print(f"{int(seen):>5}/{n_samples} [{bar:.<30}] - {dt:.0f}s {1e3 * dt / steps:.0f}ms/step - {msg}",
-                      file=out)
+                line = self._progress_line(seen, n_samples, dt, steps, loss_sum, correct, final=True)
+                extra = "".join(f" - {k}: {v:.4f}" for k, v in logs.items() if k.startswith("val_"))
+                print(("\r" if live else "") + line + extra, file=out)
             for cb in callbacks:
                 cb.on_epoch_end(epoch, logs)
             if self.stop_training:
@@ -251,6 +280,28 @@ class Sequential(Model):
             cb.on_train_end()
         self.history = history
         return history
+
+    def _progress_line(self, seen, n_samples, dt, steps_done, loss_sum, correct, final: bool) -> str:
+        """One Keras-style progress line: ``seen/total [===>....] - ETA: m:ss - loss: - accuracy:`` while samples
+        remain (also at the end of an epoch cut short by ``steps_per_epoch``, exactly as README.md:309-311 and
+        413-415 show), ``- 9s 23ms/step`` once the whole array has been consumed.  Both metrics are streaming
+        means over the samples seen so far this epoch, summed over all replicas."""
+        seen_i = int(seen)
+        width = 30
+        filled = min(width, int(width * seen / max(n_samples, 1)))
+        bar = "=" * filled if filled >= width else "=" * max(filled - 1, 0) + (">" if filled else "") \
+            + "." * (width - max(filled, 0))
+        bar = (bar + "." * width)[:width]
+        parts = [f"{seen_i:>{len(str(n_samples))}}/{n_samples} [{bar}]"]
+        if seen_i < n_samples:
+            eta = (n_samples - seen) * dt / max(seen, 1.0)
+            parts.append("ETA: " + (f"{int(eta) // 60}:{int(eta) % 60:02d}" if eta >= 60 else f"{eta:.0f}s"))
+        else:
+            parts.append(f"{dt:.0f}s {1e3 * dt / max(steps_done, 1):.0f}ms/step")
+        parts.append(f"loss: {loss_sum / max(seen, 1.0):.4f}")
+        if "accuracy" in self.metrics_names:
+            parts.append(f"accuracy: {float(np.float32(correct) / np.float32(max(seen, 1.0))):.4f}")
+        return " - ".join(parts)
 
     # ---- inference (not exercised by the reference; provided for the local validation flow) --
     def predict(self, x, batch_size=None, verbose=0):
@@ -312,17 +363,12 @@ class Sequential(Model):
         export.save_model(self, filepath)
 
     def get_config(self):
-        return {"name": self.name, "layers": [
-            {"class_name": type(l).__name__, "config": _layer_config(l)} for l in self.layers]}
+        """Keras-2 Sequential config: every layer as {"class_name", "config"} (Residual blocks recursively)."""
+        return {"name": self.name, "layers": [L.layer_to_config(l) for l in self.layers]}
 
-
-def _layer_config(l):
-    import inspect
-    cfg = {"name": l.name}
-    accepted = set(inspect.signature(type(l).__init__).parameters)
-    for k in ("filters", "kernel_size", "strides", "padding", "activation", "use_bias", "units", "pool_size"):
-        if k in accepted and hasattr(l, k):
-            cfg[k] = getattr(l, k)
-    if l.input_shape_arg is not None:
-        cfg["input_shape"] = list(l.input_shape_arg)
-    return cfg
+    @classmethod
+    def from_config(cls, config):
+        model = cls(name=config.get("name", "sequential"))
+        for spec in config["layers"]:
+            model.add(L.layer_from_config(spec))
+        return model

@@ -33,7 +33,18 @@ class AllreduceDesc(C.Structure):
                 ("n_params", C.c_int64), ("n_total", C.c_int64), ("lr", C.c_float),
                 ("rank", C.c_int), ("world", C.c_int), ("algo", C.c_int), ("emulate", C.c_int),
                 ("plain", C.c_int), ("blocks", C.c_int), ("g_zero", C.c_void_p), ("timeline", C.c_void_p),
-                ("seg_begin", C.c_int64 * 2), ("seg_end", C.c_int64 * 2), ("nseg", C.c_int)]
+                ("seg_begin", C.c_int64 * 2), ("seg_end", C.c_int64 * 2), ("nseg", C.c_int),
+                ("w_out", _VP8), ("w_out_mc", C.c_void_p), ("flags", C.c_int)]
+
+
+class LlDesc(C.Structure):
+    _fields_ = [("inbox", _VP8), ("epoch", _VP8), ("w", _VP8), ("w_out", _VP8), ("g", _VP8), ("g_zero", _VP8),
+                ("seg_begin", C.c_int64 * 2), ("seg_end", C.c_int64 * 2), ("nseg", C.c_int),
+                ("n_params", C.c_int64), ("lr", C.c_float), ("rank", C.c_int), ("world", C.c_int),
+                ("emulate", C.c_int)]
+
+
+AR_NO_EXIT_BARRIER, AR_STRICT_ENTRY = 1, 2
 
 
 def _declare(lib):
@@ -55,6 +66,10 @@ def _declare(lib):
     lib.b2d_allreduce_epoch_bytes.restype = sz
     lib.b2d_allreduce_pick_algo.argtypes = [C.c_int64, i, i]
     lib.b2d_allreduce_sgd.argtypes = [C.POINTER(AllreduceDesc), vp]
+    lib.b2d_ll_inbox_bytes.restype = sz
+    lib.b2d_ll_epoch_bytes.restype = sz
+    lib.b2d_ll_max_floats.restype = C.c_int64
+    lib.b2d_ll_allreduce_sgd.argtypes = [C.POINTER(LlDesc), vp]
     lib._symm_declared = True
 
 
@@ -87,13 +102,20 @@ class SymmComm:
         arena_bytes = self.n * 4
         self.sig_bytes = int(lib.b2d_allreduce_signal_bytes())
         self.epoch_bytes = int(lib.b2d_allreduce_epoch_bytes())
+        self.ll_inbox_bytes = int(lib.b2d_ll_inbox_bytes())
+        self.ll_epoch_bytes = int(lib.b2d_ll_epoch_bytes())
+        self.ll_max_floats = int(lib.b2d_ll_max_floats())
         # layout of the symmetric block (same offsets on every replica)
+        a = _align(arena_bytes, 4096)
         self.off_w = 0
-        self.off_g = _align(arena_bytes, 4096)
-        self.off_g2 = self.off_g + _align(arena_bytes, 4096)       # second gradient buffer (ping-pong)
-        self.off_sig = self.off_g2 + _align(arena_bytes, 4096)
+        self.off_g = a
+        self.off_g2 = 2 * a                                        # second gradient buffer (ping-pong)
+        self.off_w2 = 3 * a                                        # second weight buffer (ping-pong)
+        self.off_sig = 4 * a
         self.off_epoch = self.off_sig + _align(self.sig_bytes * self.CHANNELS, 4096)
-        total = self.off_epoch + _align(self.epoch_bytes * self.CHANNELS, 4096)
+        self.off_ll = self.off_epoch + _align(self.epoch_bytes * self.CHANNELS, 4096)
+        self.off_ll_epoch = self.off_ll + _align(self.ll_inbox_bytes, 4096)
+        total = self.off_ll_epoch + _align(self.ll_epoch_bytes, 4096)
         h = C.c_void_p()
         torch.cuda.set_device(self.device)
         dist.barrier()
@@ -157,21 +179,90 @@ class SymmComm:
         self._next += 1
         return self._tensor(off, n)
 
+    def alloc_arenas(self, n, be, ping_pong: bool):
+        """([weight buffers], [gradient buffers]) in symmetric memory: two of each when the step is replayed
+        from graphs (step t reads W[t & 1], accumulates into G[t & 1]; the update writes W[(t + 1) & 1])."""
+        assert n <= self.n, "arena larger than the communicator's capacity"
+        bucketed = ping_pong and os.environ.get("B200DIST_BUCKETS", "1") != "0"
+        ws = [self._tensor(self.off_w, n)] + ([self._tensor(self.off_w2, n)] if bucketed else [])
+        gs = [self._tensor(self.off_g, n)] + ([self._tensor(self.off_g2, n)] if ping_pong else [])
+        return ws, gs
+
+    def _off_of(self, t):
+        return t.data_ptr() - self.base[self.rank]
+
+    def pick(self, n_floats: int) -> int:
+        return self.algo if self.algo >= 0 else int(
+            self._lib.b2d_allreduce_pick_algo(n_floats, self.world, 1 if self.mc_base else 0))
+
+    def make_step_updates(self, be, w_in, w_out, g, g_other, n_params, lr, early, late_segments):
+        """The update of one step as a bucket schedule (engine/trainer.py):
+
+        * ``early`` — list of [begin, end) float ranges, each reduced by its own fused all-reduce+SGD launch on
+          the communication branch of the step graph as soon as its gradients are final.  Reads ``w_in`` / ``g``,
+          writes ``w_out`` of every replica, no closing barrier (B2D_AR_NO_EXIT_BARRIER).
+        * ``late_segments`` — the ranges that are final only when the backward pass ends (first layer + metric
+          tail), on the critical path: the LL exchange when they fit, else one fused launch with its barriers.
+          Either way this launch closes the step for all buckets.
+
+        Returns (list of early launches, late launch, description)."""
+        n_total = w_in.numel()
+        fns = []
+        for (b0, e0) in early:
+            fns.append(self.make_update(be, w_in, g, n_params, lr, grads_other=g_other, segments=[(b0, e0)],
+                                        channel=0, w_out=w_out, flags=AR_NO_EXIT_BARRIER))
+        n_late = sum(e - b for b, e in late_segments)
+        if n_late <= self.ll_max_floats and os.environ.get("B200DIST_LL", "1") != "0":
+            d = LlDesc()
+            for p in range(self.world):
+                d.inbox[p] = self.base[p] + self.off_ll
+                d.epoch[p] = self.base[p] + self.off_ll_epoch
+                d.w[p] = self.base[p] + self._off_of(w_in)
+                d.w_out[p] = self.base[p] + self._off_of(w_out)
+                d.g[p] = self.base[p] + self._off_of(g)
+                d.g_zero[p] = self.base[p] + self._off_of(g_other)
+            d.nseg = len(late_segments)
+            for k, (b0, e0) in enumerate(late_segments):
+                d.seg_begin[k], d.seg_end[k] = b0, e0
+            d.n_params, d.lr, d.rank, d.world, d.emulate = n_params, float(lr), self.rank, self.world, 0
+            self._descs = getattr(self, "_descs", []) + [d]
+            lib = self._lib
+
+            def late():
+                nl.check(lib.b2d_ll_allreduce_sgd(C.byref(d), torch.cuda.current_stream().cuda_stream),
+                         "b2d_ll_allreduce_sgd")
+            late_name = f"LL push exchange ({n_late} values)"
+        else:
+            segs = list(late_segments)
+            late = self.make_update(be, w_in, g, n_params, lr, grads_other=g_other, segments=segs, channel=1,
+                                    w_out=w_out)
+            late_name = ALGO_NAMES[self.pick(max(e - b for b, e in segs))]
+        names = [ALGO_NAMES[self.pick(e - b)] for b, e in early]
+        desc = (f"{len(early)} overlapped bucket(s) [{', '.join(names)}] + closing bucket [{late_name}]"
+                if early else f"closing bucket [{late_name}]")
+        return fns, late, desc
+
     def make_update(self, be, params, grads, n_params, lr, grads_other=None, segments=None, channel=0,
-                    algo=None):
+                    algo=None, w_out=None, flags=0):
         """Fused all-reduce+SGD over ``grads``; ``grads_other`` (the other ping-pong buffer of this
         rank) is zeroed by the same kernel, which lets one-shot run with a single barrier.
         ``segments``: up to two [begin, end) float ranges (bucketing); ``channel``: signal pad."""
         d = AllreduceDesc()
-        off_g = self.off_g if grads.data_ptr() == self.base[self.rank] + self.off_g else self.off_g2
+        off_g, off_w = self._off_of(grads), self._off_of(params)
+        assert off_g in (self.off_g, self.off_g2) and off_w in (self.off_w, self.off_w2)
         for p in range(self.world):
-            d.w[p] = self.base[p] + self.off_w
+            d.w[p] = self.base[p] + off_w
             d.g[p] = self.base[p] + off_g
             d.sig[p] = self.base[p] + self.off_sig + channel * self.sig_bytes
             d.epoch[p] = self.base[p] + self.off_epoch + channel * self.epoch_bytes
+            if w_out is not None:
+                d.w_out[p] = self.base[p] + self._off_of(w_out)
         if self.mc_base:
-            d.w_mc = self.mc_base + self.off_w
+            d.w_mc = self.mc_base + off_w
             d.g_mc = self.mc_base + off_g
+            if w_out is not None:
+                d.w_out_mc = self.mc_base + self._off_of(w_out)
+        d.flags = flags
         d.g_zero = grads_other.data_ptr() if grads_other is not None else None
         n_total = params.numel()
         assert params.data_ptr() == d.w[self.rank] and grads.data_ptr() == d.g[self.rank]
@@ -190,44 +281,6 @@ class SymmComm:
             nl.check(lib.b2d_allreduce_sgd(C.byref(d), torch.cuda.current_stream().cuda_stream),
                      "b2d_allreduce_sgd")
         return run
-
-    def make_bucketed_updates(self, be, params, g_slot, g_other, n_params, lr, early_begin):
-        """Two fused all-reduce+SGD launches per step (engine/trainer.py):
-
-        * ``early`` — [early_begin, n_params): every layer after the first parametrised one, on its own
-                       signal channel, launched on the side branch as soon as those gradients are final;
-        * ``late``  — [0, early_begin) + the metric tail: the first layer's (small) bucket, one-shot, the
-                       only communication left on the critical path.
-        Each zeroes its own ranges of the other ping-pong gradient buffer."""
-        n_total = params.numel()
-        return {
-            "early": self.make_update(be, params, g_slot, n_params, lr, grads_other=g_other,
-                                      segments=[(early_begin, n_params)], channel=1),
-            "late": self.make_update(be, params, g_slot, n_params, lr, grads_other=g_other,
-                                     segments=[(0, early_begin), (n_params, n_total)], channel=0, algo=0),
-        }
-
-    def make_pipelined_updates(self, be, params, g_slot, g_other, n_params, lr, deferred_begin):
-        """Bucketed update that hides the big bucket behind compute (see engine/trainer.py).
-
-        * ``small``    — [0, deferred_begin) + metric tail of THIS step's gradients, at the end of
-                          the step: one-shot, one barrier (the only communication on the critical path).
-        * ``deferred`` — [deferred_begin, n_params) of the PREVIOUS step's gradients (other ping-pong
-                          buffer), launched on the side stream at the start of the step; it must
-                          finish before the first kernel that reads those weights.
-        * ``flush``    — applies the still-pending deferred bucket of this slot (end of a run).
-        """
-        n_total = params.numel()
-        seg_small = [(0, deferred_begin), (n_params, n_total)]
-        seg_def = [(deferred_begin, n_params)]
-        return {
-            "small": self.make_update(be, params, g_slot, n_params, lr, grads_other=g_other,
-                                      segments=seg_small, channel=0, algo=0),
-            "deferred": self.make_update(be, params, g_other, n_params, lr, grads_other=g_slot,
-                                         segments=seg_def, channel=1),
-            "flush": self.make_update(be, params, g_slot, n_params, lr, grads_other=None,
-                                      segments=seg_def, channel=2),
-        }
 
     # -- control plane ------------------------------------------------------------------
     def barrier(self):

@@ -292,11 +292,42 @@ typedef struct b2d_allreduce_desc {
   int64_t seg_begin[2]; /* bucketing: up to two [begin, end) float ranges of the arenas handled  */
   int64_t seg_end[2];   /* by this launch (multiples of 4); nseg == 0 means the whole arena      */
   int nseg;
+  void* w_out[8];   /* weight ping-pong: where the UPDATED weights are written (every rank's other
+                       weight buffer); NULL entries = update w in place                       */
+  void* w_out_mc;   /* multicast view of w_out (NVLS) or NULL                                 */
+  int flags;        /* B2D_AR_* bits                                                          */
 } b2d_allreduce_desc;
+#define B2D_AR_NO_EXIT_BARRIER 1 /* the caller closes the step with a later exchange (b2d_ll_allreduce_sgd):
+                                    skip the barrier after the remote weight writes; needs g_zero    */
+#define B2D_AR_STRICT_ENTRY 2    /* entry barrier with st.release.sys (also: env B200DIST_AR_STRICT=1) */
 size_t b2d_allreduce_signal_bytes(void);
 size_t b2d_allreduce_epoch_bytes(void);
 int b2d_allreduce_pick_algo(int64_t n_total_floats, int world, int have_multicast);
 int b2d_allreduce_sgd(const b2d_allreduce_desc* desc, void* stream);
+
+/* Small-bucket variant (the first layer's gradients + the metric sums, README.md:404-407): every
+ * rank pushes {value, epoch} pairs as single 8-byte stores into the peers' inboxes and sums what
+ * arrives in rank order — one one-way NVLink trip, no barrier, bit-identical on every rank; the
+ * exchange doubles as the closing barrier of a step whose other buckets used
+ * B2D_AR_NO_EXIT_BARRIER.  At most b2d_ll_max_floats() values per launch. */
+typedef struct b2d_ll_desc {
+  void* inbox[8];   /* b2d_ll_inbox_bytes() of zero-initialised symmetric memory per rank        */
+  void* epoch[8];   /* b2d_ll_epoch_bytes() of zero-initialised local memory per rank           */
+  void* w[8];       /* weights read  (only [rank] unless emulate)                               */
+  void* w_out[8];   /* weights written (NULL = in place)                                        */
+  void* g[8];       /* gradients of this step                                                   */
+  void* g_zero[8];  /* the other gradient buffer, zeroed over the same ranges, or NULL          */
+  int64_t seg_begin[2], seg_end[2]; /* one or two [begin, end) float ranges of the arenas       */
+  int nseg;
+  int64_t n_params; /* indices >= n_params are metric sums: added, not averaged                 */
+  float lr;
+  int rank, world;
+  int emulate;      /* all ranks in one cooperative launch on one GPU (tests)                   */
+} b2d_ll_desc;
+size_t b2d_ll_inbox_bytes(void);
+size_t b2d_ll_epoch_bytes(void);
+int64_t b2d_ll_max_floats(void);
+int b2d_ll_allreduce_sgd(const b2d_ll_desc* desc, void* stream);
 
 /* ---------------------------------------------------------------------------------------
  * Native step executor (csrc/runtime/executor.cpp): captures the step's launches into CUDA
@@ -313,6 +344,7 @@ int b2d_exec_join(b2d_executor* e);            /* main continues after everythin
 int b2d_exec_set_io(b2d_executor* e, int slot, void* x_dev, size_t x_bytes, void* y_dev, size_t y_bytes);
 int b2d_exec_set_metrics(b2d_executor* e, const void* metrics_dev, size_t bytes, void* pinned_ring,
                          int ring_len);
+int b2d_exec_set_metrics_slot(b2d_executor* e, int slot, const void* metrics_dev); /* weight ping-pong */
 int b2d_exec_begin_capture(b2d_executor* e);
 int b2d_exec_end_capture(b2d_executor* e, int slot);
 uint64_t b2d_exec_graph_nodes(const b2d_executor* e, int slot);

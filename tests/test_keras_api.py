@@ -103,6 +103,34 @@ def test_errors():
         m.fit(np.zeros((10, 28, 28, 1)), np.zeros(10), batch_size=64, verbose=0)
 
 
+def test_fit_refuses_what_it_would_otherwise_ignore():
+    m = _readme_model()
+    x, y = np.zeros((64, 28, 28, 1), np.float32), np.zeros(64)
+    with pytest.raises(TypeError, match="validation_split"):
+        m.fit(x, y, batch_size=64, verbose=0, validation_split=0.1)
+    with pytest.raises(NotImplementedError):
+        m.fit(x, y, batch_size=64, verbose=0, shuffle=True)
+
+
+def test_validation_data_and_progress_lines(capsys):
+    """The console contract of README.md:307-311: 'Train on N samples', 'Epoch k/n', then
+    'seen/N [bar] - ETA: .. - loss: .. - accuracy: ..' (an epoch cut short by steps_per_epoch still has samples
+    left, hence the ETA), metrics being streaming means over the samples seen this epoch."""
+    m = _readme_model()
+    rng = np.random.default_rng(0)
+    x, y = rng.random((640, 28, 28, 1)).astype(np.float32), rng.integers(0, 10, 640)
+    h = m.fit(x, y, batch_size=64, epochs=2, steps_per_epoch=5, validation_data=(x[:128], y[:128]))
+    out = capsys.readouterr().out.splitlines()
+    assert out[0] == "Train on 640 samples" and out[1] == "Epoch 1/2"
+    import re
+    assert re.fullmatch(r"320/640 \[=+>\.+\] - ETA: \d+s - loss: \d\.\d{4} - accuracy: 0\.\d{4}"
+                        r" - val_loss: \d\.\d{4} - val_accuracy: 0\.\d{4}", out[2]), out[2]
+    assert set(h.history) == {"loss", "accuracy", "val_loss", "val_accuracy"} and len(h.history["val_loss"]) == 2
+    h = m.fit(x, y, batch_size=64, epochs=1)                     # whole array: the line ends with the timing instead
+    last = capsys.readouterr().out.splitlines()[-1]
+    assert re.fullmatch(r"640/640 \[=+\] - \d+s \d+ms/step - loss: \d\.\d{4} - accuracy: 0\.\d{4}", last), last
+
+
 def test_version_and_datasets():
     assert tf.utils.tf_version() == "2.0" and tf.__version__.startswith("2.0")
     (xtr, ytr), (xte, yte) = tf.keras.datasets.mnist.load_data()

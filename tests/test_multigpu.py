@@ -19,7 +19,7 @@ def _worker(ctx, n, algo, steps=5, epochs=2, env=None):
     strategy = tf.distribute.experimental.MultiWorkerMirroredStrategy()
     rng = np.random.default_rng(0)
     gb = 64 * n
-    x = rng.random((gb * steps * epochs, 28, 28, 1)).astype(np.float32)
+    x = rng.random((gb * min(steps * epochs, 8), 28, 28, 1)).astype(np.float32)     # longer runs wrap around
     y = rng.integers(0, 10, len(x))
     with strategy.scope():
         model = tf.models.mnist_cnn(learning_rate=0.01)
@@ -34,7 +34,7 @@ def _worker(ctx, n, algo, steps=5, epochs=2, env=None):
     out = {"loss": h.history["loss"], "acc": h.history["accuracy"],
            "digest": [float(np.abs(a).astype(np.float64).sum()) for a in w],
            "device": str(t.be.device), "comm": t.comm.description, "graph": t.use_graph,
-           "kernels": t.kernels_per_step}
+           "kernels": t.kernels_per_step, "schedule": getattr(t, "update_schedule", "single fused launch")}
     t.close()
     return json.dumps(out)
 
@@ -78,13 +78,17 @@ def test_n_gpus_match_one_gpu_with_the_global_batch():
         assert abs(a - b) <= 2e-3 * max(abs(a), 1.0)
 
 
-@pytest.mark.parametrize("env", [{"B200DIST_BUCKETS": "1"}, {"B200DIST_PIPELINE": "1"}, {"B200DIST_SIDE_WGRAD": "0"}])
+@pytest.mark.parametrize("env", [{"B200DIST_BUCKETS": "0"}, {"B200DIST_LL": "0"}, {"B200DIST_SIDE_WGRAD": "0"},
+                                 {"B200DIST_AR_STRICT": "1"}, {"B200DIST_BUCKET_MB": "0.001"}])
 def test_optional_update_schedules_keep_replicas_identical_and_match_the_default(env):
-    """Bucketed (intra-step), pipelined (cross-step) and single-chain schedules are different graphs over the
-    same kernels: replicas must stay bit-identical and the training trajectory must match the default one."""
+    """The default update is a bucket schedule overlapped with the backward pass (weight ping-pong, early buckets
+    on the communication branch, LL closing exchange).  One fused launch (BUCKETS=0), a barrier-based closing
+    bucket (LL=0), a single-chain step, release/acquire entry barriers and one bucket per layer are different
+    graphs over the same arithmetic: replicas must stay bit-identical and the trajectory must match the default."""
     from distributed_b200.launch import barrier_apply
     n = min(_ngpu(), 8)
     base = json.loads(barrier_apply(lambda ctx: _worker(ctx, n, "auto", steps=4, epochs=1), n, timeout=600)[0])
+    assert "overlapped bucket" in base["schedule"]
     res = [json.loads(s) if s.startswith("{") else s for s in
            barrier_apply(lambda ctx: _worker(ctx, n, "auto", steps=4, epochs=1, env=env), n, timeout=600)]
     assert all(isinstance(r, dict) for r in res), res
@@ -93,3 +97,85 @@ def test_optional_update_schedules_keep_replicas_identical_and_match_the_default
     assert abs(res[0]["loss"][0] - base["loss"][0]) < 1e-3
     for a, b in zip(res[0]["digest"], base["digest"]):
         assert abs(a - b) <= 1e-3 * max(abs(a), 1.0)
+
+
+@pytest.mark.parametrize("algo", ["auto", "pull", "twoshot"])
+def test_debug_mode_stress_random_delays_poison_and_monotone_flags(algo):
+    """the race detector of the peer-memory path.  B200DIST_AR_DEBUG=1 pauses pseudo-random (rank,
+    block, epoch) combinations at every phase of the all-reduce kernels, poisons each consumed gradient buffer
+    with NaNs for 20 us before zeroing it, and traps when a barrier flag is not monotone.  A read outside the
+    protocol's windows turns the weights into NaNs or makes replicas diverge; the arithmetic is unchanged, so
+    the result must be bit-identical to the run without the debug mode."""
+    from distributed_b200.launch import barrier_apply
+    n = min(_ngpu(), 8)
+    steps = 400
+    ref = json.loads(barrier_apply(lambda ctx: _worker(ctx, n, algo, steps=steps, epochs=1), n, timeout=900)[0])
+    res = [json.loads(s) if s.startswith("{") else s for s in
+           barrier_apply(lambda ctx: _worker(ctx, n, algo, steps=steps, epochs=1,
+                                             env={"B200DIST_AR_DEBUG": "1"}), n, timeout=900)]
+    assert all(isinstance(r, dict) for r in res), res
+    for r in res:
+        assert all(np.isfinite(v) for v in r["digest"]) and np.isfinite(r["loss"][0])
+        assert r["digest"] == res[0]["digest"]
+    assert res[0]["digest"] == ref["digest"] and res[0]["loss"] == ref["loss"]
+
+
+def _allreduce_vs_nccl(ctx, n):
+    """Plain all-reduce of the peer-memory kernels against torch.distributed.all_reduce (NCCL), SURVEY 4.2."""
+    import os
+    import ctypes as C
+    os.environ["TF_CONFIG"] = json.dumps(ctx.tf_config(base_port=int(ctx.address[0].split(":")[1]) % 20000 + 30000))
+    import torch
+    import torch.distributed as dist
+    import distributed_b200 as tf
+    from distributed_b200._native import cuda_lib as nl
+    from distributed_b200.parallel import symm
+    strategy = tf.distribute.experimental.MultiWorkerMirroredStrategy()
+    strategy._ensure_group()
+    rank = strategy.rank
+    dev = torch.device("cuda", rank)
+    torch.cuda.set_device(dev)
+    nccl = dist.new_group(backend="nccl")
+    sizes = [4, 4 * (n + 1), 4 * (3 * n + 1), 1000 * 4 + 4, 347172, (1 << 20) + 4 * (n - 1), (1 << 22) + 12]
+    comm = symm.SymmComm(strategy, f"cmp-{ctx.address[0]}", max(sizes) + 64, dev)
+    lib = nl.lib()
+    out = {"sizes": sizes, "max_err": [], "digests": []}
+    algos = [0, 1] + ([2] if comm.mc_base else [])
+    for n_floats in sizes:
+        g = torch.Generator(device=dev).manual_seed(1000 * rank + n_floats)
+        src = torch.randn(n_floats, device=dev, generator=g)
+        ref = src.clone()
+        dist.all_reduce(ref, group=nccl)
+        for algo in algos:
+            G = comm._tensor(comm.off_g, n_floats)
+            O = comm._tensor(comm.off_w, n_floats)
+            G.copy_(src)
+            O.zero_()
+            comm.barrier()
+            d = symm.AllreduceDesc()
+            for p in range(n):
+                d.w[p] = d.out[p] = comm.base[p] + comm.off_w
+                d.g[p] = comm.base[p] + comm.off_g
+                d.sig[p], d.epoch[p] = comm.base[p] + comm.off_sig, comm.base[p] + comm.off_epoch
+            if comm.mc_base:
+                d.w_mc, d.g_mc = comm.mc_base + comm.off_w, comm.mc_base + comm.off_g
+            d.n_params = d.n_total = n_floats
+            d.lr, d.rank, d.world, d.algo, d.emulate, d.plain, d.blocks = 0.0, rank, n, algo, 0, 1, 0
+            nl.check(lib.b2d_allreduce_sgd(C.byref(d), torch.cuda.current_stream().cuda_stream), "allreduce")
+            comm.barrier()
+            res = O if algo == 0 else G          # one-shot writes `out`; two-shot / NVLS reduce in place
+            out["max_err"].append(float((res - ref).abs().max() / ref.abs().max()))
+            out["digests"].append(res.double().sum().item().hex() + res.view(torch.int32).sum().item().__repr__())
+    comm.close()
+    return json.dumps(out)
+
+
+def test_plain_allreduce_matches_nccl_on_odd_sizes_and_is_bitwise_identical_across_ranks():
+    from distributed_b200.launch import barrier_apply
+    n = min(_ngpu(), 8)
+    res = [json.loads(s) if s.startswith("{") else s for s in
+           barrier_apply(lambda ctx: _allreduce_vs_nccl(ctx, n), n, timeout=600)]
+    assert all(isinstance(r, dict) for r in res), res
+    assert max(res[0]["max_err"]) < 1e-5, res[0]["max_err"]                 # vs NCCL (its summation order differs)
+    for r in res[1:]:
+        assert r["digests"] == res[0]["digests"]                              # every rank holds the same bits
