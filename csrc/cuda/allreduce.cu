@@ -487,6 +487,25 @@ static long long ar_timeout_ns() {
   if (!(s > 0.0)) s = 30.0;
   return static_cast<long long>(s * 1e9);
 }
+extern "C" size_t b2d_allreduce_signal_bytes(void) {
+  return sizeof(uint32_t) * kMaxArBlocks * kMaxRanks;
+}
+// per-block epochs, followed by the debug mode's "last flag seen" words per (block, peer)
+extern "C" size_t b2d_allreduce_epoch_bytes(void) { return sizeof(uint32_t) * kMaxArBlocks * (1 + kMaxRanks); }
+
+// Size-based dispatch: below the crossover the single pass of one-shot wins on latency; above
+// it the (N-1)/N traffic of two-shot (or S/N of NVLS) wins on bandwidth.
+extern "C" int b2d_allreduce_pick_algo(int64_t n_total_floats, int world, int have_multicast) {
+  const int64_t bytes = n_total_floats * 4;
+  // Measured on 8 x B200 (profiles/r01_allreduce.md): one-shot (single barrier, reads only) wins
+  // at 2 ranks and for tiny messages; with multicast bound the switch reduction wins from
+  // ~256 KB up at >= 4 ranks; without it the pull variant is the latency choice up to a few MB.
+  if (world <= 2 || bytes <= (256 << 10) / world * 2) return kOneShot;
+  if (have_multicast && bytes >= (256 << 10)) return kNvls;
+  if (bytes <= (4 << 20)) return kPull;
+  return kTwoShot;
+}
+
 extern "C" int b2d_allreduce_sgd(const b2d_allreduce_desc* d, void* stream) {
   B2D_REQUIRE(d != nullptr, "allreduce_sgd: null descriptor");
   B2D_REQUIRE(d->world >= 1 && d->world <= kMaxRanks, "allreduce_sgd: world must be in [1, %d]", kMaxRanks);
