@@ -122,8 +122,9 @@ __device__ __forceinline__ void rank_barrier(const ArArgs& a, int rank, uint32_t
     const uint32_t* mine = a.sig[rank] + b * kMaxRanks + p;
     long long t_start = 0;
     uint32_t spins = 0, v;
-    // Polling with acquire costs nothing measurable (it only keeps the later loads behind it).
-    while (static_cast<int32_t>((v = ld_acquire_sys(mine)) - e) < 0) {
+    // Poll relaxed (an acquire load per poll made this wait 4-8 us longer on B200); where the barrier
+    // publishes remote writes, ONE acquire load of the satisfied flag orders the later accesses behind it.
+    while (static_cast<int32_t>((v = ld_relaxed_sys(mine)) - e) < 0) {
       if ((++spins & 0x3ff) == 0) {  // a peer died: fail loudly instead of hanging the GPU forever
         const long long now = ar_time_ns();
         if (t_start == 0) t_start = now;
@@ -133,6 +134,7 @@ __device__ __forceinline__ void rank_barrier(const ArArgs& a, int rank, uint32_t
         }
       }
     }
+    if (kPublish) v = ld_acquire_sys(mine);
     if (a.debug) {
       // Monotone epochs: a flag never runs backwards, and a peer can be at most one barrier ahead
       // of this block (it cannot pass barrier e+1 before this block has signalled it).
@@ -158,8 +160,12 @@ __device__ __forceinline__ float4 apply_update(float4 w, float4 s, bool is_param
 
 enum ArAlgo : int { kOneShot = 0, kTwoShot = 1, kNvls = 2, kPull = 3 };
 
-template <int ALGO>
-__global__ void __launch_bounds__(kArThreads) allreduce_sgd_kernel(const ArArgs a) {
+// kW = compile-time bound on the number of ranks (2, 4 or 8): the gather keeps kW x kUnroll float4 in
+// registers, and the kernel has to stay light — its blocks share the SMs with the backward kernels they
+// overlap (two 512-thread blocks per SM must fit next to a GEMM CTA, hence at most 64 registers when
+// kW <= 4; a block that has to wait for a free SM shows up as a late barrier arrival on every peer).
+template <int ALGO, int kW>
+__global__ void __launch_bounds__(kArThreads, kW <= 4 ? 2 : 1) allreduce_sgd_kernel(const ArArgs a) {
   __shared__ uint32_t s_epoch;
   const int rank = a.emulate ? blockIdx.y : a.rank;
   const int world = a.world;
@@ -200,9 +206,9 @@ __global__ void __launch_bounds__(kArThreads) allreduce_sgd_kernel(const ArArgs 
   // before the first use, and only then summed in fixed rank order (identical bits everywhere).
   constexpr int kUnroll = 2;
   auto gather_sum = [&](long long i0, long long limit, float4 (&acc)[kUnroll]) {
-    float4 v[kMaxRanks][kUnroll];
+    float4 v[kW][kUnroll];
 #pragma unroll
-    for (int p = 0; p < kMaxRanks; ++p)
+    for (int p = 0; p < kW; ++p)
       if (p < world) {
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
@@ -213,7 +219,7 @@ __global__ void __launch_bounds__(kArThreads) allreduce_sgd_kernel(const ArArgs 
 #pragma unroll
     for (int u = 0; u < kUnroll; ++u) acc[u] = zero;
 #pragma unroll
-    for (int p = 0; p < kMaxRanks; ++p)
+    for (int p = 0; p < kW; ++p)
       if (p < world) {
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) acc[u] = f4_add(acc[u], v[p][u]);
@@ -320,7 +326,7 @@ __global__ void __launch_bounds__(kArThreads) allreduce_sgd_kernel(const ArArgs 
           multimem_st_f4(reinterpret_cast<float4*>(a.plain ? a.g_mc : a.wo_mc) + i, v);
         } else {
 #pragma unroll
-          for (int p = 0; p < kMaxRanks; ++p)
+          for (int p = 0; p < kW; ++p)
             if (p < world) st_na_f4(reinterpret_cast<float4*>(a.plain ? a.g[p] : a.wo[p]) + i, v);
         }
       }
@@ -340,6 +346,7 @@ __global__ void __launch_bounds__(kArThreads) allreduce_sgd_kernel(const ArArgs 
     dbg[2] += s_t[2] - s_t[1];
     dbg[3] += s_t[3] - s_t[2];
     dbg[4] += t_end - s_t[3];
+    dbg[5] = s_t[0], dbg[6] = s_t[3], dbg[7] = t_end;   // absolute stamps of the last launch: start, past barrier A, end
   }
   if (a.gz != nullptr) {
     if (ALGO == kOneShot || ALGO == kPull) return;
@@ -399,6 +406,7 @@ struct LlArgs {
   float scale;
   int rank, world, emulate, debug;
   long long timeout_ns;
+  long long* dbg;                        // optional: 4 absolute globaltimer stamps per block (last launch)
 };
 
 __device__ __forceinline__ void st_relaxed_sys_u64(unsigned long long* p, unsigned long long v) {
@@ -414,8 +422,11 @@ __global__ void __launch_bounds__(kLlThreads) ll_allreduce_sgd_kernel(const LlAr
   __shared__ uint32_t s_epoch;
   const int rank = a.emulate ? blockIdx.y : a.rank;
   const int world = a.world;
+  long long* dbg = a.dbg == nullptr ? nullptr : a.dbg + 4 * blockIdx.x;
+  if (dbg != nullptr && threadIdx.x == 0) dbg[0] = ar_time_ns();
   pdl_wait();     // this replica's backward has finished writing these gradients
   pdl_trigger();
+  if (dbg != nullptr && threadIdx.x == 0) dbg[1] = ar_time_ns();
   if (threadIdx.x == 0) {
     uint32_t* ep = a.epoch[rank] + blockIdx.x;
     uint32_t e = *ep + 1;
@@ -468,6 +479,7 @@ __global__ void __launch_bounds__(kLlThreads) ll_allreduce_sgd_kernel(const LlAr
   }
   a.wo[rank][idx] = idx < a.n_params ? wv - a.scale * sum : wv + sum;
   if (a.gz[rank] != nullptr) a.gz[rank][idx] = 0.f;
+  if (dbg != nullptr && threadIdx.x == 0) dbg[2] = ar_time_ns();
 }
 
 }  // namespace b2d
@@ -558,10 +570,20 @@ extern "C" int b2d_allreduce_sgd(const b2d_allreduce_desc* d, void* stream) {
                              : static_cast<int>(std::min<long long>(
                                    kMaxArBlocks, std::max<long long>(1, (work4 + kArThreads * 2 - 1) / (kArThreads * 2))));  // ~2 float4 per thread
   blocks = std::min(blocks, kMaxArBlocks);
-  void (*kern)(const ArArgs) = algo == kOneShot  ? allreduce_sgd_kernel<kOneShot>
-                               : algo == kTwoShot ? allreduce_sgd_kernel<kTwoShot>
-                               : algo == kPull    ? allreduce_sgd_kernel<kPull>
-                                                  : allreduce_sgd_kernel<kNvls>;
+  void (*kern)(const ArArgs) = nullptr;
+#define B2D_AR_PICK(W)                                                                    \
+  kern = algo == kOneShot  ? allreduce_sgd_kernel<kOneShot, W>                            \
+         : algo == kTwoShot ? allreduce_sgd_kernel<kTwoShot, W>                           \
+         : algo == kPull    ? allreduce_sgd_kernel<kPull, W>                              \
+                            : allreduce_sgd_kernel<kNvls, W>
+  if (d->world <= 2) {
+    B2D_AR_PICK(2);
+  } else if (d->world <= 4) {
+    B2D_AR_PICK(4);
+  } else {
+    B2D_AR_PICK(8);
+  }
+#undef B2D_AR_PICK
   if (d->emulate) blocks = std::max(1, std::min(blocks, 128 / d->world));  // cooperative: all co-resident
   B2D_REQUIRE(!(algo == kPull && d->plain), "allreduce_sgd: the pull algorithm is fused-SGD only");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -610,6 +632,7 @@ extern "C" int b2d_ll_allreduce_sgd(const b2d_ll_desc* d, void* stream) {
   a.rank = d->rank, a.world = d->world, a.emulate = d->emulate;
   a.debug = ar_env_flag("B200DIST_AR_DEBUG");
   a.timeout_ns = ar_timeout_ns();
+  a.dbg = static_cast<long long*>(d->timeline);
   const int blocks = static_cast<int>((n + kLlThreads - 1) / kLlThreads);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (d->emulate) {

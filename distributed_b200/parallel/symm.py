@@ -41,7 +41,7 @@ class LlDesc(C.Structure):
     _fields_ = [("inbox", _VP8), ("epoch", _VP8), ("w", _VP8), ("w_out", _VP8), ("g", _VP8), ("g_zero", _VP8),
                 ("seg_begin", C.c_int64 * 2), ("seg_end", C.c_int64 * 2), ("nseg", C.c_int),
                 ("n_params", C.c_int64), ("lr", C.c_float), ("rank", C.c_int), ("world", C.c_int),
-                ("emulate", C.c_int)]
+                ("emulate", C.c_int), ("timeline", C.c_void_p)]
 
 
 AR_NO_EXIT_BARRIER, AR_STRICT_ENTRY = 1, 2

@@ -288,7 +288,9 @@ typedef struct b2d_allreduce_desc {
   void* g_zero;     /* double-buffered gradients: this rank's OTHER gradient buffer, zeroed by
                        the kernel (one-shot then runs with a single cross-GPU barrier); NULL =
                        single buffer, zeroed in place after a second barrier              */
-  void* timeline;   /* optional debug: 8 x int64 globaltimer stamps per block, or NULL       */
+  void* timeline;   /* optional debug, 8 x int64 per block or NULL: launches, ns waited for upstream / in the
+                       release / for peers / moving data (sums), then start, past-barrier and end stamps of
+                       the last launch (globaltimer)                                            */
   int64_t seg_begin[2]; /* bucketing: up to two [begin, end) float ranges of the arenas handled  */
   int64_t seg_end[2];   /* by this launch (multiples of 4); nseg == 0 means the whole arena      */
   int nseg;
@@ -323,6 +325,7 @@ typedef struct b2d_ll_desc {
   float lr;
   int rank, world;
   int emulate;      /* all ranks in one cooperative launch on one GPU (tests)                   */
+  void* timeline;   /* optional debug: 4 x int64 globaltimer stamps per block (start, inputs ready, done) */
 } b2d_ll_desc;
 size_t b2d_ll_inbox_bytes(void);
 size_t b2d_ll_epoch_bytes(void);
