@@ -158,7 +158,7 @@ __device__ __forceinline__ float4 apply_update(float4 w, float4 s, bool is_param
   return f4_add(w, s);  // metric tail: running sums
 }
 
-enum ArAlgo : int { kOneShot = 0, kTwoShot = 1, kNvls = 2, kPull = 3 };
+enum ArAlgo : int { kOneShot = 0, kTwoShot = 1, kNvls = 2, kPull = 3, kScattered = 4 };
 
 // kW = compile-time bound on the number of ranks (2, 4 or 8): the gather keeps kW x kUnroll float4 in
 // registers, and the kernel has to stay light — its blocks share the SMs with the backward kernels they
@@ -297,6 +297,36 @@ __global__ void __launch_bounds__(kArThreads, kW <= 4 ? 2 : 1) allreduce_sgd_ker
         }
       }
     }
+  } else if (ALGO == kScattered) {
+    // The producing GEMMs of all replicas have already added their results into the owners' arenas
+    // (gemm_tcgen05.cu, kFlagScatter): my shard of my own G is the complete sum.  Read it locally, zero it
+    // in place for the step after next, update, and broadcast the new weights.
+    const long long per = (seg_e - seg_b + world - 1) / world;
+    const long long s0 = min(seg_e, seg_b + per * rank), s1 = min(seg_e, s0 + per);
+    float4* gl = reinterpret_cast<float4*>(a.g[rank]);
+    const float4* wl = reinterpret_cast<const float4*>(a.w[rank]);
+    for (long long i0 = s0 + t0; i0 < s1; i0 += stride * 4) {
+      float4 acc[4], wv[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const long long i = i0 + u * stride;
+        if (i < s1) acc[u] = __ldcg(gl + i), wv[u] = wl[i];
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const long long i = i0 + u * stride;
+        if (i >= s1) continue;
+        gl[i] = zero;
+        const float4 v = apply_update(wv[u], acc[u], i < a.n_params4, a.scale);
+        if (a.wo_mc != nullptr) {
+          multimem_st_f4(reinterpret_cast<float4*>(a.wo_mc) + i, v);
+        } else {
+#pragma unroll
+          for (int p = 0; p < kW; ++p)
+            if (p < world) st_na_f4(reinterpret_cast<float4*>(a.wo[p]) + i, v);
+        }
+      }
+    }
   } else {
     const long long per = (seg_e - seg_b + world - 1) / world;
     const long long s0 = min(seg_e, seg_b + per * rank), s1 = min(seg_e, s0 + per);
@@ -347,6 +377,11 @@ __global__ void __launch_bounds__(kArThreads, kW <= 4 ? 2 : 1) allreduce_sgd_ker
     dbg[3] += s_t[3] - s_t[2];
     dbg[4] += t_end - s_t[3];
     dbg[5] = s_t[0], dbg[6] = s_t[3], dbg[7] = t_end;   // absolute stamps of the last launch: start, past barrier A, end
+  }
+  if (ALGO == kScattered) {
+    // in-place zeroing is done; the other gradient buffer's range was zeroed the same way one step ago
+    if (!a.no_exit) rank_barrier<true>(a, rank, &s_epoch);
+    return;
   }
   if (a.gz != nullptr) {
     if (ALGO == kOneShot || ALGO == kPull) return;
@@ -572,10 +607,11 @@ extern "C" int b2d_allreduce_sgd(const b2d_allreduce_desc* d, void* stream) {
   blocks = std::min(blocks, kMaxArBlocks);
   void (*kern)(const ArArgs) = nullptr;
 #define B2D_AR_PICK(W)                                                                    \
-  kern = algo == kOneShot  ? allreduce_sgd_kernel<kOneShot, W>                            \
-         : algo == kTwoShot ? allreduce_sgd_kernel<kTwoShot, W>                           \
-         : algo == kPull    ? allreduce_sgd_kernel<kPull, W>                              \
-                            : allreduce_sgd_kernel<kNvls, W>
+  kern = algo == kOneShot    ? allreduce_sgd_kernel<kOneShot, W>                          \
+         : algo == kTwoShot   ? allreduce_sgd_kernel<kTwoShot, W>                         \
+         : algo == kPull      ? allreduce_sgd_kernel<kPull, W>                            \
+         : algo == kScattered ? allreduce_sgd_kernel<kScattered, W>                       \
+                              : allreduce_sgd_kernel<kNvls, W>
   if (d->world <= 2) {
     B2D_AR_PICK(2);
   } else if (d->world <= 4) {
@@ -585,7 +621,8 @@ extern "C" int b2d_allreduce_sgd(const b2d_allreduce_desc* d, void* stream) {
   }
 #undef B2D_AR_PICK
   if (d->emulate) blocks = std::max(1, std::min(blocks, 128 / d->world));  // cooperative: all co-resident
-  B2D_REQUIRE(!(algo == kPull && d->plain), "allreduce_sgd: the pull algorithm is fused-SGD only");
+  B2D_REQUIRE(!((algo == kPull || algo == kScattered) && d->plain),
+              "allreduce_sgd: the pull and scattered algorithms are fused-SGD only");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (d->emulate) {
     // All ranks in one launch: the blocks wait on one another, so they must be co-resident.

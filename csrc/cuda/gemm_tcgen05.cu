@@ -33,6 +33,19 @@ enum GemmFlags : int {
   kFlagFinalize = 4,    // split-K: meet in workspace, last CTA applies the epilogue
   kFlagOutBf16 = 8,
   kFlagMaskBf16 = 16,   // the ReLU mask tensor is bf16 (same row pitch convention, in elements)
+  kFlagScatter = 32,    // accumulate into the gradient arena of the replica that OWNS each element (reduce-scatter)
+};
+
+// GEMM -> reduce-scatter in one kernel: D is a range of the replicated gradient arena, cut into `world`
+// equal shards; every 16-byte vector of the result is added (red.add over NVLink) into the arena of the
+// replica that owns its shard, so when all replicas' GEMMs have finished each owner holds the complete sum
+// of its shard and nobody has to fetch anything (csrc/cuda/allreduce.cu, kScattered).
+struct ScatterArgs {
+  float* base[8];        // gradient arena of every replica (peer-mapped); base[rank] is local
+  long long d_off;       // float offset of D[0][0] inside the arena
+  long long seg_begin;   // float offset of the sharded range
+  long long per;         // floats per shard (multiple of 4)
+  int world;
 };
 
 // Implicit-GEMM convolution view of the A operand (stride-1 NHWC convolutions): the M tile is a
@@ -76,6 +89,7 @@ struct GemmArgs {
   int kb_total, kb_per_split, splits;
   int m_tiles, n_tiles;   // tile grid (persistent CTAs walk m_tiles * n_tiles * splits tiles)
   int flags;
+  ScatterArgs sc;
 };
 
 __device__ __forceinline__ long long gtime_ns() {
@@ -86,6 +100,12 @@ __device__ __forceinline__ long long gtime_ns() {
 
 __device__ __forceinline__ void red_add_f4(float* p, float a, float b, float c, float d) {
   asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b),
+               "f"(c), "f"(d)
+               : "memory");
+}
+
+__device__ __forceinline__ void red_add_f4_sys(float* p, float a, float b, float c, float d) {
+  asm volatile("red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b),
                "f"(c), "f"(d)
                : "memory");
 }
@@ -130,7 +150,11 @@ __device__ __forceinline__ void epilogue_store4(const GemmArgs& a, int row, int 
     v0 = m.x > 0.f ? v0 : 0.f, v1 = m.y > 0.f ? v1 : 0.f;
     v2 = m.z > 0.f ? v2 : 0.f, v3 = m.w > 0.f ? v3 : 0.f;
   }
-  if (a.flags & kFlagAccumulate) {
+  if (a.flags & kFlagScatter) {
+    const long long idx = a.sc.d_off + (long long)row * a.ldd + col;
+    const int owner = min(a.sc.world - 1, static_cast<int>((idx - a.sc.seg_begin) / a.sc.per));
+    red_add_f4_sys(a.sc.base[owner] + idx, v0, v1, v2, v3);
+  } else if (a.flags & kFlagAccumulate) {
     red_add_f4(reinterpret_cast<float*>(a.D) + (long long)row * a.ldd + col, v0, v1, v2, v3);
   } else if (OUT_BF16 && (a.flags & kFlagOutBf16)) {
     uint2 p;
@@ -833,6 +857,26 @@ extern "C" int b2d_gemm_plan_run(const b2d_gemm_plan* p, void* stream) {
 }
 
 extern "C" void b2d_gemm_plan_destroy(b2d_gemm_plan* p) { delete p; }
+
+// Turns an accumulating fp32 plan into GEMM -> reduce-scatter (see ScatterArgs).
+extern "C" int b2d_gemm_plan_set_scatter(b2d_gemm_plan* p, const b2d_gemm_scatter* sc) {
+  B2D_REQUIRE(p != nullptr && sc != nullptr, "gemm_plan_set_scatter: null argument");
+  GemmArgs& a = p->args;
+  B2D_REQUIRE((a.flags & kFlagAccumulate) != 0 && (a.flags & (kFlagOutBf16 | kFlagFinalize)) == 0,
+              "gemm_plan_set_scatter: the plan must accumulate into an fp32 output");
+  B2D_REQUIRE(sc->world >= 1 && sc->world <= 8 && sc->per > 0 && sc->per % 4 == 0 && sc->d_off % 4 == 0 &&
+                  sc->seg_begin % 4 == 0 && sc->d_off >= sc->seg_begin,
+              "gemm_plan_set_scatter: bad shard geometry");
+  for (int r = 0; r < sc->world; ++r) {
+    B2D_REQUIRE(sc->base[r] != nullptr, "gemm_plan_set_scatter: null arena of replica %d", r);
+    a.sc.base[r] = static_cast<float*>(sc->base[r]);
+  }
+  B2D_REQUIRE(a.sc.base[sc->rank] + sc->d_off == static_cast<float*>(a.D),
+              "gemm_plan_set_scatter: D is not at d_off inside this replica's arena");
+  a.sc.d_off = sc->d_off, a.sc.seg_begin = sc->seg_begin, a.sc.per = sc->per, a.sc.world = sc->world;
+  a.flags |= kFlagScatter;
+  return B2D_OK;
+}
 
 // Latency analysis: 16 globaltimer stamps per CTA are written to `buf` (start, prologue done,
 // upstream complete, first tiles landed, MMAs issued, accumulator ready, epilogue done, end).

@@ -31,6 +31,11 @@ class GemmDesc(C.Structure):
     ]
 
 
+class GemmScatter(C.Structure):
+    _fields_ = [("base", C.c_void_p * 8), ("d_off", C.c_int64), ("seg_begin", C.c_int64), ("per", C.c_int64),
+                ("rank", C.c_int), ("world", C.c_int)]
+
+
 class GemmGeometry(C.Structure):
     _fields_ = [(n, C.c_int) for n in
                 ("block_n", "m_tiles", "n_tiles", "splits", "k_blocks", "stages", "smem_bytes", "ctas")]
@@ -48,6 +53,7 @@ def _declare(lib) -> None:
     lib.b2d_gemm_plan_run.argtypes = [C.c_void_p, C.c_void_p]
     lib.b2d_gemm_plan_destroy.argtypes = [C.c_void_p]
     lib.b2d_gemm_plan_destroy.restype = None
+    lib.b2d_gemm_plan_set_scatter.argtypes = [C.c_void_p, C.POINTER(GemmScatter)]
     # Everything else is declared by the op wrappers next to their use (see ops/).
 
 

@@ -30,6 +30,7 @@ class CudaBackend:
         self.device = torch.device(device)
         self.act_dtype = act_dtype      # storage type of 4-D activations (fp32, or bf16 = mixed precision)
         self.plans = []                 # keep GemmPlans (TMA descriptors) alive
+        self.scattered = []             # arena ranges reduce-scattered by their producing GEMM (see dense_wgrad)
         self._params = self._shadow = None
         self._cols, self._casts = {}, {}
 
@@ -244,10 +245,27 @@ class CudaBackend:
             return self._plan(x, w, y, b_mn_major=True, bias=b, relu=relu)
         return lambda: nn.sgemm_simt(x, w, y, bias=b, relu=relu)
 
+    # GEMM -> reduce-scatter (set by the trainer before lowering a step whose update is overlapped):
+    # ``scatter_target`` = {"bases": gradient arena of every replica, "local": this replica's arena tensor,
+    # "rank", "world", "min_floats"}; ``scattered`` collects the arena ranges whose weight-gradient GEMM adds
+    # its result straight into the owning replica's arena.
+    scatter_target = None
+
     def dense_wgrad(self, x, dy, dw, db):
         k, n = dw.shape
         if self._tc_ok(k, n):
-            gemm = self._plan(x, dy, dw, a_mn_major=True, b_mn_major=True, accumulate=True)
+            plan = GemmPlan(x, dy, dw, a_mn_major=True, b_mn_major=True, accumulate=True)
+            self.plans.append(plan)
+            gemm = plan.run
+            st = self.scatter_target
+            if (st is not None and plan.geometry.splits == 1 and dw.numel() >= st["min_floats"]
+                    and dw.numel() % 4 == 0 and dw.is_contiguous()):
+                off = (dw.data_ptr() - st["local"].data_ptr()) // 4
+                world = st["world"]
+                per = -(-(dw.numel() // 4) // world) * 4           # the all-reduce kernel's shard size, in floats
+                if 0 <= off and off + dw.numel() <= st["local"].numel() and off % 4 == 0:
+                    plan.set_scatter(st["bases"], off, off, per, st["rank"])
+                    self.scattered.append((off, off + dw.numel()))
         else:
             def gemm():
                 nn.sgemm_simt(x, dy, dw, trans_a=True, accumulate=True)

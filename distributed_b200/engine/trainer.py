@@ -160,8 +160,15 @@ class Trainer:
             for slot in range(n_slots):
                 g_slot = self.grad_bufs[slot % len(self.grad_bufs)]
                 w_slot = self.param_bufs[slot % len(self.param_bufs)]
+                overlapped = len(self.param_bufs) == 2
+                # GEMM -> reduce-scatter: with the overlapped update, large Dense weight-gradient GEMMs add their
+                # result straight into the owning replica's gradient arena over NVLink (cuda_backend.dense_wgrad)
+                be.scattered = []
+                be.scatter_target = self.comm.scatter_target(g_slot) if overlapped else None
                 prog = lower(self.layers, self.batch, be, lay, w_slot, g_slot,
                              self.x_in[slot], self.y_in[slot], lr=self.lr)
+                prog.scattered = sorted(be.scattered)
+                be.scatter_target = None
                 sched = None
                 if len(self.param_bufs) == 2:
                     # Default for peer-memory replicas: the update is a bucket schedule overlapped with the
@@ -170,8 +177,8 @@ class Trainer:
                     early, late_segs = self._bucket_plan(prog)
                     fns, late, desc = self.comm.make_step_updates(
                         be, w_slot, w_other, g_slot, g_other, lay.n_params, self.lr,
-                        [(b, e) for _, b, e in early], late_segs)
-                    sched = ([(n, f) for (n, _, _), f in zip(early, fns)], late)
+                        [(b, e, sc) for _, b, e, sc in early], late_segs)
+                    sched = ([(n, f) for (n, _, _, _), f in zip(early, fns)], late)
                     upd = late
                     self.update_schedule = desc
                 elif len(self.grad_bufs) > 1:
@@ -188,8 +195,13 @@ class Trainer:
                 # warm every kernel once outside capture (module load, smem attributes), on zero
                 # inputs with the update skipped so the weights are untouched
                 self.progs[0].run()
+                self.stream.synchronize()
+                if getattr(self.progs[0], "scattered", None):
+                    self.comm.barrier()           # every replica's warm-up pushes into the peers' arenas have landed
                 self.grad_bufs[0].zero_()
                 self.stream.synchronize()
+                if getattr(self.progs[0], "scattered", None):
+                    self.comm.barrier()           # nobody starts before every arena is clean again
                 for slot in range(n_slots):
                     prog = self.progs[slot]
                     nl.check(lib.b2d_exec_begin_capture(h), "b2d_exec_begin_capture")
@@ -289,8 +301,9 @@ class Trainer:
     def _bucket_plan(self, prog):
         """Cut the gradient arena into buckets for the overlapped update.
 
-        Returns (early, late_segments).  ``early`` = [(n, begin, end)]: the floats [begin, end) are final once the
-        first n backward launches are done; buckets run from the last layer towards the first, each at least
+        Returns (early, late_segments).  ``early`` = [(n, begin, end, scattered)]: the floats [begin, end) are final
+        once the first n backward launches are done (``scattered``: already summed into their owners' arenas by the
+        producing GEMM); buckets run from the last layer towards the first, each at least
         B200DIST_BUCKET_MB (default 16 MB) unless the model is smaller, whole top-level layers only.
         ``late_segments``: what only becomes final when the backward pass ends — the first parametrised layer —
         plus the metric tail; it is the closing launch of the step."""
@@ -299,19 +312,42 @@ class Trainer:
         n_bwd = len(prog.backward)
         target = max(1, int(float(os.environ.get("B200DIST_BUCKET_MB", "16")) * (1 << 20) / 4))
         table = list(prog.grad_final)
-        early, end = [], lay.n_params
+        cuts, end = [], lay.n_params
         rest = None                         # (n, begin) of the lowest layer that may still join an early bucket
         for begin, n in reversed(table[1:]):
             if n >= n_bwd or begin <= 0:
                 break
             rest = (n, begin)
             if end - begin >= target:
-                early.append((n, begin, end))
+                cuts.append((n, begin, end))
                 end, rest = begin, None
         if rest is not None and rest[1] < end:
-            early.append((rest[0], rest[1], end))
+            cuts.append((rest[0], rest[1], end))
             end = rest[1]
-        return early, [(0, end), (lay.n_params, lay.n_total)]
+        # Ranges that their weight-gradient GEMM has already reduce-scattered become buckets of their own
+        # (the update only has to finish them); what is left of a bucket around them is reduced as before.
+        early = []
+        for n, b, e in cuts:
+            pos = b
+            for sb, se in getattr(prog, "scattered", []):
+                if sb < b or se > e:
+                    continue
+                if sb > pos:
+                    early.append((n, pos, sb, False))
+                early.append((n, sb, se, True))
+                pos = se
+            if pos < e:
+                early.append((n, pos, e, False))
+        early.sort(key=lambda t: t[0])
+        late = [(0, end), (lay.n_params, lay.n_total)]
+        # A small plain remainder that touches the metric tail (biases and the last layers of a small model)
+        # rides in the closing exchange instead of paying for a launch and a barrier of its own.
+        ll_max = getattr(self.comm, "ll_max_floats", 0)
+        tails = [t for t in early if not t[3] and t[2] == lay.n_params]
+        if tails and (end + lay.n_total - tails[0][1]) <= ll_max:
+            early.remove(tails[0])
+            late = [(0, end), (tails[0][1], lay.n_total)]
+        return early, late
 
     # ------------------------------------------------------------------------------
     def describe(self) -> list[str]:

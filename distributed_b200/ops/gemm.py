@@ -75,6 +75,15 @@ class GemmPlan:
         self._h = h
         self._lib = lib
 
+    def set_scatter(self, bases, d_off: int, seg_begin: int, per: int, rank: int) -> None:
+        """GEMM -> reduce-scatter: add every 16-byte vector of the result into the gradient arena of the
+        replica that owns it (``bases``: every replica's arena as mapped here; offsets in floats)."""
+        sc = nl.GemmScatter()
+        for p, b in enumerate(bases):
+            sc.base[p] = b
+        sc.d_off, sc.seg_begin, sc.per, sc.rank, sc.world = d_off, seg_begin, per, rank, len(bases)
+        nl.check(self._lib.b2d_gemm_plan_set_scatter(self._h, C.byref(sc)), "b2d_gemm_plan_set_scatter")
+
     def run(self, stream=None) -> None:
         nl.check(self._lib.b2d_gemm_plan_run(self._h, _stream_ptr(stream)), "b2d_gemm_plan_run")
 

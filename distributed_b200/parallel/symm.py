@@ -188,6 +188,16 @@ class SymmComm:
         gs = [self._tensor(self.off_g, n)] + ([self._tensor(self.off_g2, n)] if ping_pong else [])
         return ws, gs
 
+    def scatter_target(self, g):
+        """Where a weight-gradient GEMM may add its result directly (GEMM -> reduce-scatter, ops/gemm.py):
+        gradient arena ``g`` of every replica as mapped in this process."""
+        if os.environ.get("B200DIST_FUSED_RS", "1") == "0":
+            return None
+        off = self._off_of(g)
+        return {"bases": [self.base[p] + off for p in range(self.world)], "local": g, "rank": self.rank,
+                "world": self.world,
+                "min_floats": int(float(os.environ.get("B200DIST_FUSED_RS_MIN_KB", "256")) * 256)}
+
     def _off_of(self, t):
         return t.data_ptr() - self.base[self.rank]
 
@@ -207,10 +217,13 @@ class SymmComm:
 
         Returns (list of early launches, late launch, description)."""
         n_total = w_in.numel()
-        fns = []
-        for (b0, e0) in early:
+        fns, names = [], []
+        for (b0, e0, scattered) in early:
             fns.append(self.make_update(be, w_in, g, n_params, lr, grads_other=g_other, segments=[(b0, e0)],
-                                        channel=0, w_out=w_out, flags=AR_NO_EXIT_BARRIER))
+                                        channel=0, w_out=w_out, flags=AR_NO_EXIT_BARRIER,
+                                        algo=4 if scattered else None))
+            names.append("reduce-scattered by the weight-gradient GEMM" if scattered
+                         else ALGO_NAMES[self.pick(e0 - b0)])
         n_late = sum(e - b for b, e in late_segments)
         if n_late <= self.ll_max_floats and os.environ.get("B200DIST_LL", "1") != "0":
             d = LlDesc()
@@ -237,7 +250,6 @@ class SymmComm:
             late = self.make_update(be, w_in, g, n_params, lr, grads_other=g_other, segments=segs, channel=1,
                                     w_out=w_out)
             late_name = ALGO_NAMES[self.pick(max(e - b for b, e in segs))]
-        names = [ALGO_NAMES[self.pick(e - b)] for b, e in early]
         desc = (f"{len(early)} overlapped bucket(s) [{', '.join(names)}] + closing bucket [{late_name}]"
                 if early else f"closing bucket [{late_name}]")
         return fns, late, desc

@@ -88,6 +88,20 @@ size_t b2d_gemm_counter_count(const b2d_gemm_desc* desc);
 int b2d_gemm_plan_create(const b2d_gemm_desc* desc, b2d_gemm_plan** out);
 int b2d_gemm_plan_run(const b2d_gemm_plan* plan, void* stream);
 void b2d_gemm_plan_destroy(b2d_gemm_plan* plan);
+/* GEMM -> reduce-scatter in one kernel (the weight-gradient GEMM followed by the gradient all-reduce of
+ * README.md:403): an accumulating fp32 plan whose D is a range of the replicated gradient arena adds every
+ * 16-byte vector of its result into the arena of the replica that owns that vector's shard — directly over
+ * NVLink from the epilogue — instead of into the local arena.  The shard of an element at arena offset i is
+ * min(world - 1, (i - seg_begin) / per); b2d_allreduce_sgd with algo 4 then finishes the update from the
+ * owner's complete sums. */
+typedef struct b2d_gemm_scatter {
+  void* base[8];      /* gradient arena of every replica as mapped in this process   */
+  int64_t d_off;      /* float offset of D inside the arena                          */
+  int64_t seg_begin;  /* float offset of the sharded range                           */
+  int64_t per;        /* floats per shard (multiple of 4)                            */
+  int rank, world;
+} b2d_gemm_scatter;
+int b2d_gemm_plan_set_scatter(b2d_gemm_plan* plan, const b2d_gemm_scatter* sc);
 /* Latency analysis (tools/gemm_timeline.py): attach a buffer of 16 x int64 per persistent CTA (geometry.ctas)
  * that receives %globaltimer stamps — start, prologue done, upstream kernel complete, first tiles landed, first
  * tile's MMAs issued, accumulator visible to the epilogue, epilogue done, end — or detach with NULL. */
@@ -268,7 +282,9 @@ int b2d_symm_destroy(b2d_symm* s);
  * Fused gradient all-reduce + 1/world averaging + SGD + metric sums + gradient zeroing over
  * peer memory (csrc/cuda/allreduce.cu): replaces "batch_all_reduce: 6 all-reduces", the four
  * metric all-reduces and the optimizer step of the reference (README.md:403-407, 302).
- * algo: 0 one-shot, 1 two-shot (weights all-gather), 2 NVLS multicast, -1 by size.
+ * algo: 0 one-shot, 1 two-shot (weights all-gather), 2 NVLS multicast, 3 two-shot pull, -1 by size;
+ * 4 = the gradients were already reduce-scattered by the producing GEMM (b2d_gemm_plan_set_scatter): every
+ * owner updates its shard from its own arena and broadcasts the weights.
  * ------------------------------------------------------------------------------------- */
 typedef struct b2d_allreduce_desc {
   void* w[8];      /* weight arenas of every rank (peer-mapped)          */

@@ -183,6 +183,69 @@ def test_nvls_kernel_on_one_gpu():
         lib.b2d_symm_destroy(h)
 
 
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_gemm_reduce_scatter_epilogue_then_scattered_update(world):
+    """GEMM -> reduce-scatter in one kernel, then the update that finishes it (single-GPU emulation: the
+    replicas' gradient arenas are separate buffers on this device).  Every replica's weight-gradient GEMM adds
+    each 16-byte vector of its result into the arena of the replica owning that vector's shard; afterwards the
+    owners hold the complete sums, everything else is untouched, and the algo-4 update reproduces plain SGD on
+    the summed gradient."""
+    from distributed_b200._native import cuda_lib as nl
+    from distributed_b200.ops.gemm import GemmPlan
+    from distributed_b200.parallel import symm
+    lib = nl.lib()
+    symm._declare(lib)
+    M, N, K, off, lr = 5408, 64, 64, 320, 0.1                            # dense-64 weight gradient of the README model
+    n_params = off + M * N + 96
+    n_total = n_params + 4
+    gen = torch.Generator(device="cuda").manual_seed(world)
+    G = [torch.zeros(n_total, device="cuda") for _ in range(world)]
+    xs = [torch.randn(K, M, device="cuda", generator=gen) for _ in range(world)]      # x^T . dy, both MN-major
+    dys = [torch.randn(K, N, device="cuda", generator=gen) for _ in range(world)]
+    per = -(-(M * N // 4) // world) * 4
+    plans = []
+    for r in range(world):
+        dw = G[r][off:off + M * N].view(M, N)
+        p = GemmPlan(xs[r], dys[r], dw, a_mn_major=True, b_mn_major=True, accumulate=True)
+        assert p.geometry.splits == 1
+        p.set_scatter([g.data_ptr() for g in G], off, off, per, r)
+        plans.append(p)
+    for p in plans:
+        p.run()
+    torch.cuda.synchronize()
+    total = sum(x.double().t() @ dy.double() for x, dy in zip(xs, dys)).reshape(-1)
+    for r in range(world):
+        got = G[r][off:off + M * N].double()
+        lo, hi = min(M * N, per * r), min(M * N, per * (r + 1))
+        scale = total.abs().max().item()
+        assert (got[lo:hi] - total[lo:hi]).abs().max().item() < 2e-2 * scale      # tf32 products, fp32 sums
+        assert got[:lo].abs().max().item() == 0 if lo else True
+        assert got[hi:].abs().max().item() == 0 if hi < M * N else True
+        assert G[r][:off].abs().max().item() == 0 and G[r][off + M * N:].abs().max().item() == 0
+    # the update that finishes the bucket
+    w0 = torch.randn(n_total, device="cuda", generator=gen)
+    W = [w0.clone() for _ in range(world)]
+    sig = [torch.zeros(lib.b2d_allreduce_signal_bytes() // 4, dtype=torch.int32, device="cuda") for _ in range(world)]
+    ep = [torch.zeros(lib.b2d_allreduce_epoch_bytes() // 4, dtype=torch.int32, device="cuda") for _ in range(world)]
+    summed = torch.zeros(M * N, device="cuda")
+    for r in range(world):
+        summed += G[r][off:off + M * N]
+    d = symm.AllreduceDesc()
+    for p in range(world):
+        d.w[p], d.g[p], d.sig[p], d.epoch[p] = W[p].data_ptr(), G[p].data_ptr(), sig[p].data_ptr(), ep[p].data_ptr()
+    d.n_params, d.n_total, d.lr = n_params, n_total, lr
+    d.rank, d.world, d.algo, d.emulate, d.plain, d.blocks = 0, world, 4, 1, 0, 0
+    d.nseg, d.seg_begin[0], d.seg_end[0] = 1, off, off + M * N
+    nl.check(lib.b2d_allreduce_sgd(C.byref(d), torch.cuda.current_stream().cuda_stream), "allreduce scattered")
+    torch.cuda.synchronize()
+    expect = w0.clone()
+    expect[off:off + M * N] -= lr / world * summed
+    for p in range(world):
+        assert torch.equal(W[p], W[0])
+        assert G[p].abs().max().item() == 0
+    assert torch.allclose(W[0], expect, atol=1e-6, rtol=1e-6)
+
+
 def test_algo_dispatch_by_size():
     from distributed_b200._native import cuda_lib as nl
     from distributed_b200.parallel import symm
