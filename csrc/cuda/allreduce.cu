@@ -547,7 +547,10 @@ extern "C" int b2d_allreduce_pick_algo(int64_t n_total_floats, int world, int ha
   // Measured on 8 x B200 (profiles/r01_allreduce.md): one-shot (single barrier, reads only) wins
   // at 2 ranks and for tiny messages; with multicast bound the switch reduction wins from
   // ~256 KB up at >= 4 ranks; without it the pull variant is the latency choice up to a few MB.
-  if (world <= 2 || bytes <= (256 << 10) / world * 2) return kOneShot;
+  // At 2 ranks one-shot and two-shot move the same bytes, but two-shot uses both link directions: it wins
+  // from a few MB up (16 MB: 48 vs 54 us).
+  if (world <= 2) return bytes >= (4 << 20) ? kTwoShot : kOneShot;
+  if (bytes <= (256 << 10) / world * 2) return kOneShot;
   if (have_multicast && bytes >= (256 << 10)) return kNvls;
   if (bytes <= (4 << 20)) return kPull;
   return kTwoShot;

@@ -256,4 +256,5 @@ def test_algo_dispatch_by_size():
     assert lib.b2d_allreduce_pick_algo(347204, 8, 1) == 2          # README gradient with multicast: NVLS
     assert lib.b2d_allreduce_pick_algo(1 << 24, 8, 1) == 2         # 64 MB with multicast: NVLS
     assert lib.b2d_allreduce_pick_algo(1 << 24, 8, 0) == 1         # 64 MB without multicast: two-shot
-    assert lib.b2d_allreduce_pick_algo(1 << 24, 2, 0) == 0         # 2 ranks: one-shot == two-shot traffic
+    assert lib.b2d_allreduce_pick_algo(347204, 2, 1) == 0          # 2 ranks, README gradient: one-shot (one barrier)
+    assert lib.b2d_allreduce_pick_algo(1 << 24, 2, 0) == 1         # 2 ranks, 64 MB: two-shot uses both directions

@@ -109,7 +109,7 @@ def test_debug_mode_stress_random_delays_poison_and_monotone_flags(algo):
     weight gradients, which differs from run to run)."""
     from distributed_b200.launch import barrier_apply
     n = min(_ngpu(), 8)
-    steps = 400
+    steps = 300
     ref = json.loads(barrier_apply(lambda ctx: _worker(ctx, n, algo, steps=steps, epochs=1), n, timeout=900)[0])
     res = [json.loads(s) if s.startswith("{") else s for s in
            barrier_apply(lambda ctx: _worker(ctx, n, algo, steps=steps, epochs=1,
@@ -118,9 +118,9 @@ def test_debug_mode_stress_random_delays_poison_and_monotone_flags(algo):
     for r in res:
         assert all(np.isfinite(v) for v in r["digest"]) and np.isfinite(r["loss"][0])
         assert r["digest"] == res[0]["digest"]
-    assert abs(res[0]["loss"][0] - ref["loss"][0]) < 1e-3
+    assert abs(res[0]["loss"][0] - ref["loss"][0]) < 2e-3
     for a, b in zip(res[0]["digest"], ref["digest"]):
-        assert abs(a - b) <= 1e-3 * max(abs(a), 1.0)
+        assert abs(a - b) <= 5e-3 * max(abs(a), 1.0)        # sum |w| per tensor; a wrong update is off by far more
 
 
 def _allreduce_vs_nccl(ctx, n):
