@@ -585,6 +585,202 @@ __global__ void __launch_bounds__(256, 2) gemm_tc_kernel(const __grid_constant__
   if (dbg != nullptr && threadIdx.x == 0) dbg[7] = gtime_ns();
 }
 
+
+// ----------------------------------------------------------------------------------------
+// CTA-pair GEMM (tcgen05 cta_group::2) for the long-K regime.
+//
+// A cluster of two CTAs (two SMs of one TPC) owns one 256 x BLOCK_N output tile.  CTA r of the pair loads
+// rows [128 r, 128 r + 128) of the A tile and columns [BLOCK_N/2 r, ...) of the B tile into its own ring —
+// half of B per SM, so each stage costs 16 KB + BLOCK_N/2 x 128 B instead of 16 KB + BLOCK_N x 128 B — and
+// credits the bytes to the LEADER's full barrier.  One thread of the leader issues M = 256 MMAs that read both
+// CTAs' shared memory; each CTA accumulates its 128 rows x BLOCK_N columns in its own tensor memory
+// (double-buffered) and drains them with its own epilogue warps.  tcgen05.commit arrives on both CTAs'
+// barriers.  No operand is multicast: every byte of A and B is loaded by exactly one CTA.
+// ----------------------------------------------------------------------------------------
+template <MmaKind KIND, bool A_MN, bool B_MN, int BLOCK_N, bool OUT_BF16>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(256, 1)
+    gemm_tc_pair_kernel(const __grid_constant__ GemmArgs args) {
+  constexpr int HALF_N = BLOCK_N / 2;
+  using Cfg = GemmCfg<KIND, A_MN, B_MN, HALF_N>;           // per-CTA ring geometry
+  constexpr uint32_t IDESC =
+      umma_idesc(KIND == MmaKind::TF32 ? 2u : 1u, A_MN ? 1u : 0u, B_MN ? 1u : 0u, 2 * kBlockM, BLOCK_N);
+  const int STAGES = args.stages;
+  constexpr int STAGE_BYTES = Cfg::STAGE_BYTES;
+  constexpr int BLOCK_K = Cfg::BLOCK_K;
+  constexpr uint32_t ACC_COLS = BLOCK_N;                    // one accumulator: 128 lanes x BLOCK_N fp32 columns
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);   // used in the leader only
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;      // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;      // [2], used in the leader only (8 arrivals: 4 warps x 2 CTAs)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t cta_rank = cluster_ctarank();
+  const bool leader = cta_rank == 0;
+  const int pairs = gridDim.x >> 1, pair = blockIdx.x >> 1;
+  const int total_tiles = args.m_tiles * args.n_tiles;       // m_tiles counts 256-row tiles here
+  const uint32_t tmem_cols = total_tiles > pairs ? 2 * ACC_COLS : ACC_COLS;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&args.tmA);
+    tma_prefetch_desc(&args.tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tmem_full_bar[b], 1);
+      mbar_init(&tmem_empty_bar[b], 8);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc_pair(tmem_slot, tmem_cols);
+  tc_fence_before();
+  cluster_sync_all();          // both CTAs' barriers are initialised and both allocations are done
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
+  pdl_trigger();
+
+  // Tile order: column groups of kGroupN tiles, rows fastest inside a group, so the tiles in flight at any
+  // time (one per pair) share a few row blocks of A and a few column blocks of B that fit in L2 together;
+  // B is then read from HBM once and A once per group instead of B once per wave.
+  constexpr int kGroupN = 8;
+  auto decode = [&](int tile, int& mt, int& nt) {
+    const int per_group = kGroupN * args.m_tiles;
+    const int grp = tile / per_group, r = tile - grp * per_group;
+    const int width = min(kGroupN, args.n_tiles - grp * kGroupN);
+    mt = r / width;
+    nt = grp * kGroupN + (r - mt * width);
+  };
+
+  if (warp == 0) {
+    // ===== TMA producer (both CTAs; bytes are credited to the leader's full barrier) =====
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int tile = pair; tile < total_tiles; tile += pairs) {
+        int mt, nt;
+        decode(tile, mt, nt);
+        const int m0 = mt * 2 * kBlockM + static_cast<int>(cta_rank) * kBlockM;
+        const int n0 = nt * BLOCK_N + static_cast<int>(cta_rank) * HALF_N;
+        for (int kb = 0; kb < args.kb_total; ++kb, ++it) {
+          const int stage = it % STAGES;
+          const uint32_t phase = (it / STAGES) & 1;
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * STAGE_BYTES;
+          uint8_t* sb = sa + kABytes;
+          const int k0 = kb * BLOCK_K;
+          const uint32_t bar = mapa_u32(&full_bar[stage], 0);
+          if (leader) mbar_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
+          if constexpr (!A_MN) {
+            tma_load_2d_pair(sa, &args.tmA, bar, k0, m0);
+          } else {
+#pragma unroll
+            for (int a = 0; a < kBlockM / Cfg::ATOM_E; ++a)
+              tma_load_2d_pair(sa + a * (BLOCK_K * 128), &args.tmA, bar, m0 + a * Cfg::ATOM_E, k0);
+          }
+          if constexpr (!B_MN) {
+            tma_load_2d_pair(sb, &args.tmB, bar, k0, n0);
+          } else {
+#pragma unroll
+            for (int a = 0; a < HALF_N / Cfg::ATOM_E; ++a)
+              tma_load_2d_pair(sb + a * (BLOCK_K * 128), &args.tmB, bar, n0 + a * Cfg::ATOM_E, k0);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: one thread of the leader CTA drives both SMs' tensor cores =====
+    if (leader && lane == 0) {
+      uint32_t it = 0, t = 0;
+      for (int tile = pair; tile < total_tiles; tile += pairs, ++t) {
+        const uint32_t buf = t & 1;
+        mbar_wait(&tmem_empty_bar[buf], ((t >> 1) & 1) ^ 1);   // both CTAs' epilogues have drained this accumulator
+        tc_fence_after();
+        const uint32_t acc = tmem_base + buf * ACC_COLS;
+        for (int kb = 0; kb < args.kb_total; ++kb, ++it) {
+          const int stage = it % STAGES;
+          const uint32_t phase = (it / STAGES) & 1;
+          mbar_wait(&full_bar[stage], phase);                    // both CTAs' halves have landed
+          tc_fence_after();
+          const uint32_t a_base = smem_u32(smem + stage * STAGE_BYTES);
+          const uint32_t b_base = a_base + kABytes;
+#pragma unroll
+          for (int j = 0; j < BLOCK_K / Cfg::UMMA_K; ++j) {
+            const uint64_t da = A_MN ? umma_smem_desc_sw128(a_base + j * Cfg::UMMA_K * 128,
+                                                            BLOCK_K * 128, Cfg::MN_SBO, Cfg::MN_LAYOUT)
+                                     : umma_smem_desc_sw128(a_base + j * 32, 16, 1024);
+            const uint64_t db = B_MN ? umma_smem_desc_sw128(b_base + j * Cfg::UMMA_K * 128,
+                                                            BLOCK_K * 128, Cfg::MN_SBO, Cfg::MN_LAYOUT)
+                                     : umma_smem_desc_sw128(b_base + j * 32, 16, 1024);
+            tc_mma_pair<KIND>(acc, da, db, IDESC, (kb | j) != 0 ? 1u : 0u);
+          }
+          tc_commit_pair(&empty_bar[stage], 0b11);   // frees this ring slot in BOTH CTAs
+        }
+        tc_commit_pair(&tmem_full_bar[buf], 0b11);   // accumulator complete in both CTAs
+      }
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue: each CTA drains its own 128 rows; warp q owns TMEM lanes [32q, 32q+32) =====
+    const int q = warp - 4;
+    const bool wide_bf16 = OUT_BF16 && (args.flags & (kFlagOutBf16 | kFlagAccumulate)) == kFlagOutBf16 &&
+                           (args.ldd & 7) == 0 && (args.mask == nullptr || (args.ldmask & 7) == 0);
+    uint32_t t = 0;
+    for (int tile = pair; tile < total_tiles; tile += pairs, ++t) {
+      int mt, nt;
+      decode(tile, mt, nt);
+      const int n0 = nt * BLOCK_N;
+      const int row = mt * 2 * kBlockM + static_cast<int>(cta_rank) * kBlockM + q * 32 + lane;
+      const bool row_ok = row < args.M;
+      const uint32_t buf = t & 1;
+      mbar_wait(&tmem_full_bar[buf], (t >> 1) & 1);
+      tc_fence_after();
+      const uint32_t acc = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * ACC_COLS;
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(acc + c * 32, v);
+        tmem_ld_wait();
+        if (c == BLOCK_N / 32 - 1) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(&tmem_empty_bar[buf], 0);   // the leader's barrier counts 8 warps
+        }
+        const int col0 = n0 + c * 32;
+        if (!row_ok) continue;
+        if (wide_bf16 && col0 + 32 <= args.N) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            float f[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) f[k] = __uint_as_float(v[g * 8 + k]);
+            epilogue_store8_bf16(args, row, col0 + g * 8, f);
+          }
+        } else {
+#pragma unroll
+          for (int g = 0; g < 8; ++g) {
+            const int col = col0 + g * 4;
+            if (col < args.N)
+              epilogue_store4<OUT_BF16>(args, row, col, __uint_as_float(v[g * 4 + 0]), __uint_as_float(v[g * 4 + 1]),
+                                        __uint_as_float(v[g * 4 + 2]), __uint_as_float(v[g * 4 + 3]));
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();          // the leader's MMAs read the peer's shared memory until the last commit
+  if (warp == 2) tmem_dealloc_pair(tmem_base, tmem_cols);
+}
+
 // Debug hook: attach a timeline buffer (8 x int64 per CTA) to a plan, or detach with NULL.
 // ---------------------------------------------------------------------------------------
 // Host side
@@ -646,10 +842,10 @@ static int pick_block_n(const b2d_gemm_desc& d) {
   // Prefer the widest tile that still yields at least one full wave of CTAs (never wider than N).
   const int kb = ceil_div(d.K, d.dtype == B2D_F32 ? 32 : 64);
   const bool shallow = coresident_enabled() && kb <= kShallowKBlocks;
-  if (d.N > 128 && mt * ceil_div(d.N, 256) >= 148 && !shallow) return 256;
-  if (mt * ceil_div(d.N, 128) >= 120) return 128;
+  if (d.N > 128 && mt * ceil_div(d.N, 256) >= sm_count() && !shallow) return 256;
+  if (mt * ceil_div(d.N, 128) >= sm_count() * 13 / 16) return 128;
   // Few tiles: narrower tiles double the CTA count and halve each CTA's epilogue.
-  if (mt * ceil_div(d.N, 128) < 74) return 64;
+  if (mt * ceil_div(d.N, 128) < sm_count() / 2) return 64;
   return d.N % 128 == 0 || d.N > 512 ? 128 : 64;
 }
 
@@ -659,7 +855,7 @@ static int persistent_ctas(const b2d_gemm_geometry& g) {
   const int total = g.m_tiles * g.n_tiles * g.splits;
   const int acc_cols = g.block_n < 32 ? 32 : g.block_n;
   const bool two = g.smem_bytes + 1024 <= (227 * 1024) / 2 && 2 * (2 * acc_cols) <= 512;
-  return min(total, 148 * (two ? 2 : 1));
+  return min(total, sm_count() * (two ? 2 : 1));
 }
 
 static int resolve(const b2d_gemm_desc& d, b2d_gemm_geometry* g) {
@@ -673,6 +869,7 @@ static int resolve(const b2d_gemm_desc& d, b2d_gemm_geometry* g) {
   B2D_REQUIRE(d.N % 4 == 0 && d.ldd % 4 == 0, "gemm: N and ldd must be multiples of 4");
   B2D_REQUIRE(!(d.accumulate && d.out_dtype != B2D_F32), "gemm: accumulate needs fp32 output");
   B2D_REQUIRE(d.mask == nullptr || d.ldmask % 4 == 0, "gemm: ldmask must be a multiple of 4");
+  g->pair = 0;
   g->block_n = pick_block_n(d);
   g->m_tiles = ceil_div(d.M, kBlockM);
   g->n_tiles = ceil_div(d.N, g->block_n);
@@ -689,7 +886,8 @@ static int resolve(const b2d_gemm_desc& d, b2d_gemm_geometry* g) {
       const int v = e != nullptr ? atoi(e) : 2;
       return v >= 1 ? v : 2;
     }();
-    if (tiles < 74 && g->k_blocks >= 8) splits = min(max(1, g->k_blocks / min_kb), max(1, 148 / tiles));
+    if (tiles < sm_count() / 2 && g->k_blocks >= 8)
+      splits = min(max(1, g->k_blocks / min_kb), max(1, sm_count() / tiles));
   }
   splits = max(1, min(splits, g->k_blocks));
   const int per = ceil_div(g->k_blocks, splits);
@@ -700,7 +898,7 @@ static int resolve(const b2d_gemm_desc& d, b2d_gemm_geometry* g) {
   const int per_cta = ceil_div(g->k_blocks, g->splits);
   g->stages = max(2, min(min(kMaxStages, kSmemBudget / stage_bytes), per_cta));
   const int ctas = g->m_tiles * g->n_tiles * g->splits;
-  if (coresident_enabled() && ctas > 148 && g->k_blocks <= kShallowKBlocks && g->block_n <= 128) {
+  if (coresident_enabled() && ctas > sm_count() && g->k_blocks <= kShallowKBlocks && g->block_n <= 128) {
     const int together = 2;   // registers (<= 128 per thread) allow two CTAs per SM
     const int budget = (227 * 1024) / together - 1024 /*per-CTA reserve*/ - 1024 - 256;
     g->stages = max(2, min(g->stages, budget / stage_bytes));
@@ -708,6 +906,39 @@ static int resolve(const b2d_gemm_desc& d, b2d_gemm_geometry* g) {
   g->smem_bytes = g->stages * stage_bytes + 1024 + 256;
   g->ctas = persistent_ctas(*g);
   return B2D_OK;
+}
+
+// CTA-pair kernel (gemm_tc_pair_kernel): long-K plain GEMMs with at least one full wave of 256-row tiles.
+// Picks the tile width (256 or 128 columns) that wastes the least of the last wave.  B2D_GEMM_PAIR=0 disables.
+static void pick_pair(const b2d_gemm_desc& d, b2d_gemm_geometry* g) {
+  static const bool on = [] {
+    const char* e = getenv("B2D_GEMM_PAIR");
+    return e == nullptr || e[0] != '0';
+  }();
+  g->pair = 0;
+  if (!on || g->splits != 1 || g->k_blocks < 16 || d.M < 256 || d.N < 128) return;
+  const int pairs = sm_count() / 2;
+  const int mt2 = ceil_div(d.M, 2 * kBlockM);
+  int best_bn = 0;
+  double best_eff = 0.0;
+  // Only 256-column tiles: with N = 128 per instruction each SM's tensor core re-reads its A rows twice as often
+  // and falls far below peak (measured 808 vs 1083 TFLOP/s at 4096^3 bf16 against the single-CTA kernel).
+  for (int bn : {256}) {
+    if (bn > d.N) continue;
+    const int tiles = mt2 * ceil_div(d.N, bn);
+    if (tiles < pairs) continue;
+    const double eff = static_cast<double>(tiles) / (static_cast<double>(ceil_div(tiles, pairs)) * pairs);
+    if (eff >= 0.8 && eff > best_eff) best_eff = eff, best_bn = bn;
+  }
+  if (best_bn == 0) return;
+  g->pair = 1;
+  g->block_n = best_bn;
+  g->m_tiles = mt2;
+  g->n_tiles = ceil_div(d.N, best_bn);
+  const int stage_bytes = kABytes + (best_bn / 2) * 128;
+  g->stages = max(2, min(min(kMaxStages, kSmemBudget / stage_bytes), g->k_blocks));
+  g->smem_bytes = g->stages * stage_bytes + 1024 + 256;
+  g->ctas = 2 * min(g->m_tiles * g->n_tiles, pairs);
 }
 
 }  // namespace b2d
@@ -727,8 +958,32 @@ struct b2d_gemm_plan {
 static void finish_plan(b2d_gemm_plan* p) {
   GemmArgs& a = p->args;
   a.m_tiles = p->geo.m_tiles, a.n_tiles = p->geo.n_tiles;
-  p->geo.ctas = persistent_ctas(p->geo);      // the convolution plans changed m_tiles after resolve()
+  if (!p->geo.pair) p->geo.ctas = persistent_ctas(p->geo);      // the convolution plans changed m_tiles after resolve()
   p->grid = p->geo.ctas;
+}
+
+template <MmaKind KIND, bool A_MN, bool B_MN, bool OUT_BF16>
+static void select_pair_n(int block_n, void (**k)(const GemmArgs), int* smem) {
+  if (block_n == 256) {
+    *k = gemm_tc_pair_kernel<KIND, A_MN, B_MN, 256, OUT_BF16>;
+    *smem = GemmCfg<KIND, A_MN, B_MN, 128>::SMEM_BYTES;
+  } else {
+    *k = gemm_tc_pair_kernel<KIND, A_MN, B_MN, 128, OUT_BF16>;
+    *smem = GemmCfg<KIND, A_MN, B_MN, 64>::SMEM_BYTES;
+  }
+}
+template <MmaKind KIND>
+static void select_pair(bool a_mn, bool b_mn, int block_n, int out_dtype, void (**k)(const GemmArgs), int* smem) {
+  if (out_dtype == B2D_BF16) {
+    if (a_mn && b_mn) return select_pair_n<KIND, true, true, true>(block_n, k, smem);
+    if (a_mn) return select_pair_n<KIND, true, false, true>(block_n, k, smem);
+    if (b_mn) return select_pair_n<KIND, false, true, true>(block_n, k, smem);
+    return select_pair_n<KIND, false, false, true>(block_n, k, smem);
+  }
+  if (a_mn && b_mn) return select_pair_n<KIND, true, true, false>(block_n, k, smem);
+  if (a_mn) return select_pair_n<KIND, true, false, false>(block_n, k, smem);
+  if (b_mn) return select_pair_n<KIND, false, true, false>(block_n, k, smem);
+  return select_pair_n<KIND, false, false, false>(block_n, k, smem);
 }
 
 template <MmaKind KIND, bool A_MN, bool B_MN, bool OUT_BF16>
@@ -771,7 +1026,9 @@ static void select_major(bool a_mn, bool b_mn, int block_n, int out_dtype, void 
 
 extern "C" int b2d_gemm_query(const b2d_gemm_desc* desc, b2d_gemm_geometry* out) {
   B2D_REQUIRE(desc != nullptr && out != nullptr, "gemm_query: null argument");
-  return resolve(*desc, out);
+  const int rc = resolve(*desc, out);
+  if (rc == B2D_OK) pick_pair(*desc, out);
+  return rc;
 }
 
 extern "C" size_t b2d_gemm_workspace_bytes(const b2d_gemm_desc* desc) {
@@ -794,6 +1051,8 @@ extern "C" int b2d_gemm_plan_create(const b2d_gemm_desc* desc, b2d_gemm_plan** o
   b2d_gemm_geometry g;
   int rc = resolve(d, &g);
   if (rc != B2D_OK) return rc;
+  pick_pair(d, &g);
+  const int b_box_n = g.pair ? g.block_n / 2 : g.block_n;      // a CTA of a pair loads half of the B tile
   B2D_REQUIRE(d.A && d.B && d.D, "gemm: null operand pointer");
   B2D_REQUIRE((reinterpret_cast<uintptr_t>(d.A) % 16) == 0 && (reinterpret_cast<uintptr_t>(d.B) % 16) == 0 &&
                   (reinterpret_cast<uintptr_t>(d.D) % 16) == 0,
@@ -814,7 +1073,7 @@ extern "C" int b2d_gemm_plan_create(const b2d_gemm_desc* desc, b2d_gemm_plan** o
     rc = encode_tmap_2d(&p->args.tmA, d.dtype, d.A, d.M, d.K, d.lda * es, atom, block_k, true);
   if (rc == B2D_OK) {
     if (!d.b_mn_major)
-      rc = encode_tmap_2d(&p->args.tmB, d.dtype, d.B, d.K, d.N, d.ldb * es, block_k, g.block_n, false);
+      rc = encode_tmap_2d(&p->args.tmB, d.dtype, d.B, d.K, d.N, d.ldb * es, block_k, b_box_n, false);
     else
       rc = encode_tmap_2d(&p->args.tmB, d.dtype, d.B, d.N, d.K, d.ldb * es, atom, block_k, true);
   }
@@ -833,10 +1092,16 @@ extern "C" int b2d_gemm_plan_create(const b2d_gemm_desc* desc, b2d_gemm_plan** o
   a.stages = g.stages;
   p->launch_smem = g.smem_bytes;
   p->geo = g;
-  if (d.dtype == B2D_F32)
+  if (g.pair) {
+    if (d.dtype == B2D_F32)
+      select_pair<MmaKind::TF32>(d.a_mn_major, d.b_mn_major, g.block_n, d.out_dtype, &p->kernel, &p->smem_bytes);
+    else
+      select_pair<MmaKind::F16>(d.a_mn_major, d.b_mn_major, g.block_n, d.out_dtype, &p->kernel, &p->smem_bytes);
+  } else if (d.dtype == B2D_F32) {
     select_major<MmaKind::TF32>(d.a_mn_major, d.b_mn_major, g.block_n, d.out_dtype, &p->kernel, &p->smem_bytes);
-  else
+  } else {
     select_major<MmaKind::F16>(d.a_mn_major, d.b_mn_major, g.block_n, d.out_dtype, &p->kernel, &p->smem_bytes);
+  }
   cudaError_t e = cudaFuncSetAttribute(reinterpret_cast<const void*>(p->kernel),
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem_bytes);
   if (e != cudaSuccess) {
@@ -1344,7 +1609,7 @@ extern "C" int b2d_conv_wgrad_plan_create(const b2d_conv_desc* dp, b2d_conv_wgra
   }
   p->smem_bytes = a.stages * stage_bytes + 1024 + 256;
   const int fixed = d.KH * d.KW * a.m_tiles * a.n_tiles;
-  int chunks = max(1, min(a.tiles_total, (148 * 2 + fixed - 1) / fixed));
+  int chunks = max(1, min(a.tiles_total, (sm_count() * 2 + fixed - 1) / fixed));
   a.tiles_per_cta = ceil_div(a.tiles_total, chunks);
   chunks = ceil_div(a.tiles_total, a.tiles_per_cta);
   p->grid = dim3(fixed, chunks);

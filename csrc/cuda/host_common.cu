@@ -47,6 +47,24 @@ void set_uniform_carveout(const void* kernel) {
   }
 }
 
+int sm_count() {
+  static std::atomic<int> cached[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+    (void)cudaGetLastError();
+    return 148;
+  }
+  int n = cached[dev].load(std::memory_order_relaxed);
+  if (n == 0) {
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) {
+      (void)cudaGetLastError();
+      n = 148;
+    }
+    cached[dev].store(n, std::memory_order_relaxed);
+  }
+  return n;
+}
+
 void* driver_fn(const char* name) {
   void* fn = nullptr;
   cudaDriverEntryPointQueryResult q;

@@ -51,6 +51,11 @@ void* driver_fn(const char* name);
 
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
+// Streaming multiprocessors of the current device (cudaDevAttrMultiProcessorCount, cached per device).
+// Grids and tile schedules are sized from this at run time; on a GPU-less build host it reports the
+// B200's 148 so that geometry queries still answer.
+int sm_count();
+
 // Programmatic dependent launch: every kernel of this library is launched with the
 // programmatic-stream-serialization attribute and begins with griddepcontrol.wait /
 // griddepcontrol.launch_dependents (pdl_wait / pdl_trigger in ptx.cuh), so kernel N+1 is

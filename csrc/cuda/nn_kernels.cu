@@ -689,7 +689,8 @@ __global__ void cast_f32_bf16_kernel(const float* __restrict__ src, uint16_t* __
   }
 }
 
-static inline int grid_for(size_t n, int block = 256, int cap = 148 * 8) {
+static inline int grid_for(size_t n, int block = 256, int ctas_per_sm = 8) {
+  const int cap = sm_count() * ctas_per_sm;
   size_t g = (n + block - 1) / block;
   return (int)(g < 1 ? 1 : (g > (size_t)cap ? cap : g));
 }
@@ -708,7 +709,7 @@ extern "C" int b2d_conv_c1_pool_fwd(const float* x, const float* w, const float*
   const int OH = H - KS + 1, OW = W - KS + 1, PH = OH / 2, PW = OW / 2;
   B2D_REQUIRE(PH > 0 && PW > 0, "conv_c1_pool: input too small");
   // Two bands per image at small batch keeps >= 128 CTAs in flight for batch 64.
-  const int bands = N >= 296 ? 1 : (N >= 148 ? 2 : 4);
+  const int bands = N >= 2 * sm_count() ? 1 : (N >= sm_count() ? 2 : 4);
   const int band = ceil_div(PH, bands);
   const dim3 grid(N, ceil_div(PH, band));
   const size_t smem = (size_t)(2 * band + KS) * W * sizeof(float);
@@ -783,7 +784,7 @@ extern "C" int b2d_maxpool2_bwd(const float* dy, const uint8_t* code, const floa
   const int PH = H / 2, PW = W / 2;
   if (C % 4 == 0) {
     const size_t n4 = (size_t)N * H * W * (C / 4);
-    B2D_CUDA_CHECK(launch_pdl(maxpool2_bwd_v4_kernel, dim3(grid_for(n4, 256, 148 * 32)), dim3(256), 0,
+    B2D_CUDA_CHECK(launch_pdl(maxpool2_bwd_v4_kernel, dim3(grid_for(n4, 256, 32)), dim3(256), 0,
                               static_cast<cudaStream_t>(stream), reinterpret_cast<const float4*>(dy),
                               reinterpret_cast<const uchar4*>(code), reinterpret_cast<const float4*>(y_pooled),
                               reinterpret_cast<float4*>(dx), N, H, W, C / 4, PH, PW, act_relu));

@@ -673,7 +673,8 @@ __global__ void __launch_bounds__(256) cast_kernel(const TI* __restrict__ src, T
   if (t < n) store_scalar(dst + t, load_scalar(src + t));
 }
 
-static inline int grid_1d(size_t n, int block = 256, int cap = 148 * 16) {
+static inline int grid_1d(size_t n, int block = 256, int ctas_per_sm = 16) {
+  const int cap = sm_count() * ctas_per_sm;
   size_t g = (n + block - 1) / block;
   return (int)(g < 1 ? 1 : (g > (size_t)cap ? cap : g));
 }
@@ -685,7 +686,8 @@ struct ChanGrid {
 };
 // ctas: how many CTAs to aim for — streaming kernels want many (8 per SM), the reduction kernels few
 // and fat ones (2 per SM): every CTA ends in atomics on the same 2C floats.
-static inline ChanGrid chan_grid(int M, int C, int V, int ctas = 148 * 8) {
+static inline ChanGrid chan_grid(int M, int C, int V, int ctas = 0) {
+  if (ctas <= 0) ctas = sm_count() * 8;
   const int cvec = C / V;
   int lanes = 1;
   while (lanes < 32 && lanes < cvec) lanes <<= 1;
@@ -707,7 +709,7 @@ typedef __nv_bfloat16 bf16_t;
 #define B2D_DTYPE_OK(dt) B2D_REQUIRE((dt) == B2D_F32 || (dt) == B2D_BF16, "unknown dtype %d", (int)(dt))
 
 static inline int vec_of(int dtype) { return dtype == B2D_F32 ? 4 : 8; }
-constexpr int kReduceCtas = 148 * 2;
+static inline int reduce_ctas() { return sm_count() * 2; }
 // Reduction kernels end in atomics on 2C floats: few fat CTAs when those floats are a handful of L2 lines
 // (C <= 128), more CTAs (better latency hiding: the kernels run at ~25 % occupancy) when they spread out.
 // B2D_BN_REDUCE_CTAS_PER_SM overrides the per-SM count for wide tensors (default 2 = same as narrow).
@@ -717,7 +719,7 @@ static int reduce_ctas(int C) {
     const int v = e != nullptr ? atoi(e) : 2;
     return v >= 1 && v <= 8 ? v : 2;
   }();
-  return C <= 128 ? kReduceCtas : 148 * wide;
+  return C <= 128 ? reduce_ctas() : sm_count() * wide;
 }
 
 static int fill_bn_args(const b2d_bn_desc& d, BnArgs* a) {

@@ -38,7 +38,7 @@ class GemmScatter(C.Structure):
 
 class GemmGeometry(C.Structure):
     _fields_ = [(n, C.c_int) for n in
-                ("block_n", "m_tiles", "n_tiles", "splits", "k_blocks", "stages", "smem_bytes", "ctas")]
+                ("block_n", "m_tiles", "n_tiles", "splits", "k_blocks", "stages", "smem_bytes", "ctas", "pair")]
 
 
 def _declare(lib) -> None:

@@ -79,6 +79,7 @@ typedef struct b2d_gemm_plan b2d_gemm_plan;
 typedef struct b2d_gemm_geometry {
   int block_n, m_tiles, n_tiles, splits, k_blocks, stages, smem_bytes;
   int ctas; /* persistent CTAs launched: min(m_tiles * n_tiles * splits, SMs x CTAs that fit an SM together) */
+  int pair; /* 1: CTA-pair kernel (tcgen05 cta_group::2): 256 x block_n tiles, m_tiles counts 256-row tiles  */
 } b2d_gemm_geometry;
 
 int b2d_gemm_query(const b2d_gemm_desc* desc, b2d_gemm_geometry* out);

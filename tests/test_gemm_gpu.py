@@ -35,6 +35,12 @@ CASES = [
     (260, 36, 72, True, True),
     (8192, 2048, 256, False, True),   # 1024 tiles: persistent CTAs walk several tiles, double-buffered TMEM
     (4096, 640, 8192, False, False),  # 160 tiles, long K loop (deep ring, one CTA per SM)
+    # CTA-pair kernel (tcgen05 cta_group::2, 256-row tiles): every operand layout, ragged M / N tails
+    (4096, 2048, 2048, False, False),
+    (2304 + 40, 2176 + 24, 2048, False, True),
+    (2304 + 40, 2176 + 24, 2048, True, False),
+    (2560, 2304, 2048, True, True),
+    (8192, 1152, 1024, False, False),  # 128-column pair tiles (less waste in the last wave)
 ]
 
 
@@ -56,6 +62,26 @@ def test_gemm_matches_fp32_reference(M, N, K, a_mn, b_mn, dtype):
     tol = 2e-3 if dtype == torch.float32 else 1e-2   # tf32 inputs truncate to 10 mantissa bits
     err = (d - ref).abs().max().item() / max(ref.abs().max().item(), 1e-6)
     assert err < tol, f"rel err {err} geometry={[getattr(plan.geometry, f) for f, _ in plan.geometry._fields_]}"
+
+
+def test_pair_kernel_is_selected_for_long_k_and_epilogue_variants_match():
+    """The CTA-pair kernel with bias + ReLU + mask, bf16 output, and accumulation, against fp64."""
+    from distributed_b200.ops.gemm import GemmPlan
+    g = torch.Generator(device="cuda").manual_seed(11)
+    M, N, K = 4096, 2304, 2048
+    a, b = _mk((M, K), torch.bfloat16, g), _mk((N, K), torch.bfloat16, g)
+    bias, mask = _mk((N,), torch.float32, g), _mk((M, N), torch.bfloat16, g)
+    d = torch.empty((M, N), device="cuda", dtype=torch.bfloat16)
+    plan = GemmPlan(a, b, d, bias=bias, relu=True, mask=mask)
+    assert plan.geometry.pair == 1 and plan.geometry.ctas % 2 == 0
+    plan.run()
+    ref = _ref(a, b, False, False, bias, True, mask)
+    assert (d.float() - ref).abs().max().item() < 0.02 * ref.abs().max().item()
+    acc = torch.ones((M, N), device="cuda")
+    a32, b32 = _mk((M, K), torch.float32, g), _mk((N, K), torch.float32, g)
+    GemmPlan(a32, b32, acc, accumulate=True).run()
+    ref = _ref(a32, b32, False, False, None, False, None) + 1
+    assert (acc - ref).abs().max().item() < 2e-3 * ref.abs().max().item()
 
 
 def test_gemm_epilogue_bias_relu_mask_and_bf16_out():

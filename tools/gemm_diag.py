@@ -44,16 +44,36 @@ if __name__ == "__main__":
             run(256, 256, 1024, a_mn, b_mn, dtype, splits=1)
     run(64, 64, 5408, False, True, torch.float32)
     run(4096, 4096, 4096, False, False, torch.bfloat16)
-    # quick throughput probe
-    for dtype, M in ((torch.bfloat16, 8192), (torch.float32, 4096)):
+    for dtype in (torch.float32, torch.bfloat16):          # CTA-pair kernel
+        for (a_mn, b_mn) in ((False, False), (False, True), (True, False), (True, True)):
+            run(2344, 2200, 2048, a_mn, b_mn, dtype)
+    # throughput: bf16 / tf32 square GEMMs vs torch.matmul (cuBLAS), L2 flushed between iterations
+    import subprocess
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def timed(fn, iters=10):
+        for _ in range(3):
+            fn()
+        e = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(iters)]
+        for e0, e1 in e:
+            flush.zero_()
+            e0.record(); fn(); e1.record()
+        torch.cuda.synchronize()
+        ts = sorted(a.elapsed_time(b) for a, b in e)
+        return ts[len(ts) // 2]
+
+    torch.backends.cuda.matmul.allow_tf32 = True
+    for dtype, M, out_dtype in ((torch.bfloat16, 8192, torch.bfloat16), (torch.bfloat16, 8192, torch.float32),
+                                (torch.bfloat16, 4096, torch.bfloat16), (torch.float32, 4096, torch.float32),
+                                (torch.float32, 8192, torch.float32)):
         a = torch.randn(M, M, device="cuda").to(dtype); b = torch.randn(M, M, device="cuda").to(dtype)
-        d = torch.empty(M, M, device="cuda")
+        d = torch.empty(M, M, device="cuda", dtype=out_dtype)
         p = GemmPlan(a, b, d)
-        for _ in range(3): p.run()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(10): p.run()
-        e1.record(); torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1) / 10
-        print(f"perf {str(dtype)[6:]} {M}^3: {ms:.3f} ms  {2*M**3/ms/1e9:.1f} TFLOP/s")
-        ref = torch.matmul(a, b.t()) if dtype == torch.bfloat16 else None
+        ms = timed(p.run)
+        ms_lib = timed(lambda: torch.matmul(a, b.t()))
+        clk = subprocess.run(["nvidia-smi", "--query-gpu=clocks.sm,clocks.max.sm,clocks_throttle_reasons.active",
+                              "--format=csv,noheader", "-i", "0"], capture_output=True, text=True).stdout.strip()
+        geo = {f: getattr(p.geometry, f) for f, _ in p.geometry._fields_}
+        print(f"perf {str(dtype)[6:]}->{str(out_dtype)[6:]} {M}^3: {ms:.3f} ms {2*M**3/ms/1e9:.1f} TFLOP/s | "
+              f"cuBLAS {ms_lib:.3f} ms {2*M**3/ms_lib/1e9:.1f} TFLOP/s | ratio {ms_lib/ms:.3f} | pair={geo['pair']} "
+              f"bn={geo['block_n']} stages={geo['stages']} ctas={geo['ctas']} | clocks {clk}")
