@@ -843,6 +843,25 @@ static int pick_block_n(const b2d_gemm_desc& d) {
   const int kb = ceil_div(d.K, d.dtype == B2D_F32 ? 32 : 64);
   const bool shallow = coresident_enabled() && kb <= kShallowKBlocks;
   if (d.N > 128 && mt * ceil_div(d.N, 256) >= sm_count() && !shallow) return 256;
+  if (!shallow && d.N > 64 && d.splits <= 0 && !d.accumulate) {
+    // Long K, too few tiles for a wave of wide ones: the main loop is bound by the bytes each CTA pulls into
+    // shared memory per k-block (16 KB of A + 128 B per column of B), so prefer the tile width — with the
+    // split-K factor that fills the SMs — that minimises waves x k-blocks per CTA x bytes per k-block.
+    // (Dense-1024 forward at batch 1024: 128 x 64 tiles, 45.8 us -> 256-wide tiles, split-K 4.)
+    const int sms = sm_count();
+    int best_bn = 0;
+    long long best_cost = 0;
+    for (int bn : {256, 128, 64}) {
+      if (bn > 64 && bn / 2 >= d.N) continue;
+      const int tiles = mt * ceil_div(d.N, bn);
+      const int splits = (tiles < sms / 2 && kb >= 8) ? max(1, min(kb / 2, sms / tiles)) : 1;
+      const int per = ceil_div(kb, splits);
+      const long long waves = ceil_div(tiles * ceil_div(kb, per), sms);
+      const long long cost = waves * (per + (splits > 1 ? 6 : 2)) * (16 + bn / 8);   // + prologue / epilogue / meeting
+      if (best_bn == 0 || cost < best_cost) best_bn = bn, best_cost = cost;
+    }
+    return best_bn;
+  }
   if (mt * ceil_div(d.N, 128) >= sm_count() * 13 / 16) return 128;
   // Few tiles: narrower tiles double the CTA count and halve each CTA's epilogue.
   if (mt * ceil_div(d.N, 128) < sm_count() / 2) return 64;

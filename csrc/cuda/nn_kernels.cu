@@ -32,7 +32,9 @@ __device__ __forceinline__ float warp_max(float v) {
 //   in shared memory and is read by broadcast; the 26x26xCo conv map never reaches HBM.
 //   code[n,ph,pw,c] = argmax position (0..3 = dy*2+dx) or 4 when ReLU clamped the maximum.
 // =======================================================================================
-template <int KS>
+//   CG = channel groups of 32 handled per pixel: the (KS+1)^2 input window is fetched once (broadcast
+//   shared-memory loads are the bottleneck of this kernel) and reused for CG x 32 output channels.
+template <int KS, int CG>
 __global__ void __launch_bounds__(256) conv_c1_pool_fwd_kernel(
     const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
     float* __restrict__ y, uint8_t* __restrict__ code, int H, int W, int Co, int PH, int PW,
@@ -50,13 +52,15 @@ __global__ void __launch_bounds__(256) conv_c1_pool_fwd_kernel(
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
   const int npix = (ph1 - ph0) * PW;
-  for (int cg = 0; cg < Co; cg += 32) {
-    const int c = cg + lane;
-    const bool c_ok = c < Co;
-    float wr[KS * KS];
+  for (int cg0 = 0; cg0 < Co; cg0 += 32 * CG) {
+    float wr[CG][KS * KS], bv[CG];
 #pragma unroll
-    for (int t = 0; t < KS * KS; ++t) wr[t] = c_ok ? w[t * Co + c] : 0.f;
-    const float bv = c_ok ? bias[c] : 0.f;
+    for (int g = 0; g < CG; ++g) {
+      const int c = cg0 + 32 * g + lane;
+#pragma unroll
+      for (int t = 0; t < KS * KS; ++t) wr[g][t] = c < Co ? w[t * Co + c] : 0.f;
+      bv[g] = c < Co ? bias[c] : 0.f;
+    }
     for (int p = warp; p < npix; p += nwarp) {
       const int ph = ph0 + p / PW, pw = p % PW;
       const float* base = xs + (2 * ph - r0) * W + 2 * pw;
@@ -65,23 +69,27 @@ __global__ void __launch_bounds__(256) conv_c1_pool_fwd_kernel(
       for (int i = 0; i < KS + 1; ++i)
 #pragma unroll
         for (int j = 0; j < KS + 1; ++j) win[i * (KS + 1) + j] = base[i * W + j];
-      float best = -INFINITY;
-      int arg = 0;
 #pragma unroll
-      for (int dy = 0; dy < 2; ++dy)
+      for (int g = 0; g < CG; ++g) {
+        const int c = cg0 + 32 * g + lane;
+        float best = -INFINITY;
+        int arg = 0;
 #pragma unroll
-        for (int dx = 0; dx < 2; ++dx) {
-          float acc = bv;
+        for (int dy = 0; dy < 2; ++dy)
 #pragma unroll
-          for (int i = 0; i < KS; ++i)
+          for (int dx = 0; dx < 2; ++dx) {
+            float acc = bv[g];
 #pragma unroll
-            for (int j = 0; j < KS; ++j) acc = fmaf(win[(dy + i) * (KS + 1) + dx + j], wr[i * KS + j], acc);
-          if (acc > best) best = acc, arg = dy * 2 + dx;
+            for (int i = 0; i < KS; ++i)
+#pragma unroll
+              for (int j = 0; j < KS; ++j) acc = fmaf(win[(dy + i) * (KS + 1) + dx + j], wr[g][i * KS + j], acc);
+            if (acc > best) best = acc, arg = dy * 2 + dx;
+          }
+        if (c < Co) {
+          const size_t o = (((size_t)n * PH + ph) * PW + pw) * Co + c;
+          y[o] = fmaxf(best, 0.f);
+          code[o] = best > 0.f ? (uint8_t)arg : (uint8_t)4;
         }
-      if (c_ok) {
-        const size_t o = (((size_t)n * PH + ph) * PW + pw) * Co + c;
-        y[o] = fmaxf(best, 0.f);
-        code[o] = best > 0.f ? (uint8_t)arg : (uint8_t)4;
       }
     }
   }
@@ -309,6 +317,180 @@ __global__ void __launch_bounds__(256) dense_xent_head_kernel(
     atomicAdd(&metrics[0], loss_sum);
     atomicAdd(&metrics[1], correct_sum);
     atomicAdd(&metrics[2], (float)(row1 - row0));
+  }
+}
+
+
+// The same head for LARGE batches (scaled configurations: batch 1024 per GPU, K = 1024): throughput- instead
+// of instruction-fetch-bound.  One warp per row, 8 rows per pass.  Differences to the kernel above: the class
+// loop is innermost and fully unrolled (kC = 16 accumulators in registers: 16 independent FMA chains per k),
+// W sits in shared memory with a 16-byte aligned row pitch and is read as float4 (4 shared loads per 16 FMAs
+// instead of 1 per FMA), and in the dW phase each thread owns whole rows of dW (all kC classes of its k's), so
+// one h value and four broadcast float4 of dz feed 16 FMAs; the partial sums stay in registers across passes
+// (one global atomic per output per CTA).
+template <int kC>
+__global__ void __launch_bounds__(256) dense_xent_head_wide_kernel(
+    const float* __restrict__ h, const float* __restrict__ w, const float* __restrict__ bias,
+    const int* __restrict__ labels, float* __restrict__ logits_out, float* __restrict__ dh,
+    float* __restrict__ dw, float* __restrict__ db, float* __restrict__ dh_colsum,
+    float* __restrict__ metrics, int B, int K, int C, float grad_scale, int relu_mask, int passes) {
+  static_assert(kC == 16, "the float4 paths assume 16 classes per row");
+  pdl_wait();
+  pdl_trigger();
+  constexpr int kRows = 8, kPitch = kC + 4, kOwnK = 4;       // K <= 256 * kOwnK
+  extern __shared__ __align__(16) float sm[];
+  float* ws = sm;                          // [K][kPitch]
+  float* hs = ws + (size_t)K * kPitch;     // [8][K]
+  float* dhs = hs + kRows * K;             // [8][K]
+  float* dzs = dhs + kRows * K;            // [8][kC]
+  float* rowm = dzs + kRows * kC;          // [8][2]
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+#pragma unroll 8
+  for (int i = tid; i < K * kC; i += 256) {
+    const int k = i >> 4, c = i & 15;
+    ws[k * kPitch + c] = c < C ? __ldg(w + (size_t)k * C + c) : 0.f;
+  }
+  float accw[kOwnK][kC];                   // dW rows k = tid + 256 j
+  float acck[kOwnK];                       // dh column sums of the same k's
+#pragma unroll
+  for (int j = 0; j < kOwnK; ++j) {
+    acck[j] = 0.f;
+#pragma unroll
+    for (int c = 0; c < kC; ++c) accw[j][c] = 0.f;
+  }
+  float acc_b = 0.f, loss_sum = 0.f, correct_sum = 0.f;
+  __syncthreads();
+  const int row0 = blockIdx.x * (kRows * passes);
+#pragma unroll 1
+  for (int pass = 0; pass < passes; ++pass) {
+    const int r = row0 + pass * kRows + warp;
+    float* hrow = hs + warp * K;
+    float* dhrow = dhs + warp * K;
+    float* dzrow = dzs + warp * kC;
+    if (r < B) {
+      const float* hr = h + (size_t)r * K;
+      float p[kC];
+#pragma unroll
+      for (int c = 0; c < kC; ++c) p[c] = 0.f;
+      // the whole row first (K <= 1024: 32 loads in flight per lane), then the arithmetic: one memory latency
+      // per row instead of one per k
+      float hreg[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) hreg[j] = lane + 32 * j < K ? __ldg(hr + lane + 32 * j) : 0.f;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int k = lane + 32 * j;
+        if (k >= K) continue;
+        const float hv = hreg[j];
+        hrow[k] = hv;
+        const float4* wr = reinterpret_cast<const float4*>(ws + k * kPitch);
+#pragma unroll
+        for (int q = 0; q < kC / 4; ++q) {
+          const float4 w4 = wr[q];
+          p[4 * q + 0] = fmaf(hv, w4.x, p[4 * q + 0]), p[4 * q + 1] = fmaf(hv, w4.y, p[4 * q + 1]);
+          p[4 * q + 2] = fmaf(hv, w4.z, p[4 * q + 2]), p[4 * q + 3] = fmaf(hv, w4.w, p[4 * q + 3]);
+        }
+      }
+      float zc = -INFINITY;
+#pragma unroll
+      for (int c = 0; c < kC; ++c) {
+        const float t = warp_sum(p[c]);
+        if (lane == c && c < C) zc = t + bias[c];
+      }
+      if (logits_out != nullptr && lane < C) logits_out[(size_t)r * C + lane] = zc;
+      float mx = zc;
+      int arg = lane < C ? lane : 0x7fffffff;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+        const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+        if (om > mx || (om == mx && oa < arg)) mx = om, arg = oa;
+      }
+      const float e = lane < C ? __expf(zc - mx) : 0.f;
+      const float se = warp_sum(e);
+      const int yl = labels[r];
+      const float zy = __shfl_sync(0xffffffffu, zc, yl);
+      const float dz = lane < C ? (e / se - (lane == yl ? 1.f : 0.f)) * grad_scale : 0.f;
+      if (lane < kC) dzrow[lane] = dz;
+      if (lane == 0) rowm[warp * 2] = mx + __logf(se) - zy, rowm[warp * 2 + 1] = arg == yl ? 1.f : 0.f;
+      float dzr[kC];
+#pragma unroll
+      for (int c = 0; c < kC; ++c) dzr[c] = __shfl_sync(0xffffffffu, dz, c);
+#pragma unroll 2
+      for (int k = lane; k < K; k += 32) {
+        const float4* wr = reinterpret_cast<const float4*>(ws + k * kPitch);
+        float g = 0.f;
+#pragma unroll
+        for (int q = 0; q < kC / 4; ++q) {
+          const float4 w4 = wr[q];
+          g = fmaf(dzr[4 * q + 0], w4.x, g), g = fmaf(dzr[4 * q + 1], w4.y, g);
+          g = fmaf(dzr[4 * q + 2], w4.z, g), g = fmaf(dzr[4 * q + 3], w4.w, g);
+        }
+        if (relu_mask && !(hrow[k] > 0.f)) g = 0.f;
+        dhrow[k] = g;
+        if (dh != nullptr) dh[(size_t)r * K + k] = g;
+      }
+    } else {
+      for (int k = lane; k < K; k += 32) hrow[k] = 0.f, dhrow[k] = 0.f;
+      if (lane < kC) dzrow[lane] = 0.f;
+      if (lane == 0) rowm[warp * 2] = 0.f, rowm[warp * 2 + 1] = 0.f;
+    }
+    __syncthreads();
+    // ---- dW / column sums: thread owns rows k = tid + 256 j of dW ----
+#pragma unroll
+    for (int rr = 0; rr < kRows; ++rr) {
+      float dzv[kC];
+#pragma unroll
+      for (int q = 0; q < kC / 4; ++q) {
+        const float4 t4 = reinterpret_cast<const float4*>(dzs + rr * kC)[q];     // broadcast
+        dzv[4 * q] = t4.x, dzv[4 * q + 1] = t4.y, dzv[4 * q + 2] = t4.z, dzv[4 * q + 3] = t4.w;
+      }
+#pragma unroll
+      for (int j = 0; j < kOwnK; ++j) {
+        const int k = tid + 256 * j;
+        if (k < K) {
+          const float hv = hs[rr * K + k];
+#pragma unroll
+          for (int c = 0; c < kC; ++c) accw[j][c] = fmaf(hv, dzv[c], accw[j][c]);
+          acck[j] += dhs[rr * K + k];
+        }
+      }
+    }
+    if (tid < C) {
+#pragma unroll
+      for (int rr = 0; rr < kRows; ++rr) acc_b += dzs[rr * kC + tid];
+    }
+    if (tid == 0) {
+#pragma unroll
+      for (int rr = 0; rr < kRows; ++rr) loss_sum += rowm[rr * 2], correct_sum += rowm[rr * 2 + 1];
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int j = 0; j < kOwnK; ++j) {
+    const int k = tid + 256 * j;
+    if (k < K) {
+      float* dst = dw + (size_t)k * C;
+      if ((C & 1) == 0) {          // rows of dW start 8-byte aligned: half as many reductions, as float2
+#pragma unroll
+        for (int c = 0; c < kC; c += 2)
+          if (c < C)
+            asm volatile("red.relaxed.gpu.global.add.v2.f32 [%0], {%1, %2};" ::"l"(dst + c), "f"(accw[j][c]),
+                         "f"(accw[j][c + 1])
+                         : "memory");
+      } else {
+#pragma unroll
+        for (int c = 0; c < kC; ++c)
+          if (c < C) atomicAdd(dst + c, accw[j][c]);
+      }
+      if (dh_colsum != nullptr) atomicAdd(&dh_colsum[k], acck[j]);
+    }
+  }
+  if (tid < C) atomicAdd(&db[tid], acc_b);
+  if (tid == 0 && metrics != nullptr) {
+    atomicAdd(&metrics[0], loss_sum);
+    atomicAdd(&metrics[1], correct_sum);
+    atomicAdd(&metrics[2], (float)(min(B, row0 + kRows * passes) - row0));
   }
 }
 
@@ -714,10 +896,16 @@ extern "C" int b2d_conv_c1_pool_fwd(const float* x, const float* w, const float*
   const dim3 grid(N, ceil_div(PH, band));
   const size_t smem = (size_t)(2 * band + KS) * W * sizeof(float);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (KS == 3)
-    B2D_CUDA_CHECK(launch_pdl(conv_c1_pool_fwd_kernel<3>, dim3(grid), dim3(256), smem, st, x, w, bias, y, code, H, W, Co, PH, PW, band));
+  // README model (32 filters): one channel group, the small-footprint instantiation; wider layers reuse each
+  // input window for two groups of 32 channels
+  if (KS == 3 && Co <= 32)
+    B2D_CUDA_CHECK(launch_pdl(conv_c1_pool_fwd_kernel<3, 1>, dim3(grid), dim3(256), smem, st, x, w, bias, y, code, H, W, Co, PH, PW, band));
+  else if (KS == 3)
+    B2D_CUDA_CHECK(launch_pdl(conv_c1_pool_fwd_kernel<3, 2>, dim3(grid), dim3(256), smem, st, x, w, bias, y, code, H, W, Co, PH, PW, band));
+  else if (Co <= 32)
+    B2D_CUDA_CHECK(launch_pdl(conv_c1_pool_fwd_kernel<5, 1>, dim3(grid), dim3(256), smem, st, x, w, bias, y, code, H, W, Co, PH, PW, band));
   else
-    B2D_CUDA_CHECK(launch_pdl(conv_c1_pool_fwd_kernel<5>, dim3(grid), dim3(256), smem, st, x, w, bias, y, code, H, W, Co, PH, PW, band));
+    B2D_CUDA_CHECK(launch_pdl(conv_c1_pool_fwd_kernel<5, 2>, dim3(grid), dim3(256), smem, st, x, w, bias, y, code, H, W, Co, PH, PW, band));
   B2D_CUDA_CHECK(cudaGetLastError());
   return B2D_OK;
 }
@@ -745,6 +933,23 @@ extern "C" int b2d_dense_xent_head(const float* h, const float* w, const float* 
                                    float* db, float* dh_colsum, float* metrics, int B, int K, int C,
                                    float grad_scale, int relu_mask, void* stream) {
   B2D_REQUIRE(C >= 1 && C <= kHeadMaxC, "dense_xent_head: C must be in [1, %d]", kHeadMaxC);
+  // Large batches: the throughput-oriented variant (16 classes at most, K * 16 / 256 outputs per thread <= 64)
+  if (B >= 256 && C <= 16 && K <= 1024 && K % 32 == 0) {
+    const size_t smem_w = ((size_t)K * 20 + 16 * K + 8 * 16 + 16) * sizeof(float);
+    static bool attr_w = false;
+    if (!attr_w) {
+      B2D_CUDA_CHECK(cudaFuncSetAttribute(dense_xent_head_wide_kernel<16>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      attr_w = true;
+    }
+    // 8 rows per CTA until that is more than two waves of CTAs; then 16 (half the global atomics)
+    const int passes = B > 8 * 2 * sm_count() ? 2 : 1;
+    B2D_CUDA_CHECK(launch_pdl(dense_xent_head_wide_kernel<16>, dim3(ceil_div(B, 8 * passes)), dim3(256), smem_w,
+                              static_cast<cudaStream_t>(stream), h, w, bias, labels, logits_out, dh, dw, db,
+                              dh_colsum, metrics, B, K, C, grad_scale, relu_mask, passes));
+    B2D_CUDA_CHECK(cudaGetLastError());
+    return B2D_OK;
+  }
   const size_t smem =
       ((size_t)2 * K * C + (2 * kHeadRows + 1) * K + kHeadRows * kHeadMaxC + 2 * kHeadRows) * sizeof(float);
   B2D_REQUIRE(smem <= 200 * 1024, "dense_xent_head: K*C too large for the fused head (K=%d C=%d)", K, C);

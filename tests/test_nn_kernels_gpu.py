@@ -44,7 +44,8 @@ def test_conv_c1_pool_forward_and_backward(N, H, W, Co, KS):
     assert torch.allclose(db, b.grad, atol=2e-3 * b.grad.abs().max().item(), rtol=1e-3)
 
 
-@pytest.mark.parametrize("B,K,C,relu_mask", [(64, 64, 10, True), (1024, 1024, 10, True), (37, 50, 7, False), (5000, 256, 32, True)])
+@pytest.mark.parametrize("B,K,C,relu_mask", [(64, 64, 10, True), (1024, 1024, 10, True), (37, 50, 7, False), (5000, 256, 32, True),
+                                              (1000, 512, 16, True), (300, 96, 3, False)])   # wide-batch variant, ragged
 def test_dense_xent_head_matches_autograd(B, K, C, relu_mask):
     from distributed_b200.ops import nn
     g = _gen(B + K)
