@@ -39,6 +39,19 @@ def _worker(ctx, n, algo, steps=5, epochs=2, env=None):
     return json.dumps(out)
 
 
+_BASE = {}
+
+
+def _baseline(n, algo, steps):
+    """Default-schedule run, shared by the tests that compare against it (one gang launch instead of one each)."""
+    from distributed_b200.launch import barrier_apply
+    key = (n, algo, steps)
+    if key not in _BASE:
+        _BASE[key] = json.loads(barrier_apply(lambda ctx: _worker(ctx, n, algo, steps=steps, epochs=1), n,
+                                              timeout=900)[0])
+    return _BASE[key]
+
+
 def _ngpu():
     import torch
     return torch.cuda.device_count()
@@ -87,7 +100,7 @@ def test_optional_update_schedules_keep_replicas_identical_and_match_the_default
     graphs over the same arithmetic: replicas must stay bit-identical and the trajectory must match the default."""
     from distributed_b200.launch import barrier_apply
     n = min(_ngpu(), 8)
-    base = json.loads(barrier_apply(lambda ctx: _worker(ctx, n, "auto", steps=4, epochs=1), n, timeout=600)[0])
+    base = _baseline(n, "auto", 4)
     assert "overlapped bucket" in base["schedule"]
     res = [json.loads(s) if s.startswith("{") else s for s in
            barrier_apply(lambda ctx: _worker(ctx, n, "auto", steps=4, epochs=1, env=env), n, timeout=600)]
@@ -110,7 +123,7 @@ def test_debug_mode_stress_random_delays_poison_and_monotone_flags(algo):
     from distributed_b200.launch import barrier_apply
     n = min(_ngpu(), 8)
     steps = 300
-    ref = json.loads(barrier_apply(lambda ctx: _worker(ctx, n, algo, steps=steps, epochs=1), n, timeout=900)[0])
+    ref = _baseline(n, algo, steps)
     res = [json.loads(s) if s.startswith("{") else s for s in
            barrier_apply(lambda ctx: _worker(ctx, n, algo, steps=steps, epochs=1,
                                              env={"B200DIST_AR_DEBUG": "1"}), n, timeout=900)]

@@ -67,11 +67,13 @@ def main():
     for nbytes in sizes:
         n = nbytes // 4
         row = {"bytes": nbytes}
-        iters = args.iters if nbytes <= (64 << 20) else max(5, args.iters // 4)
-        algos = [("oneshot", 0), ("twoshot", 1)] + ([("nvls", 2)] if comm.mc_base else [])
+        iters = args.iters if nbytes <= (64 << 20) else max(4, args.iters // 5)
+        algos = [("oneshot", 0), ("twoshot", 1), ("pull", 3)] + ([("nvls", 2)] if comm.mc_base else [])
+        picked = int(lib.b2d_allreduce_pick_algo(n + 4, world, 1 if comm.mc_base else 0))
+        row["picked"] = {0: "oneshot", 1: "twoshot", 2: "nvls", 3: "pull"}[picked]
         for name, algo in algos:
-            if algo == 0 and nbytes > (16 << 20):
-                continue
+            if algo in (0, 3) and nbytes > (16 << 20) and algo != picked:
+                continue                      # latency variants: pointless (and slow) far above their range
             d = symm.AllreduceDesc()
             for p in range(world):
                 d.w[p], d.g[p] = comm.base[p] + comm.off_w, comm.base[p] + comm.off_g
@@ -80,6 +82,21 @@ def main():
                 d.w_mc, d.g_mc = comm.mc_base + comm.off_w, comm.mc_base + comm.off_g
             d.n_params, d.n_total, d.lr = n, n + 4, 1e-3
             d.rank, d.world, d.algo, d.emulate, d.plain, d.blocks = rank, world, algo, 0, 0, 0
+            if algo == picked:
+                # correctness of the dispatched variant at this size: w -= lr/N * sum(g) against NCCL's sum
+                gen = torch.Generator(device="cuda").manual_seed(1000 * rank + n % 9973)
+                src = torch.randn(min(n, 1 << 22), device="cuda", generator=gen)
+                m = src.numel()
+                g[:m].copy_(src); g[m:n + 4].zero_(); w[:n + 4].zero_()
+                ref = src.clone()
+                dist.all_reduce(ref, group=nccl)
+                comm.barrier()
+                nl.check(lib.b2d_allreduce_sgd(C.byref(d), st), "ar")
+                comm.barrier()
+                err = float((w[:m] + (1e-3 / world) * ref).abs().max() / ((1e-3 / world) * ref.abs().max()))
+                row["picked_rel_err_vs_nccl"] = err
+                assert err < 1e-4, (nbytes, name, err)
+                assert float(g[:n + 4].abs().max()) == 0.0, "gradient arena not zeroed"
             t = timed(lambda: nl.check(lib.b2d_allreduce_sgd(C.byref(d), st), "ar"), iters)
             row[name + "_us"] = t * 1e6
             row[name + "_busbw"] = 2 * (world - 1) / world * nbytes / t / 1e9

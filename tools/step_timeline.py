@@ -41,7 +41,10 @@ def make_step_updates(self, *a, **k):
 
 symm.SymmComm.make_update, symm.SymmComm.make_step_updates = make_update, make_step_updates
 steps = 400                               # even: slot 1 holds the last step, slot 0 the one before
-model.fit(x, y, batch_size=gb, epochs=1, steps_per_epoch=steps, verbose=0)
+model.fit(x, y, batch_size=gb, epochs=1, steps_per_epoch=4, verbose=0)          # builds the trainer / graphs
+t = model._trainer
+xd, yd = x.to(t.be.device), y.to(t.be.device)                                   # device-resident data, as in bench.py
+t.run_steps(xd, yd, 4, 16, steps - 4, gb)
 torch.cuda.synchronize()
 if len(ll_bufs) == 2:
     ll = [b.view(64, 4).cpu()[0].double() / 1e3 for b, _ in ll_bufs]            # block 0 of each slot, us
