@@ -228,6 +228,11 @@ def run_ours(args) -> dict:
         torch.cuda.empty_cache()
         same = {}
         variants = [("eager", False)] + ([("graph", True)] if world == 1 else [])
+        # NCCL prints its version banner to stdout when DDP initialises it: this process must print exactly
+        # ONE line (the JSON), so stdout is pointed at stderr for the duration of the baseline arm.
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         for name, use_graph in variants:
             try:
                 a2 = argparse.Namespace(**vars(args))
@@ -241,6 +246,9 @@ def run_ours(args) -> dict:
                     same[f"e2e_ratio_vs_{name}"] = e2e / r["e2e"]["value"]
             except Exception as exc:                                   # the framework's own line must survive
                 same[name] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        os.close(saved_stdout)
         out["baseline_same_box"] = same
     return out if rank == 0 else {}
 
@@ -303,7 +311,18 @@ def main():
         if int(os.environ.get("RANK", "0")) == 0:
             print(json.dumps(out), flush=True)
         return
-    out = run_torch(args) if args.impl == "torch" else run_ours(args)
+    if args.impl == "torch":
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)                     # NCCL's version banner goes to stderr; stdout carries the JSON line only
+        try:
+            out = run_torch(args)
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
+    else:
+        out = run_ours(args)
     if out:
         print(json.dumps(out), flush=True)
     import torch.distributed as dist

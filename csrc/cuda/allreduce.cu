@@ -544,16 +544,17 @@ extern "C" size_t b2d_allreduce_epoch_bytes(void) { return sizeof(uint32_t) * kM
 // it the (N-1)/N traffic of two-shot (or S/N of NVLS) wins on bandwidth.
 extern "C" int b2d_allreduce_pick_algo(int64_t n_total_floats, int world, int have_multicast) {
   const int64_t bytes = n_total_floats * 4;
-  // Measured on 8 x B200 (profiles/r01_allreduce.md): one-shot (single barrier, reads only) wins
-  // at 2 ranks and for tiny messages; with multicast bound the switch reduction wins from
-  // ~256 KB up at >= 4 ranks; without it the pull variant is the latency choice up to a few MB.
-  // At 2 ranks one-shot and two-shot move the same bytes, but two-shot uses both link directions: it wins
-  // from a few MB up (16 MB: 48 vs 54 us).
+  // Measured on 2 / 4 / 8 x B200 (profiles/r02_allreduce.md):
+  // * 2 ranks: one-shot and two-shot move the same bytes, two-shot uses both link directions and wins from
+  //   a few MB up (16 MB: 45 vs 46 us, 1 GB: 2.09 ms); NVLS never wins with two ranks.
+  // * with multicast bound and >= 3 ranks the switch-side reduction is the fastest variant from 8 KB up
+  //   (8 ranks: 64 KB 15.7 vs 20.6 us two-shot, 16 MB 70 vs 82 us, 256 MB 708 vs 897 us); below that one
+  //   barrier less makes one-shot as good.
+  // * without multicast two-shot wins from 16 KB; the pull variant (an acquire/release pair per phase) is
+  //   never the fastest and is only used when asked for by name.
   if (world <= 2) return bytes >= (4 << 20) ? kTwoShot : kOneShot;
-  if (bytes <= (256 << 10) / world * 2) return kOneShot;
-  if (have_multicast && bytes >= (256 << 10)) return kNvls;
-  if (bytes <= (4 << 20)) return kPull;
-  return kTwoShot;
+  if (have_multicast) return bytes >= (8 << 10) ? kNvls : kOneShot;
+  return bytes >= (16 << 10) ? kTwoShot : kOneShot;
 }
 
 extern "C" int b2d_allreduce_sgd(const b2d_allreduce_desc* d, void* stream) {

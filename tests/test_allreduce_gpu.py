@@ -252,7 +252,9 @@ def test_algo_dispatch_by_size():
     lib = nl.lib()
     symm._declare(lib)
     assert lib.b2d_allreduce_pick_algo(1024, 8, 0) == 0            # 4 KB: one-shot
-    assert lib.b2d_allreduce_pick_algo(347204, 8, 0) == 3          # README gradient, no multicast: pull
+    assert lib.b2d_allreduce_pick_algo(1024, 8, 1) == 0
+    assert lib.b2d_allreduce_pick_algo(16384, 8, 1) == 2           # 64 KB with multicast: NVLS (not pull)
+    assert lib.b2d_allreduce_pick_algo(347204, 8, 0) == 1          # README gradient, no multicast: two-shot
     assert lib.b2d_allreduce_pick_algo(347204, 8, 1) == 2          # README gradient with multicast: NVLS
     assert lib.b2d_allreduce_pick_algo(1 << 24, 8, 1) == 2         # 64 MB with multicast: NVLS
     assert lib.b2d_allreduce_pick_algo(1 << 24, 8, 0) == 1         # 64 MB without multicast: two-shot
