@@ -117,7 +117,7 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 }
 
 // Applies bias / ReLU / mask to four consecutive columns of one row and stores them.
-template <bool OUT_BF16>
+template <bool OUT_BF16, bool SCATTER = false>
 __device__ __forceinline__ void epilogue_store4(const GemmArgs& a, int row, int col, float v0,
                                                 float v1, float v2, float v3) {
   if (a.bias != nullptr) {
@@ -150,7 +150,7 @@ __device__ __forceinline__ void epilogue_store4(const GemmArgs& a, int row, int 
     v0 = m.x > 0.f ? v0 : 0.f, v1 = m.y > 0.f ? v1 : 0.f;
     v2 = m.z > 0.f ? v2 : 0.f, v3 = m.w > 0.f ? v3 : 0.f;
   }
-  if (a.flags & kFlagScatter) {
+  if (SCATTER) {      // compiled into the reduce-scatter instantiations only: run-once kernels pay for every instruction
     const long long idx = a.sc.d_off + (long long)row * a.ldd + col;
     const int owner = min(a.sc.world - 1, static_cast<int>((idx - a.sc.seg_begin) / a.sc.per));
     red_add_f4_sys(a.sc.base[owner] + idx, v0, v1, v2, v3);
@@ -229,7 +229,7 @@ struct GemmCfg {
       umma_idesc(KIND == MmaKind::TF32 ? 2u : 1u, A_MN ? 1u : 0u, B_MN ? 1u : 0u, kBlockM, BLOCK_N);
 };
 
-template <MmaKind KIND, bool A_MN, bool B_MN, int BLOCK_N, bool OUT_BF16>
+template <MmaKind KIND, bool A_MN, bool B_MN, int BLOCK_N, bool OUT_BF16, bool SCATTER = false>
 __global__ void __launch_bounds__(256, 2) gemm_tc_kernel(const __grid_constant__ GemmArgs args) {
   // Persistent CTA: tiles (m, n, k-split) are walked with stride gridDim.x.  The accumulator is
   // double-buffered in tensor memory, so the epilogue warps drain tile t while the MMA thread is already
@@ -528,7 +528,7 @@ __global__ void __launch_bounds__(256, 2) gemm_tc_kernel(const __grid_constant__
                 if (finalize)
                   red_add_f4(args.ws + (long long)row * args.ldws + col, f0, f1, f2, f3);
                 else
-                  epilogue_store4<OUT_BF16>(args, row, col, f0, f1, f2, f3);
+                  epilogue_store4<OUT_BF16, SCATTER>(args, row, col, f0, f1, f2, f3);
               }
             }
           }
@@ -971,6 +971,7 @@ struct b2d_gemm_plan {
   int smem_bytes;     // maximum the kernel instantiation may ask for (function attribute)
   int launch_smem;    // what this plan actually launches with (ring depth of this problem)
   int grid;           // persistent CTAs: min(tiles, SMs x CTAs that fit an SM together)
+  int dtype, a_mn, b_mn, out_dtype;   // what the kernel was instantiated for (b2d_gemm_plan_set_scatter re-selects)
 };
 
 // Last step of every plan constructor: publish the tile grid to the kernel and size the launch.
@@ -1111,6 +1112,7 @@ extern "C" int b2d_gemm_plan_create(const b2d_gemm_desc* desc, b2d_gemm_plan** o
   a.stages = g.stages;
   p->launch_smem = g.smem_bytes;
   p->geo = g;
+  p->dtype = d.dtype, p->a_mn = d.a_mn_major, p->b_mn = d.b_mn_major, p->out_dtype = d.out_dtype;
   if (g.pair) {
     if (d.dtype == B2D_F32)
       select_pair<MmaKind::TF32>(d.a_mn_major, d.b_mn_major, g.block_n, d.out_dtype, &p->kernel, &p->smem_bytes);
@@ -1159,6 +1161,25 @@ extern "C" int b2d_gemm_plan_set_scatter(b2d_gemm_plan* p, const b2d_gemm_scatte
               "gemm_plan_set_scatter: D is not at d_off inside this replica's arena");
   a.sc.d_off = sc->d_off, a.sc.seg_begin = sc->seg_begin, a.sc.per = sc->per, a.sc.world = sc->world;
   a.flags |= kFlagScatter;
+  // The reduce-scatter epilogue is its own instantiation (the weight-gradient layout: both operands MN-major,
+  // fp32 output), so every other GEMM of a step stays free of its instructions.
+  B2D_REQUIRE(p->a_mn && p->b_mn && p->out_dtype == B2D_F32 && !p->geo.pair && a.cv.enabled == 0,
+              "gemm_plan_set_scatter: only plain weight-gradient GEMMs (A and B MN-major, fp32 output) can scatter");
+#define B2D_SCATTER_PICK(KIND)                                                          \
+  switch (p->geo.block_n) {                                                             \
+    case 32: p->kernel = gemm_tc_kernel<KIND, true, true, 32, false, true>; break;     \
+    case 64: p->kernel = gemm_tc_kernel<KIND, true, true, 64, false, true>; break;     \
+    case 128: p->kernel = gemm_tc_kernel<KIND, true, true, 128, false, true>; break;   \
+    default: p->kernel = gemm_tc_kernel<KIND, true, true, 256, false, true>; break;    \
+  }
+  if (p->dtype == B2D_F32) {
+    B2D_SCATTER_PICK(MmaKind::TF32)
+  } else {
+    B2D_SCATTER_PICK(MmaKind::F16)
+  }
+#undef B2D_SCATTER_PICK
+  B2D_CUDA_CHECK(cudaFuncSetAttribute(reinterpret_cast<const void*>(p->kernel),
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, p->smem_bytes));
   return B2D_OK;
 }
 

@@ -8,7 +8,11 @@ from __future__ import annotations
 import ctypes as C
 from pathlib import Path
 
-LIB_PATH = Path(__file__).resolve().parents[1] / "_lib" / "libb200dist_cuda.so"
+import os
+
+# B200DIST_CUDA_LIB: load another build of the library (A/B measurements of two builds on one box)
+LIB_PATH = Path(os.environ.get("B200DIST_CUDA_LIB") or
+                Path(__file__).resolve().parents[1] / "_lib" / "libb200dist_cuda.so")
 
 _lib = None
 
