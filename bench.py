@@ -260,7 +260,7 @@ BASELINE_MD = {("mnist_cnn", 1): 361255.0, ("mnist_cnn", 2): 154879.0, ("mnist_c
                ("resnet50", 1): 3151.0, ("resnet50", 8): 15868.0}
 DEFAULT_BATCH = {"mnist_cnn": 64, "scaled_cnn": 1024, "resnet50": 32}
 
-ALIGN_STEPS = 8      # untimed steps enqueued right before the start event (device-side rank alignment)
+ALIGN_STEPS = 32     # untimed steps enqueued right before the start event (device-side rank alignment, clocks up)
 
 MODEL_INPUT = {"mnist_cnn": ((28, 28, 1), 10), "scaled_cnn": ((28, 28, 1), 10), "resnet50": ((224, 224, 3), 1000)}
 MODEL_NAMES = {"mnist_cnn": "README MNIST CNN (conv32-3x3/maxpool/dense64/dense10, SGD lr=1e-3)",
