@@ -12,6 +12,7 @@
 #include <errno.h>
 #include <fcntl.h>
 #include <sched.h>
+#include <signal.h>
 #include <sys/mman.h>
 #include <sys/stat.h>
 #include <time.h>
@@ -34,6 +35,8 @@ struct alignas(64) Header {
   std::atomic<uint32_t> generation;
   int32_t world;
   int64_t capacity;  // floats per slot
+  int32_t creator_pid;   // rank 0 of THIS run: attachers reject a segment whose creator is gone (left by a crashed run)
+  int64_t created_ns;    // CLOCK_REALTIME at creation, for the error message
 };
 
 constexpr uint32_t kMagic = 0xB200D157u;
@@ -97,6 +100,7 @@ B2C_API b2c_shm_comm* b2c_shm_create(const char* name, int rank, int world, int6
   c->timeout_s = timeout_s > 0 ? timeout_s : 120.0;
   c->bytes = sizeof(Header) + sizeof(float) * (size_t)capacity_floats * (world + 1);
   int fd = -1;
+  void* p = MAP_FAILED;
   const double t0 = now_s();
   if (rank == 0) {
     shm_unlink(name);
@@ -105,55 +109,78 @@ B2C_API b2c_shm_comm* b2c_shm_create(const char* name, int rank, int world, int6
       close(fd);
       fd = -1;
     }
-  } else {
-    while (true) {
-      fd = shm_open(name, O_RDWR, 0600);
-      if (fd >= 0) {
-        struct stat st;
-        if (fstat(fd, &st) == 0 && (size_t)st.st_size >= c->bytes) break;
-        close(fd);
-        fd = -1;
-      }
-      if (now_s() - t0 > c->timeout_s) break;
-      usleep(2000);
+    if (fd < 0) {
+      snprintf(t_err, sizeof(t_err), "shm_create: cannot create %s: %s", name, strerror(errno));
+      delete c;
+      return nullptr;
     }
-  }
-  if (fd < 0) {
-    snprintf(t_err, sizeof(t_err), "shm_create: cannot open %s: %s", name, strerror(errno));
-    delete c;
-    return nullptr;
-  }
-  void* p = mmap(nullptr, c->bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
-  close(fd);
-  if (p == MAP_FAILED) {
-    snprintf(t_err, sizeof(t_err), "shm_create: mmap failed: %s", strerror(errno));
-    delete c;
-    return nullptr;
-  }
-  c->hdr = static_cast<Header*>(p);
-  c->slots = reinterpret_cast<float*>(static_cast<char*>(p) + sizeof(Header));
-  c->result = c->slots + (size_t)capacity_floats * world;
-  if (rank == 0) {
+    p = mmap(nullptr, c->bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+    close(fd);
+    if (p == MAP_FAILED) {
+      snprintf(t_err, sizeof(t_err), "shm_create: mmap failed: %s", strerror(errno));
+      delete c;
+      return nullptr;
+    }
+    c->hdr = static_cast<Header*>(p);
+    timespec ts;
+    clock_gettime(CLOCK_REALTIME, &ts);
     c->hdr->world = world;
     c->hdr->capacity = capacity_floats;
+    c->hdr->creator_pid = static_cast<int32_t>(getpid());
+    c->hdr->created_ns = static_cast<int64_t>(ts.tv_sec) * 1000000000ll + ts.tv_nsec;
     c->hdr->arrive.store(0);
     c->hdr->generation.store(0);
     c->hdr->attached.store(1);
     c->hdr->magic.store(kMagic, std::memory_order_release);
   } else {
-    while (c->hdr->magic.load(std::memory_order_acquire) != kMagic) {
-      if (now_s() - t0 > c->timeout_s) {
-        snprintf(t_err, sizeof(t_err), "shm_create: rank 0 never initialised %s", name);
-        munmap(p, c->bytes);
-        delete c;
-        return nullptr;
+    // Open, map, wait for rank 0's magic — and make sure the segment belongs to a LIVE run: the name repeats
+    // across runs (TF_CONFIG ports are fixed), so a segment left behind by a crashed run may still be there until
+    // this run's rank 0 replaces it.  A segment whose creator process no longer exists is dropped and reopened.
+    while (true) {
+      fd = shm_open(name, O_RDWR, 0600);
+      if (fd >= 0) {
+        struct stat st;
+        if (fstat(fd, &st) == 0 && (size_t)st.st_size >= c->bytes) {
+          p = mmap(nullptr, c->bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+          close(fd);
+          fd = -1;
+          if (p != MAP_FAILED) {
+            Header* h = static_cast<Header*>(p);
+            bool stale = false;
+            while (h->magic.load(std::memory_order_acquire) != kMagic && now_s() - t0 <= c->timeout_s) usleep(1000);
+            if (h->magic.load(std::memory_order_acquire) == kMagic) {
+              const pid_t creator = static_cast<pid_t>(h->creator_pid);
+              stale = creator <= 0 || (kill(creator, 0) != 0 && errno == ESRCH) || h->world != world ||
+                      h->capacity != capacity_floats;
+              if (!stale) {
+                c->hdr = h;
+                break;
+              }
+            }
+            munmap(p, c->bytes);
+            p = MAP_FAILED;
+          }
+        } else {
+          close(fd);
+          fd = -1;
+        }
       }
-      usleep(1000);
+      if (now_s() - t0 > c->timeout_s) break;
+      usleep(2000);
+    }
+    if (c->hdr == nullptr) {
+      snprintf(t_err, sizeof(t_err), "shm_create: no live segment %s appeared within %.0f s (rank 0 missing, or only "
+               "a stale segment of a crashed run was found)", name, c->timeout_s);
+      delete c;
+      return nullptr;
     }
     c->hdr->attached.fetch_add(1);
   }
+  c->slots = reinterpret_cast<float*>(reinterpret_cast<char*>(c->hdr) + sizeof(Header));
+  c->result = c->slots + (size_t)capacity_floats * world;
   if (barrier(c) != 0) {  // everyone is attached: rank 0 may unlink the name
-    munmap(p, c->bytes);
+    munmap(c->hdr, c->bytes);
+    if (rank == 0) shm_unlink(name);
     delete c;
     return nullptr;
   }

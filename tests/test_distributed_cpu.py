@@ -79,6 +79,38 @@ def test_shm_allreduce_three_ranks_odd_sizes():
         assert all(out) and same is True and diff is False
 
 
+def _shm_after_crash(ctx):
+    """Rank 1 starts first and finds the segment a crashed earlier run left under the same name; rank 0 arrives
+    late and replaces it.  Rank 1 must drop the stale segment (its creator process is gone) and join the new one."""
+    import struct
+    import subprocess
+    import time
+    import torch
+    from distributed_b200.parallel.comm import ShmComm
+    job = "stale" + ctx.address[0].split(":")[1]
+    cap, world = 1 << 12, 2
+    path = f"/dev/shm/b200dist-{job}"
+    if ctx.partition == 1:
+        dead = subprocess.Popen(["true"])
+        dead.wait()                                              # a pid that no longer exists
+        hdr = struct.pack("<IIIIi4xqi4xq", 0xB200D157, 2, 1, 7, world, cap, dead.pid, 0)
+        with open(path, "wb") as f:
+            f.write(hdr.ljust(64, b"\0") + b"\0" * (4 * cap * (world + 1)))
+    else:
+        time.sleep(1.0)                                          # let rank 1 open the stale segment first
+    c = ShmComm(job, ctx.partition, world, cap, timeout_s=30.0)
+    t = torch.full((100,), float(ctx.partition + 1))
+    c.allreduce(t)
+    ok = bool((t == 3.0).all())
+    c.close()
+    return json.dumps(ok)
+
+
+def test_shm_attach_ignores_the_segment_of_a_crashed_run():
+    res = barrier_apply(_shm_after_crash, 2, timeout=120)
+    assert [json.loads(s) for s in res] == [True, True], res
+
+
 def _train_bn(ctx, num_workers, per_worker=8):
     """A BatchNorm model: per-replica batch statistics, moving statistics averaged over replicas."""
     import os
