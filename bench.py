@@ -63,14 +63,23 @@ class ClockSampler:
 
     def _poll(self):
         n = self._nvml
+        k = 0
         while not self._stop.is_set():
             try:
+                # the clock on every poll (one NVML call, so that a timed region of a few milliseconds still gets
+                # several samples); throttle reasons and power on every fourth
                 self.sm.append(float(n.nvmlDeviceGetClockInfo(self._h, n.NVML_CLOCK_SM)))
-                self.mask |= int(n.nvmlDeviceGetCurrentClocksEventReasons(self._h))
-                self.power_w = max(self.power_w, n.nvmlDeviceGetPowerUsage(self._h) / 1000.0)
+                if k % 4 == 0:
+                    self.mask |= int(n.nvmlDeviceGetCurrentClocksEventReasons(self._h))
+                    self.power_w = max(self.power_w, n.nvmlDeviceGetPowerUsage(self._h) / 1000.0)
             except Exception:
                 pass
+            k += 1
             self._stop.wait(self.period)
+        try:                      # reasons once more at the end, so that a short region cannot miss them
+            self.mask |= int(n.nvmlDeviceGetCurrentClocksEventReasons(self._h))
+        except Exception:
+            pass
 
     def __enter__(self):
         if self._nvml is not None:

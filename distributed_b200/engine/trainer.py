@@ -425,6 +425,10 @@ class Trainer:
     def metric_sums(self) -> tuple[float, float, float]:
         """Running (loss_sum, correct, samples) since the last reset, summed over replicas."""
         self.sync()
+        if self._exec is not None and self.use_graph and self.steps_done() > getattr(self, "_reset_at", -1) >= 0:
+            # the executor streamed the sums of every step into the pinned ring: no extra device read
+            t = self.metrics_host[(self.steps_done() - 1) % self.ring_len]
+            return float(t[0]), float(t[1]), float(t[2])
         t = self.params[self.layout.n_params:self.layout.n_total].detach().cpu()
         return float(t[0]), float(t[1]), float(t[2])
 
@@ -439,6 +443,15 @@ class Trainer:
         return self.metrics_host.numpy()[idx].copy()
 
     def reset_metrics(self):
+        """Zero the running sums (start of an epoch).  The sums live in the tail of this replica's own weight
+        arena(s) and only this replica's kernels write them, so no cross-replica synchronisation is involved; in
+        graph mode the clear is queued on the executor's stream, ordered before the next step, with no host wait."""
+        if self._exec is not None and self.use_graph:
+            with torch.cuda.stream(self.stream):
+                for w in self.param_bufs:
+                    w[self.layout.n_params:self.layout.n_total].zero_()
+            self._reset_at = self.steps_done()
+            return
         self.sync()
         for w in self.param_bufs:
             w[self.layout.n_params:self.layout.n_total].zero_()
