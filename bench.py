@@ -177,7 +177,7 @@ def run_ours(args) -> dict:
     # of a short run.  ALIGN untimed steps are therefore enqueued on the same stream right before the start
     # event, with no host synchronisation in between: their fused all-reduce lines the replicas up on the
     # device, so the K timed steps are steady-state steps on every rank.
-    align = ALIGN_STEPS
+    align = ALIGN_STEPS if args.model == "mnist_cnn" else 32      # ~10 ms / ~20-180 ms of untimed steady-state steps
     _barrier(world)
     torch.cuda.synchronize()
     with ClockSampler(local) as clocks:
@@ -242,6 +242,18 @@ def run_ours(args) -> dict:
         sys.stdout.flush()
         saved_stdout = os.dup(1)
         os.dup2(2, 1)
+
+        # The framework's own result must not depend on the baseline arm finishing: if it hangs (a NCCL problem on
+        # some box, a rank that failed while the others wait in a collective), every rank's watchdog prints / exits.
+        def bail():
+            out["baseline_same_box"] = {"error": f"the baseline arm did not finish within {args.baseline_timeout} s"}
+            os.dup2(saved_stdout, 1)
+            if rank == 0:
+                os.write(1, (json.dumps(out) + "\n").encode())
+            os._exit(0)
+        watchdog = threading.Timer(args.baseline_timeout, bail)
+        watchdog.daemon = True
+        watchdog.start()
         for name, use_graph in variants:
             try:
                 a2 = argparse.Namespace(**vars(args))
@@ -255,6 +267,7 @@ def run_ours(args) -> dict:
                     same[f"e2e_ratio_vs_{name}"] = e2e / r["e2e"]["value"]
             except Exception as exc:                                   # the framework's own line must survive
                 same[name] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+        watchdog.cancel()
         sys.stdout.flush()
         os.dup2(saved_stdout, 1)
         os.close(saved_stdout)
@@ -269,7 +282,8 @@ BASELINE_MD = {("mnist_cnn", 1): 365467.0, ("mnist_cnn", 2): 125524.0, ("mnist_c
                ("resnet50", 1): 3608.0, ("resnet50", 2): None, ("resnet50", 8): 15880.0}
 DEFAULT_BATCH = {"mnist_cnn": 64, "scaled_cnn": 1024, "resnet50": 32}
 
-ALIGN_STEPS = 32     # untimed steps enqueued right before the start event (device-side rank alignment, clocks up)
+ALIGN_STEPS = 200    # untimed steps enqueued right before the start event: device-side rank alignment, clocks up,
+                     # and a region long enough for the clock sampler to see several samples
 
 MODEL_INPUT = {"mnist_cnn": ((28, 28, 1), 10), "scaled_cnn": ((28, 28, 1), 10), "resnet50": ((224, 224, 3), 1000)}
 MODEL_NAMES = {"mnist_cnn": "README MNIST CNN (conv32-3x3/maxpool/dense64/dense10, SGD lr=1e-3)",
@@ -306,6 +320,8 @@ def main():
     ap.add_argument("--same-box-baseline", type=int, default=1,
                     help="ours: also run the stock-PyTorch arm in this process and report the ratio (0 = skip)")
     ap.add_argument("--baseline-steps", type=int, default=200, help="steps of the same-box baseline arm")
+    ap.add_argument("--baseline-timeout", type=float, default=300.0,
+                    help="seconds after which a stuck baseline arm is abandoned (the framework's line is printed anyway)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

@@ -47,18 +47,21 @@ void set_uniform_carveout(const void* kernel) {
   }
 }
 
+// Only used where no device can be queried (the GPU-less build host answering geometry queries).
+constexpr int kFallbackSmCount = 148;   // B200
+
 int sm_count() {
   static std::atomic<int> cached[64];
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
     (void)cudaGetLastError();
-    return 148;
+    return kFallbackSmCount;
   }
   int n = cached[dev].load(std::memory_order_relaxed);
   if (n == 0) {
     if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) {
       (void)cudaGetLastError();
-      n = 148;
+      n = kFallbackSmCount;
     }
     cached[dev].store(n, std::memory_order_relaxed);
   }
