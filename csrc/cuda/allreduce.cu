@@ -459,9 +459,9 @@ __global__ void __launch_bounds__(kLlThreads) ll_allreduce_sgd_kernel(const LlAr
   const int world = a.world;
   long long* dbg = a.dbg == nullptr ? nullptr : a.dbg + 4 * blockIdx.x;
   if (dbg != nullptr && threadIdx.x == 0) dbg[0] = ar_time_ns();
-  pdl_wait();     // this replica's backward has finished writing these gradients
-  pdl_trigger();
-  if (dbg != nullptr && threadIdx.x == 0) dbg[1] = ar_time_ns();
+  // Everything up to the gradient load is independent of the kernel this one is launched behind (the epoch
+  // counter is private to this kernel sequence, the weights were written by the previous step's update): with
+  // programmatic dependent launch it runs under the tail of the last backward kernel.
   if (threadIdx.x == 0) {
     uint32_t* ep = a.epoch[rank] + blockIdx.x;
     uint32_t e = *ep + 1;
@@ -479,16 +479,20 @@ __global__ void __launch_bounds__(kLlThreads) ll_allreduce_sgd_kernel(const LlAr
     if ((h & 3) == 0) __nanosleep(h % 20000);
   }
   if (a.debug) __syncthreads();
-  if (i >= n) return;
-  const long long idx = i < len0 ? a.seg_begin[0] + i : a.seg_begin[1] + (i - len0);
+  const bool active = i < n;
+  const long long idx = !active ? 0 : (i < len0 ? a.seg_begin[0] + i : a.seg_begin[1] + (i - len0));
   const size_t slot = static_cast<size_t>(e & 1) * kMaxRanks * kLlMaxFloats + i;
+  const float wv = active ? a.w[rank][idx] : 0.f;
+  pdl_wait();     // this replica's backward has finished writing these gradients
+  pdl_trigger();
+  if (dbg != nullptr && threadIdx.x == 0) dbg[1] = ar_time_ns();
+  if (!active) return;
   const float mine = a.g[rank][idx];
   const unsigned long long packed = (static_cast<unsigned long long>(e) << 32) | __float_as_uint(mine);
   for (int q = 1; q < world; ++q) {
     const int p = (rank + q) % world;
     st_relaxed_sys_u64(a.inbox[p] + slot + static_cast<size_t>(rank) * kLlMaxFloats, packed);
   }
-  const float wv = a.w[rank][idx];
   float sum = 0.f;
   long long t_start = 0;
   for (int p = 0; p < world; ++p) {          // fixed order: identical bits on every rank

@@ -39,8 +39,6 @@ __global__ void __launch_bounds__(256) conv_c1_pool_fwd_kernel(
     const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
     float* __restrict__ y, uint8_t* __restrict__ code, int H, int W, int Co, int PH, int PW,
     int band) {
-  pdl_wait();
-  pdl_trigger();
   extern __shared__ float xs[];  // [(2*band + KS) rows][W]
   const int n = blockIdx.x;
   const int ph0 = blockIdx.y * band;
@@ -48,7 +46,12 @@ __global__ void __launch_bounds__(256) conv_c1_pool_fwd_kernel(
   const int r0 = 2 * ph0;
   const int r1 = min(H, 2 * ph1 + KS - 1);
   const float* xi = x + (size_t)n * H * W;
+  // The input batch was copied in before this step's graph started (an earlier operation than the kernel this
+  // one is launched behind), so staging it does not have to wait for the predecessor: with programmatic
+  // dependent launch this overlaps the tail of the previous step's update.  The weights do.
   for (int i = threadIdx.x; i < (r1 - r0) * W; i += blockDim.x) xs[i] = xi[r0 * W + i];
+  pdl_wait();
+  pdl_trigger();
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
   const int npix = (ph1 - ph0) * PW;
@@ -101,8 +104,6 @@ template <int KS>
 __global__ void __launch_bounds__(256) conv_c1_pool_bwd_kernel(
     const float* __restrict__ x, const float* __restrict__ dy, const uint8_t* __restrict__ code,
     float* __restrict__ dw, float* __restrict__ db, int H, int W, int Co, int PH, int PW, int band) {
-  pdl_wait();
-  pdl_trigger();
   extern __shared__ float sm[];
   float* xs = sm;  // image band
   const int n = blockIdx.x;
@@ -113,7 +114,10 @@ __global__ void __launch_bounds__(256) conv_c1_pool_bwd_kernel(
   const int band_elems = (2 * band + KS) * W;
   float* red = sm + band_elems;  // [nwarp][KS*KS+1][32]
   const float* xi = x + (size_t)n * H * W;
+  // the input images do not depend on the predecessor kernel (see conv_c1_pool_fwd_kernel): stage them first
   for (int i = threadIdx.x; i < (r1 - r0) * W; i += blockDim.x) xs[i] = xi[r0 * W + i];
+  pdl_wait();
+  pdl_trigger();
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
   const int npix = (ph1 - ph0) * PW;
@@ -194,8 +198,6 @@ __global__ void __launch_bounds__(256) dense_xent_head_kernel(
     float* __restrict__ dw, float* __restrict__ db, float* __restrict__ dh_colsum,
     float* __restrict__ metrics, int B, int K, int C, float grad_scale, int relu_mask,
     int rows_per_cta) {
-  pdl_wait();
-  pdl_trigger();
   extern __shared__ float sm[];
   const int KC = K * C;
   float* ws = sm;                             // [K][C]
@@ -209,11 +211,15 @@ __global__ void __launch_bounds__(256) dense_xent_head_kernel(
   const int row0 = blockIdx.x * rows_per_cta;
   const int row1 = min(B, row0 + rows_per_cta);
   const bool multi_pass = row1 - row0 > kHeadRows;
+  // This layer's weights were last written by the previous step's update, which completed before the
+  // predecessor of this launch could even start: staging them overlaps the predecessor's tail.
 #pragma unroll 1
   for (int i = tid; i < KC; i += 256) ws[i] = w[i], accw[i] = 0.f;
 #pragma unroll 1
   for (int i = tid; i < K; i += 256) acck[i] = 0.f;
   float acc_b = 0.f, loss_sum = 0.f, correct_sum = 0.f;
+  pdl_wait();
+  pdl_trigger();
   __syncthreads();
 #pragma unroll 1
   for (int base = row0; base < row1; base += kHeadRows) {
@@ -335,8 +341,6 @@ __global__ void __launch_bounds__(256) dense_xent_head_wide_kernel(
     float* __restrict__ dw, float* __restrict__ db, float* __restrict__ dh_colsum,
     float* __restrict__ metrics, int B, int K, int C, float grad_scale, int relu_mask, int passes) {
   static_assert(kC == 16, "the float4 paths assume 16 classes per row");
-  pdl_wait();
-  pdl_trigger();
   constexpr int kRows = 8, kPitch = kC + 4, kOwnK = 4;       // K <= 256 * kOwnK
   extern __shared__ __align__(16) float sm[];
   float* ws = sm;                          // [K][kPitch]
@@ -359,6 +363,10 @@ __global__ void __launch_bounds__(256) dense_xent_head_wide_kernel(
     for (int c = 0; c < kC; ++c) accw[j][c] = 0.f;
   }
   float acc_b = 0.f, loss_sum = 0.f, correct_sum = 0.f;
+  // W was staged above without waiting: it was written by the previous step's update, which completed before the
+  // kernel this one is launched behind could start (programmatic dependent launch)
+  pdl_wait();
+  pdl_trigger();
   __syncthreads();
   const int row0 = blockIdx.x * (kRows * passes);
 #pragma unroll 1
