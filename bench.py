@@ -280,8 +280,8 @@ def run_ours(args) -> dict:
 
 # BASELINE.md section 3, stock PyTorch on the same 8 x B200 box (images/s; best recorded arrangement:
 # whole-step CUDA graph at 1 GPU, eager DDP/NCCL otherwise)
-BASELINE_MD = {("mnist_cnn", 1): 365467.0, ("mnist_cnn", 2): 125524.0, ("mnist_cnn", 4): 231515.0,
-               ("mnist_cnn", 8): 415281.0, ("scaled_cnn", 1): 505431.0, ("scaled_cnn", 8): 3619515.0,
+BASELINE_MD = {("mnist_cnn", 1): 366905.0, ("mnist_cnn", 2): 141688.0, ("mnist_cnn", 4): 271473.0,
+               ("mnist_cnn", 8): 506281.0, ("scaled_cnn", 1): 505431.0, ("scaled_cnn", 8): 3619515.0,
                ("resnet50", 1): 3608.0, ("resnet50", 2): None, ("resnet50", 8): 15880.0}
 DEFAULT_BATCH = {"mnist_cnn": 64, "scaled_cnn": 1024, "resnet50": 32}
 

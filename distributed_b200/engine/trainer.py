@@ -253,9 +253,23 @@ class Trainer:
             with torch.cuda.stream(self.branch_stream):
                 f()
 
+        # index of the last weight-gradient launch that goes to the side stream
+        last_side = max((i for i, f in enumerate(prog.backward) if side and getattr(f, "side_ok", False)
+                         and not (use_branch and getattr(f, "branch", False))), default=-1)
+        on_side = os.environ.get("B200DIST_BUCKET_ON_SIDE", "1") != "0"
+
         def issue_buckets(n_done):
             while early and early[0][0] <= n_done:
                 _, launch = early.pop(0)
+                if (on_side and state["forked"] and not state["open"] and not state["comm"]
+                        and n_done - 1 == last_side and not early):
+                    # The bucket became final with the LAST weight-gradient launch of the step and nothing else
+                    # will use the side stream: queue it right behind that launch on the same stream.  The edge
+                    # is then a programmatic one (the kernel is resident and waiting when its producer ends)
+                    # instead of a cross-stream dependency, which costs a launch latency on the critical path.
+                    with torch.cuda.stream(self.side_stream):
+                        launch()
+                    continue
                 streams = [main] + ([self.side_stream] if state["forked"] else []) + \
                           ([self.branch_stream] if state["open"] else [])
                 for st in streams:
