@@ -258,7 +258,8 @@ class CudaBackend:
             self.plans.append(plan)
             gemm = plan.run
             st = self.scatter_target
-            if (st is not None and plan.geometry.splits == 1 and dw.numel() >= st["min_floats"]
+            if (st is not None and plan.geometry.splits == 1 and not plan.geometry.pair
+                    and dw.numel() >= st["min_floats"]
                     and dw.numel() % 4 == 0 and dw.is_contiguous()):
                 off = (dw.data_ptr() - st["local"].data_ptr()) // 4
                 world = st["world"]

@@ -212,6 +212,10 @@ class Trainer:
             else:
                 self.kernels_per_step = None
         self.stream.synchronize()
+        if self.comm.world > 1:
+            # graph capture / instantiation takes a different time on every replica; meet here so that the first
+            # step's device-side waits start together (they are bounded by B200DIST_AR_TIMEOUT_S)
+            self.comm.barrier()
 
     def _run_step_branches(self, prog, sched=None):
         """Issue one step for capture.  Weight-gradient launches (tagged ``side_ok`` by the lowering) go to
