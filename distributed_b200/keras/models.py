@@ -268,7 +268,10 @@ class Sequential(Model):
                 if len(val) > 1:
                     logs["val_accuracy"] = val[1]
             history._append(epoch, logs)
-            if verbose:
+            if verbose == 2:      # Keras' one-line-per-epoch mode: no bar
+                print(f"{int(seen)}/{n_samples} - {dt:.0f}s - " + " - ".join(f"{k}: {v:.4f}" for k, v in logs.items()),
+                      file=out)
+            elif verbose:
                 line = self._progress_line(seen, n_samples, dt, steps, loss_sum, correct, final=True)
                 extra = "".join(f" - {k}: {v:.4f}" for k, v in logs.items() if k.startswith("val_"))
                 print(("\r" if live else "") + line + extra, file=out)
