@@ -51,7 +51,7 @@ class Group:
         return g
 
     def create_dataset(self, name: str, data) -> None:
-        self.children[name] = np.ascontiguousarray(data)
+        self.children[name] = np.require(np.asarray(data), requirements="C")    # keeps 0-d arrays 0-d
 
     def __getitem__(self, name):
         node = self
@@ -116,7 +116,7 @@ def _attribute(name: str, value) -> bytes:
     arr = _as_attr_array(value)
     nm = name.encode("utf8") + b"\0"
     dt, ds = _datatype_of(arr), _dataspace_of(arr.shape)
-    raw = arr.tobytes() if arr.dtype.kind != "S" else np.ascontiguousarray(arr).tobytes()
+    raw = np.require(arr, requirements="C").tobytes()
     body = struct.pack("<BBHHH", 1, 0, len(nm), len(dt), len(ds)) + _pad8(nm) + _pad8(dt) + _pad8(ds) + raw
     return _message(MSG_ATTRIBUTE, body)
 
@@ -143,7 +143,7 @@ class _Writer:
         self.buf[addr:addr + len(data)] = data
 
     def write_dataset(self, arr: np.ndarray, attrs: dict) -> int:
-        arr = np.ascontiguousarray(arr)
+        arr = np.require(np.asarray(arr), requirements="C")
         if arr.dtype.byteorder == ">":
             arr = arr.astype(arr.dtype.newbyteorder("<"))
         raw = arr.tobytes()

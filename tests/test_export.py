@@ -112,3 +112,71 @@ def test_layer_configs_accept_genuine_keras_keys_and_reject_what_cannot_be_honou
         L.Conv2D.from_config({**cfg, "dilation_rate": [2, 2]})
     with pytest.raises(ValueError):
         L.layer_from_config({"class_name": "LSTM", "config": {}})
+
+
+def test_hdf5_roundtrip_of_random_trees():
+    """Writer and reader agree on arbitrary small trees: nested groups (more entries than the default leaf size),
+    float / int data sets of any rank incl. empty ones, string and numeric attributes."""
+    from hypothesis import given, settings, strategies as st
+
+    names = st.text(alphabet="abcdefghijklmnopqrstuvwxyz0123456789_:", min_size=1, max_size=12)
+    shapes = st.lists(st.integers(0, 5), min_size=0, max_size=4).map(tuple)
+
+    @st.composite
+    def trees(draw, depth=0):
+        g = {"attrs": {}, "children": {}}
+        for k in draw(st.lists(names, max_size=3, unique=True)):
+            g["attrs"][k] = draw(st.one_of(st.text(alphabet="abc xyz{}:,\"", max_size=30),
+                                           st.lists(names, min_size=1, max_size=4),
+                                           st.integers(-5, 5), st.floats(-1e3, 1e3, width=32)))
+        for k in draw(st.lists(names, max_size=12 if depth == 0 else 3, unique=True)):
+            if depth < 2 and draw(st.booleans()):
+                g["children"][k] = draw(trees(depth + 1))
+            else:
+                shape = draw(shapes)
+                dt = draw(st.sampled_from([np.float32, np.float64, np.int32, np.int64, np.uint8]))
+                g["children"][k] = (np.arange(int(np.prod(shape)), dtype=np.float64).reshape(shape) - 3).astype(dt)
+        return g
+
+    def build(spec):
+        g = hdf5.Group()
+        g.attrs.update(spec["attrs"])
+        for k, v in spec["children"].items():
+            if isinstance(v, dict):
+                g.children[k] = build(v)
+            else:
+                g.create_dataset(k, v)
+        return g
+
+    def same(spec, g):
+        assert set(spec["children"]) == set(g.children)
+        for k, v in spec["attrs"].items():
+            got = g.attrs[k]
+            if isinstance(v, str):
+                assert hdf5.as_text(got) == v
+            elif isinstance(v, list):
+                assert [hdf5.as_text(x) for x in np.atleast_1d(got)] == v
+            else:
+                assert float(got) == float(np.float32(v)) or float(got) == float(v)
+        for k, v in spec["children"].items():
+            if isinstance(v, dict):
+                same(v, g.children[k])
+            else:
+                assert g.children[k].dtype == v.dtype and g.children[k].shape == v.shape
+                assert np.array_equal(g.children[k], v)
+
+    import tempfile, os
+
+    @settings(max_examples=40, deadline=None)
+    @given(trees())
+    def run(spec):
+        fd, path = tempfile.mkstemp(suffix=".h5")
+        os.close(fd)
+        try:
+            hdf5.write_file(path, build(spec))
+            assert hdf5.is_hdf5(path)
+            same(spec, hdf5.read_file(path))
+        finally:
+            os.remove(path)
+
+    run()
