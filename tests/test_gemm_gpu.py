@@ -40,7 +40,7 @@ CASES = [
     (2304 + 40, 2176 + 24, 2048, False, True),
     (2304 + 40, 2176 + 24, 2048, True, False),
     (2560, 2304, 2048, True, True),
-    (8192, 1152, 1024, False, False),  # 128-column pair tiles (less waste in the last wave)
+    (8192, 1152, 1024, False, False),  # last wave too ragged for pair tiles: stays on the single-CTA kernel
 ]
 
 
