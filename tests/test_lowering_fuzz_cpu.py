@@ -12,7 +12,7 @@ from hypothesis import given, settings, strategies as st
 from _torch_ref import torch_forward
 
 
-def _build(tf, L, draw):
+def _build(tf, L, draw, widths=(4, 8)):
     layers, c, hw = [], 3, 12
     first = True
 
@@ -23,17 +23,17 @@ def _build(tf, L, draw):
         return L.Conv2D(filters, k, strides=stride, padding=padding, use_bias=bias,
                         activation="relu" if relu else None, **kw)
 
-    c = draw(st.sampled_from([4, 8]))
+    c = draw(st.sampled_from(list(widths)))
     layers.append(conv(c, draw(st.sampled_from([1, 3])), relu=draw(st.booleans()), bias=draw(st.booleans())))
     for _ in range(draw(st.integers(1, 3))):
         kind = draw(st.sampled_from(["conv", "conv_valid", "bn", "pool", "relu", "res_id", "res_proj"]))
         if kind == "conv":
             stride = draw(st.sampled_from([1, 2])) if hw >= 6 else 1
-            c2 = draw(st.sampled_from([4, 8]))
+            c2 = draw(st.sampled_from(list(widths)))
             layers.append(conv(c2, draw(st.sampled_from([1, 3])), stride, "same", draw(st.booleans()), draw(st.booleans())))
             c, hw = c2, -(-hw // stride)
         elif kind == "conv_valid" and hw >= 5:
-            c2 = draw(st.sampled_from([4, 8]))
+            c2 = draw(st.sampled_from(list(widths)))
             layers.append(conv(c2, 3, 1, "valid", draw(st.booleans()), draw(st.booleans())))
             c, hw = c2, hw - 2
         elif kind == "relu":
@@ -51,7 +51,7 @@ def _build(tf, L, draw):
                 hw = -(-hw // 2)
         elif kind in ("res_id", "res_proj"):
             proj = kind == "res_proj"
-            c2 = draw(st.sampled_from([4, 8])) if proj else c
+            c2 = draw(st.sampled_from(list(widths))) if proj else c
             stride = draw(st.sampled_from([1, 2])) if (proj and hw >= 6) else 1
             main = [conv(4, 1, bias=False), L.BatchNormalization(momentum=0.9), L.ReLU(),
                     conv(c2, 3, stride, "same", bias=draw(st.booleans()))]
