@@ -3,26 +3,33 @@
 //
 // Every rank holds a weight arena W_r and a gradient arena G_r in symmetric memory: every GPU
 // can load/store every peer's arenas directly through NVSwitch (csrc/runtime/symm.cpp).
-// One kernel per step replaces "batch_all_reduce: 6 all-reduces" + 4 metric all-reduces + the
-// optimizer (README.md:403-407, 302).  Three algorithms, chosen per message size:
+// These kernels replace "batch_all_reduce: 6 all-reduces" + 4 metric all-reduces + the optimizer
+// (README.md:403-407, 302).  Variants of allreduce_sgd_kernel, chosen per message size
+// (b2d_allreduce_pick_algo) or by the producer of the gradients:
 //
 //   one-shot   every rank reads all peers' G, sums in rank order (bit-identical everywhere),
 //              updates its own W.                          traffic/GPU: (N-1) S in
 //   two-shot   rank r owns shard r: reads shard r of every G, averages, applies SGD, and writes
 //              the *updated weights* into every peer's W — the all-gather carries weights, so
 //              no optimizer pass exists at all.            traffic/GPU: (N-1)/N S in + out
-//   pull       latency-optimised two-shot: rank r reduces shard r and updates its OWN weights only;
-//              after a cheap flag (local fence, relaxed store) every rank *pulls* the other
-//              shards of the updated weights.  No remote writes -> no system-scope release.
+//   pull       two-shot without remote writes: rank r reduces shard r into its OWN weights, then
+//              (release / acquire flag pair) every rank pulls the other shards — block b pulls
+//              exactly what the owner's block b wrote.  Only used when asked for by name.
 //   NVLS       like two-shot, but the switch does the sum (multimem.ld_reduce) and the
 //              broadcast (multimem.st).                     traffic/GPU: S/N in + S/N out
+//   scattered  the producing GEMMs already added their tiles into the owners' arenas
+//              (gemm_tcgen05.cu, GEMM -> reduce-scatter): the owner reads its own shard, applies
+//              SGD, broadcasts the weights.                 traffic/GPU: S/N out (+ the GEMM's reds)
+// plus ll_allreduce_sgd_kernel, the push exchange for small buckets (below).
 //
 // Elements >= n_params are the metric tail slots (loss sum, correct count, ...): they are
 // summed, not averaged, and *added* to the running sums kept in W's tail.
 // After the update each rank zeroes its own G, so the next backward can accumulate into it.
 //
 // Cross-GPU barriers are per block: block b of every rank meets block b of every other rank
-// on monotone epoch counters in the peers' signal pads (st.release.sys / ld.acquire.sys).
+// on monotone epoch counters in the peers' signal pads (relaxed system-scope flags where the
+// barrier only announces earlier kernels' results, st.release.sys + one ld.acquire.sys where it
+// publishes this kernel's remote writes).  Waits are bounded by %globaltimer.
 //
 // Step schedule with weight ping-pong (engine/trainer.py): step t reads W[t&1] and the update
 // writes W[(t+1)&1], so an update can never collide with a kernel of the same step that still
