@@ -183,7 +183,7 @@ class MultiWorkerMirroredStrategy(_StrategyBase):
             else:
                 from .symm import SymmComm
                 c = SymmComm(self, tag, capacity, be.device)
-        log.info("Collective batch_all_reduce: gradients + metrics in 1 fused all-reduce+SGD, "
+        log.info("Collective batch_all_reduce: gradients + metrics fused with averaging and SGD, "
                  "num_workers = %d, implementation = %s", self.num_workers, c.description)
         return c
 

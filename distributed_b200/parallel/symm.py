@@ -1,12 +1,14 @@
 """SymmComm: the GPU communicator — fused all-reduce + average + SGD over NVLink peer memory.
 
-Each replica owns one block of *symmetric memory* (csrc/runtime/symm.cpp): weight arena,
-gradient arena and signal pads at the same offsets on every GPU, with every peer's block
-mapped into every process.  The per-step update is one kernel (csrc/cuda/allreduce.cu) that
-reads the peers' gradients and writes the peers' weights directly through NVSwitch — one-shot,
-two-shot or NVLS multicast, chosen by message size — and that is captured into the step's CUDA
-graph.  No NCCL call exists on this path; torch.distributed (gloo) is used only as the control
-plane (barriers around set-up, replica-consistency checks).
+Each replica owns one block of *symmetric memory* (csrc/runtime/symm.cpp): two weight arenas, two gradient
+arenas (both ping-pong with the two step graphs), signal pads and the LL inboxes at the same offsets on every GPU,
+with every peer's block mapped into every process and, where the fabric exposes it, an NVLS multicast view.
+The update of a step is a schedule of launches from csrc/cuda/allreduce.cu that read the peers' gradients and
+write the peers' weights directly through NVSwitch: overlapped buckets (one-shot, two-shot, NVLS by size, or
+"finish what the weight-gradient GEMM already reduce-scattered") plus a closing push exchange for the small last
+bucket — all captured into the step's CUDA graph (engine/trainer.py decides what runs when).  No NCCL call
+exists on this path; torch.distributed (gloo) is used only as the control plane (barriers around set-up,
+replica-consistency checks).
 
 This replaces the reference's "Collective batch_all_reduce: 6 all-reduces" + 4 metric
 all-reduces + optimizer step per iteration (README.md:403-407, 302).
