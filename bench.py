@@ -214,7 +214,8 @@ def run_ours(args) -> dict:
         "config": {"model": MODEL_NAMES[args.model],
                    "global_batch": global_batch, "batch_per_gpu": per_gpu, "input": "x".join(map(str, shape)),
                    "parallelism": f"dp{world}",
-                   "all_reduce": trainer.comm.description,
+                   "all_reduce": trainer.comm.description + (
+                       "; schedule: " + trainer.update_schedule if hasattr(trainer, "update_schedule") else ""),
                    "l2_policy": f"inputs larger than L2: each step reads a fresh batch of a {n_images}-image "
                                 f"({n_images * row_bytes / 1e6:.0f} MB) data set",
                    "kernels_per_step": trainer.kernels_per_step, "cuda_graph": trainer.use_graph,
